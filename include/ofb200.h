@@ -1,0 +1,103 @@
+/* ofb200 - C ABI of the B200-native variational optical-flow hot path.
+ *
+ * The reference (kursawe/OpticalFlow) is pure Python and has no FFI of its own; the boundary it exposes for
+ * this path is the Python function `variational_optical_flow` (source/optical_flow.py:715-1210).  Each entry
+ * point below replaces one stage of that function and cites it.  The Python drop-in
+ * (opticalflow_b200/optical_flow.py) binds these symbols with ctypes; INTEGRATION.md shows the stub a
+ * maintainer of the reference would add.
+ *
+ * Conventions
+ *   - return 0 on success, negative on error (text via ofb_last_error(), thread-local);
+ *   - every data pointer is a DEVICE pointer owned by the caller (e.g. torch.Tensor.data_ptr());
+ *     the library never allocates or frees device memory and keeps no global mutable state;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are asynchronous on it,
+ *     except ofb_solve, which synchronises the stream every `check_every` iterations to test convergence;
+ *   - `dtype`: OFB_F32 or OFB_F64 - the arithmetic and storage type of all image/vector arguments;
+ *   - B = number of frame pairs in the batch.  Images are [B][Nx][Ny] row-major; vectors are three SoA
+ *     planes [B][3][Nx][Ny] in the order ux, uy, remodelling (the reference's interleaved numbering
+ *     idx = 3*Ny*i + 3*j + q, :1291-1300, never exists on the device);
+ *   - per-pair regularisation weights alpha (speed_alpha) and beta (remodelling_alpha) are device arrays
+ *     of B doubles, so one batch can sweep regularisation weights (vary_regularisation, :1918-1998).
+ */
+#ifndef OFB200_H
+#define OFB200_H
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OFB_F32 0
+#define OFB_F64 1
+
+#define OFB_PRECOND_BJACOBI 0   /* pointwise 3x3 block-Jacobi */
+#define OFB_PRECOND_MG      1   /* geometric multigrid V-cycle, block-Jacobi smoother, dense coarsest solve */
+
+#define OFB_ABI_VERSION 1
+
+typedef struct ofb_solve_options {
+    int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
+    int    nu_pre;         /* pre-smoothing sweeps      default 2 */
+    int    nu_post;        /* post-smoothing sweeps     default 2 */
+    double omega;          /* Jacobi damping            default 0.8 */
+    int    check_every;    /* convergence poll period in iterations (host sync); default 1 */
+    int    rows_per_strip; /* 0 = choose from the batch size */
+    int    coarse_sweeps;  /* Jacobi sweeps on the coarsest level when it is too large for the dense solve; default 30 */
+    int    reserved;
+} ofb_solve_options;
+
+int         ofb_version(void);
+const char* ofb_last_error(void);
+void        ofb_default_options(ofb_solve_options* opt);
+
+/* Bytes of device workspace ofb_solve needs for this shape (caller allocates, contents need not be zeroed). */
+size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond);
+
+/* K1  Gaussian blur of F frames: replaces blur_movie (optical_flow.py:282-306 -> skimage.filters.gaussian,
+ *     mode 'nearest', truncate 4).  `weights` = device array of 2*radius+1 doubles (normalised kernel),
+ *     `tmp` = scratch of the same size as `in`.  in/out may not alias. */
+int ofb_blur(const void* in, void* out, void* tmp, const double* weights, int radius,
+             int F, int Nx, int Ny, int dtype, void* stream);
+
+/* K2  right-hand side of the linear system: replaces the derivative block and the RHS stores
+ *     (optical_flow.py:812-823, :889, :938, :962).  P = previous frames, C = current frames (both [B][Nx][Ny];
+ *     for a movie they are two overlapping views of the same frame stack), b3 out. */
+int ofb_build_rhs(const void* P, const void* C, void* b3, int B, int Nx, int Ny, int dtype, void* stream);
+
+/* K3  y = A x with the reference's assembled matrix (optical_flow.py:836-1072), boundary rows included;
+ *     matrix-free, nothing is assembled. */
+int ofb_apply(const void* P, const void* x3, void* y3, const double* alpha, const double* beta,
+              int B, int Nx, int Ny, int dtype, void* stream);
+
+/* K3e y = S x, the same operator with the ghost ring eliminated (what the Krylov solver iterates on):
+ *     ghost values of x are ignored (taken from the boundary rows), ghost rows of y are 0. */
+int ofb_apply_eliminated(const void* P, const void* x3, void* y3, const double* alpha, const double* beta,
+                         int B, int Nx, int Ny, int dtype, void* stream);
+
+/* K4/K5  solve A x = b: replaces the PETSc KSP solve (optical_flow.py:1081-1132; -ksp_type bcgs, rtol on the
+ *     unpreconditioned residual, nonzero initial guess).  x3: in = initial guess, out = solution (ghost ring
+ *     completed from the boundary rows).  Ghost-ring entries of b3 must be 0 (the reference never sets them,
+ *     :837).  iters_out/relres_out/converged_out: device arrays of length B (may be NULL). */
+int ofb_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta,
+              double rtol, int max_it, const ofb_solve_options* opt, void* workspace, size_t workspace_bytes,
+              int* iters_out, double* relres_out, int* converged_out,
+              int B, int Nx, int Ny, int dtype, void* stream);
+
+/* One application of the preconditioner z = M^-1 r (testing / diagnostics). */
+int ofb_precondition(const void* P, const void* r3, void* z3, const double* alpha, const double* beta,
+                     const ofb_solve_options* opt, void* workspace, size_t workspace_bytes,
+                     int B, int Nx, int Ny, int dtype, void* stream);
+
+/* K6  epilogue: replaces unpack + apply_constant_boundary_condition + functionals + scaling
+ *     (optical_flow.py:1159-1191).  functionals: device array [B][3] doubles = L1, speed, remodelling
+ *     functional of each pair (overwritten).  moments (may be NULL): device array [B][4] doubles = sum speed,
+ *     sum speed^2, sum remodelling, sum remodelling^2 over all Nx*Ny pixels - the summary statistics
+ *     vary_regularisation takes with np.mean/np.var (:1978-1981).  scale = delta_x/delta_t. */
+int ofb_epilogue(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma,
+                 double* functionals, double* moments, const double* alpha, const double* beta, double scale,
+                 int B, int Nx, int Ny, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OFB200_H */

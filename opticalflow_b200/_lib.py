@@ -1,0 +1,82 @@
+"""ctypes binding of the C ABI in ``include/ofb200.h`` (``libofb200.so``, built by ``__graft_entry__.build()``).
+
+There is no CPU fallback: if the shared library is missing, importing the symbols raises.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIBRARY_PATH = os.path.join(_HERE, 'libofb200.so')
+
+OFB_F32, OFB_F64 = 0, 1
+PRECOND_BJACOBI, PRECOND_MG = 0, 1
+ABI_VERSION = 1
+
+# every symbol include/ofb200.h declares
+EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_workspace_bytes', 'ofb_blur',
+                    'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_solve', 'ofb_precondition',
+                    'ofb_epilogue')
+
+
+class SolveOptions(ctypes.Structure):
+    _fields_ = [('precond', ctypes.c_int), ('nu_pre', ctypes.c_int), ('nu_post', ctypes.c_int),
+                ('omega', ctypes.c_double), ('check_every', ctypes.c_int), ('rows_per_strip', ctypes.c_int),
+                ('coarse_sweeps', ctypes.c_int), ('reserved', ctypes.c_int)]
+
+
+class OfbError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def load():
+    """Load libofb200.so (once).  Raises if it has not been built - the product path never falls back."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.isfile(LIBRARY_PATH):
+        raise OfbError('CUDA library %s not found: run `python -c "import __graft_entry__ as g; g.build()"` '
+                       '(nvcc, sm_100a). There is no CPU fallback.' % LIBRARY_PATH)
+    lib = ctypes.CDLL(LIBRARY_PATH)
+    vp, dp, ip, i, d, sz = (ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_double,
+                            ctypes.c_size_t)
+    lib.ofb_version.restype = i
+    lib.ofb_version.argtypes = []
+    lib.ofb_last_error.restype = ctypes.c_char_p
+    lib.ofb_last_error.argtypes = []
+    lib.ofb_default_options.restype = None
+    lib.ofb_default_options.argtypes = [ctypes.POINTER(SolveOptions)]
+    lib.ofb_workspace_bytes.restype = sz
+    lib.ofb_workspace_bytes.argtypes = [i, i, i, i, i]
+    lib.ofb_blur.restype = i
+    lib.ofb_blur.argtypes = [vp, vp, vp, dp, i, i, i, i, i, vp]
+    lib.ofb_build_rhs.restype = i
+    lib.ofb_build_rhs.argtypes = [vp, vp, vp, i, i, i, i, vp]
+    lib.ofb_apply.restype = i
+    lib.ofb_apply.argtypes = [vp, vp, vp, dp, dp, i, i, i, i, vp]
+    lib.ofb_apply_eliminated.restype = i
+    lib.ofb_apply_eliminated.argtypes = [vp, vp, vp, dp, dp, i, i, i, i, vp]
+    lib.ofb_solve.restype = i
+    lib.ofb_solve.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip,
+                              i, i, i, i, vp]
+    lib.ofb_precondition.restype = i
+    lib.ofb_precondition.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(SolveOptions), vp, sz, i, i, i, i, vp]
+    lib.ofb_epilogue.restype = i
+    lib.ofb_epilogue.argtypes = [vp, vp, vp, vp, vp, vp, vp, dp, dp, dp, dp, d, i, i, i, i, vp]
+    if lib.ofb_version() != ABI_VERSION:
+        raise OfbError('libofb200.so ABI version %d != expected %d' % (lib.ofb_version(), ABI_VERSION))
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc != 0:
+        raise OfbError('ofb200 error %d: %s' % (rc, load().ofb_last_error().decode()))
+
+
+def default_options():
+    opt = SolveOptions()
+    load().ofb_default_options(ctypes.byref(opt))
+    return opt

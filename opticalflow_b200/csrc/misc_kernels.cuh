@@ -1,0 +1,218 @@
+// ofb200 - pre/post kernels: Gaussian blur, right-hand side, full (non-eliminated) operator apply,
+// ghost-ring completion, epilogue (boundary overwrite, scaling, speed, functionals).
+#pragma once
+#include "transfer.cuh"
+#include "solver_kernels.cuh"
+
+namespace ofb {
+
+// ------------------------------------------------------------------ K1 separable Gaussian
+// skimage.filters.gaussian(frame, sigma, preserve_range=True) as called at optical_flow.py:303 ==
+// scipy.ndimage.gaussian_filter(mode='nearest', truncate=4.0): correlate1d along axis 0, then axis 1,
+// radius int(4 sigma + 0.5), clamp-to-edge.  One launch per axis; weights (double) from the host.
+template <typename T, int AXIS>
+__global__ void k_blur_axis(const T* __restrict__ in, T* __restrict__ out, int Nx, int Ny, long long frame_stride,
+                            const double* __restrict__ weights, int radius) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (j >= Ny) return;
+    const T* f = in + (long long)blockIdx.z * frame_stride;
+    T acc = T(0);
+    for (int k = -radius; k <= radius; ++k) {
+        const T w = T(weights[k + radius]);
+        if (AXIS == 0) acc += w * f[(long long)min(max(i + k, 0), Nx - 1) * Ny + j];
+        else           acc += w * f[(long long)i * Ny + min(max(j + k, 0), Ny - 1)];
+    }
+    out[(long long)blockIdx.z * frame_stride + (long long)i * Ny + j] = acc;
+}
+
+// ------------------------------------------------------------------ K2 right-hand side
+// b = (-I*Ixt, -I*Iyt, -It) on the interior, 0 on the ghost ring (optical_flow.py:815-823,:889,:938,:962).
+template <typename T>
+__global__ void k_rhs(Geom g, const T* __restrict__ P, const T* __restrict__ C, long long cur_pair, T* __restrict__ b) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    const int pair = blockIdx.z;
+    if (j >= g.Ny) return;
+    const T* p = P + (long long)pair * g.img_pair;
+    const T* c = C + (long long)pair * cur_pair;
+    T b0 = T(0), b1 = T(0), b2 = T(0);
+    if (i >= 1 && i <= g.Nx - 2 && j >= 1 && j <= g.Ny - 2) {
+        const long long o = (long long)i * g.pitch + j;
+        const T I = p[o];
+        const T Ixt = T(0.5) * (c[o + g.pitch] - c[o - g.pitch] - p[o + g.pitch] + p[o - g.pitch]);
+        const T Iyt = T(0.5) * (c[o + 1] - c[o - 1] - p[o + 1] + p[o - 1]);
+        b0 = -I * Ixt; b1 = -I * Iyt; b2 = -(c[o] - I);
+    }
+    T* out = b + (long long)pair * g.pair + (long long)i * g.pitch + j;
+    out[0] = b0; out[g.plane] = b1; out[2 * g.plane] = b2;
+}
+
+// per-pair sum of squares -> st[pair].acc[0]
+template <typename T>
+__global__ void __launch_bounds__(256) k_norm2(long long n_per_pair, long long pair_stride, const T* __restrict__ v,
+                                               PairState* __restrict__ st) {
+    const int pair = blockIdx.y;
+    double acc[1] = {0.0};
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n_per_pair; e += (long long)gridDim.x * blockDim.x) {
+        const double t = (double)v[(long long)pair * pair_stride + e];
+        acc[0] += t * t;
+    }
+    block_accumulate<1>(acc, st[pair].acc);
+}
+
+__global__ void k_state_init(PairState* __restrict__ st, int* __restrict__ active_arr, int B) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= B) return;
+    PairState s;
+    s.rho = s.rho_old = s.alpha = s.omega = 1.0; s.beta_k = 0.0;
+    s.acc[0] = s.acc[1] = s.acc[2] = s.acc[3] = 0.0;
+    s.bnorm = 0.0; s.relres = 0.0; s.active = 1; s.iters = 0; s.status = ST_RUNNING; s.pad = 0;
+    st[pair] = s;
+    active_arr[pair] = 1;
+}
+__global__ void k_state_bnorm(PairState* __restrict__ st, int B) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= B) return;
+    st[pair].bnorm = sqrt(st[pair].acc[0]);
+    st[pair].acc[0] = 0.0;
+}
+__global__ void k_state_export(const PairState* __restrict__ st, int B, int* __restrict__ iters, double* __restrict__ relres,
+                               int* __restrict__ converged) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= B) return;
+    if (iters) iters[pair] = st[pair].iters;
+    if (relres) relres[pair] = st[pair].relres;
+    if (converged) converged[pair] = (st[pair].status == ST_CONVERGED) ? 1 : 0;
+}
+
+// zero the ghost ring of a 3-plane vector (the eliminated system carries zeros there)
+template <typename T>
+__global__ void k_zero_ghosts(Geom g, T* __restrict__ x) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int pair = blockIdx.y;
+    const int ring = 2 * g.Ny + 2 * g.Nx;
+    if (t >= ring) return;
+    int i, j;
+    if (t < g.Ny) { i = 0; j = t; }
+    else if (t < 2 * g.Ny) { i = g.Nx - 1; j = t - g.Ny; }
+    else if (t < 2 * g.Ny + g.Nx) { i = t - 2 * g.Ny; j = 0; }
+    else { i = t - 2 * g.Ny - g.Nx; j = g.Ny - 1; }
+    T* p = x + (long long)pair * g.pair + (long long)i * g.pitch + j;
+    p[0] = T(0); p[g.plane] = T(0); p[2 * g.plane] = T(0);
+}
+
+// complete the ghost ring so that x solves the reference's full system, boundary rows included:
+// q(0,j)=q(2,j) ..., corner q(0,0) = q(2,0) + q(0,2) = 2 q(2,2)   (optical_flow.py:965-1070)
+template <typename T>
+__global__ void k_fill_ghosts(Geom g, T* __restrict__ x) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int pair = blockIdx.y;
+    const int ring = 2 * g.Ny + 2 * g.Nx;
+    if (t >= ring) return;
+    int i, j;
+    if (t < g.Ny) { i = 0; j = t; }
+    else if (t < 2 * g.Ny) { i = g.Nx - 1; j = t - g.Ny; }
+    else if (t < 2 * g.Ny + g.Nx) { i = t - 2 * g.Ny; j = 0; }
+    else { i = t - 2 * g.Ny - g.Nx; j = g.Ny - 1; }
+    const bool gr = (i == 0) || (i == g.Nx - 1), gc = (j == 0) || (j == g.Ny - 1);
+    const int mi = mirror_index(i, g.Nx), mj = mirror_index(j, g.Ny);
+    T* base = x + (long long)pair * g.pair;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        T v = base[q * g.plane + (long long)mi * g.pitch + mj];
+        if (gr && gc) v = v + v;
+        base[q * g.plane + (long long)i * g.pitch + j] = v;
+    }
+}
+
+// ------------------------------------------------------------------ full operator y = A x (reference matrix,
+// ghost-ring rows included; used by the C-ABI operator entry point and the parity tests)
+template <typename T>
+__global__ void k_apply_full(Geom g, const T* __restrict__ P, const T* __restrict__ x, T* __restrict__ y,
+                             const double* __restrict__ alpha, const double* __restrict__ beta) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    const int pair = blockIdx.z;
+    if (j >= g.Ny) return;
+    const T* xb = x + (long long)pair * g.pair;
+    const T* img = P + (long long)pair * g.img_pair;
+    T out[3];
+    const bool top = i == 0, bot = i == g.Nx - 1, lef = j == 0, rig = j == g.Ny - 1;
+    if (top || bot || lef || rig) {
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            const T* f = xb + q * g.plane;
+            T v = f[(long long)i * g.pitch + j];
+            if (top) v -= f[(long long)2 * g.pitch + j];
+            if (bot) v -= f[(long long)(g.Nx - 3) * g.pitch + j];
+            if (lef) v -= f[(long long)i * g.pitch + 2];
+            if (rig) v -= f[(long long)i * g.pitch + g.Ny - 3];
+            out[q] = v;
+        }
+    } else {
+        Row<T> pm, pc, pp;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            pm.v[c] = img[(long long)(i - 1) * g.pitch + j - 1 + c];
+            pc.v[c] = img[(long long)i * g.pitch + j - 1 + c];
+            pp.v[c] = img[(long long)(i + 1) * g.pitch + j - 1 + c];
+        }
+        const Coef<T> c = coef_from_image<T>(pm, pc, pp, 1);
+        auto acc = [&](int q, int ii, int jj) -> T { return xb[q * g.plane + (long long)ii * g.pitch + jj]; };
+        apply_at<T>(c, acc, i, j, T(alpha[pair]), T(beta[pair]), out);
+    }
+    T* o = y + (long long)pair * g.pair + (long long)i * g.pitch + j;
+    o[0] = out[0]; o[g.plane] = out[1]; o[2 * g.plane] = out[2];
+}
+
+// ------------------------------------------------------------------ K6 epilogue
+// apply_constant_boundary_condition (:1304-1316, even reflection, corners = f[2,2]-type value), the three
+// functionals in pixel units with d/dy == d/dx (:1167-1183), scaling by delta_x/delta_t and speed (:1189-1191).
+template <typename T>
+__global__ void __launch_bounds__(128) k_epilogue(Geom g, const T* __restrict__ P, const T* __restrict__ C, long long cur_pair,
+                                                  const T* __restrict__ x, T* __restrict__ vx, T* __restrict__ vy,
+                                                  T* __restrict__ speed, T* __restrict__ gamma, double* __restrict__ functionals,
+                                                  double* __restrict__ moments,
+                                                  const double* __restrict__ alpha, const double* __restrict__ beta, double scale) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    const int pair = blockIdx.z;
+    double acc[3] = {0.0, 0.0, 0.0};
+    double mom[4] = {0.0, 0.0, 0.0, 0.0};
+    if (j < g.Ny) {
+        const T* xb = x + (long long)pair * g.pair;
+        const int mi = mirror_index(i, g.Nx), mj = mirror_index(j, g.Ny);
+        const long long o = (long long)mi * g.pitch + mj;
+        const T ux = xb[o], uy = xb[g.plane + o], gm = xb[2 * g.plane + o];
+        const long long oo = (long long)pair * g.img_pair + (long long)i * g.pitch + j;
+        vx[oo] = ux * T(scale); vy[oo] = uy * T(scale); gamma[oo] = gm;
+        const T sp = T(sqrt((double)(ux * T(scale)) * (double)(ux * T(scale)) + (double)(uy * T(scale)) * (double)(uy * T(scale))));
+        speed[oo] = sp;
+        mom[0] = (double)sp; mom[1] = (double)sp * (double)sp; mom[2] = (double)gm; mom[3] = (double)gm * (double)gm;
+        if (i >= 1 && i <= g.Nx - 2 && j >= 1 && j <= g.Ny - 2) {
+            const int ip = mirror_index(i + 1, g.Nx), im = mirror_index(i - 1, g.Nx);
+            const long long op = (long long)ip * g.pitch + mj, om = (long long)im * g.pitch + mj;
+            const double dux = 0.5 * ((double)xb[op] - (double)xb[om]);
+            const double duy = 0.5 * ((double)xb[g.plane + op] - (double)xb[g.plane + om]);
+            const double dg = 0.5 * ((double)xb[2 * g.plane + op] - (double)xb[2 * g.plane + om]);
+            const T* p = P + (long long)pair * g.img_pair;
+            const T* c = C + (long long)pair * cur_pair;
+            const long long q = (long long)i * g.pitch + j;
+            const double I = (double)p[q];
+            const double Ix = 0.5 * ((double)p[q + g.pitch] - (double)p[q - g.pitch]);
+            const double It = (double)c[q] - I;
+            const double e = It + (double)ux * Ix + (double)uy * Ix + I * dux + I * duy - (double)gm;
+            acc[0] = e * e;
+            acc[1] = alpha[pair] * 2.0 * (dux * dux + duy * duy);
+            acc[2] = beta[pair] * 2.0 * dg * dg;
+        }
+    }
+    block_accumulate<3>(acc, functionals + 3 * pair);
+    if (moments != nullptr) {
+        __syncthreads();
+        block_accumulate<4>(mom, moments + 4 * pair);
+    }
+}
+
+}  // namespace ofb

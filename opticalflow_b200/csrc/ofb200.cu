@@ -1,0 +1,547 @@
+// ofb200 - host side of the C ABI (include/ofb200.h): workspace planning, multigrid hierarchy set-up,
+// the BiCGStab driver loop and the launch wrappers.  Compiled for sm_100a only.
+#include <cstdio>
+#include <cstring>
+#include <cstdarg>
+#include <vector>
+#include <algorithm>
+#include "../../include/ofb200.h"
+#include "misc_kernels.cuh"
+
+using namespace ofb;
+
+namespace {
+
+thread_local char g_error[512] = "";
+
+int fail(int code, const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+#define OFB_CHECK_CUDA(expr)                                                                        \
+    do {                                                                                            \
+        cudaError_t e__ = (expr);                                                                   \
+        if (e__ != cudaSuccess) return fail(-1000 - (int)e__, "%s: %s", #expr, cudaGetErrorString(e__)); \
+    } while (0)
+
+#define OFB_CHECK_LAUNCH() OFB_CHECK_CUDA(cudaGetLastError())
+
+constexpr int MAX_LEVELS = 16;
+constexpr int MIN_COARSE = 6;          // keep coarsening while both coarse sizes stay >= this
+constexpr int MAX_DENSE_N = 768;       // largest coarsest system solved with the dense inverse
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+struct LevelPlan {
+    int Nx, Ny, pitch;
+    long long plane;                    // elements per plane
+};
+
+struct Plan {
+    int nlevels;                        // 1 = no coarse levels
+    LevelPlan lv[MAX_LEVELS];
+    bool dense;                         // coarsest level solved with the dense inverse
+    int dense_n;
+};
+
+Plan make_plan(int Nx, int Ny, int precond) {
+    Plan p;
+    p.nlevels = 1;
+    p.lv[0] = {Nx, Ny, Ny, (long long)Nx * Ny};
+    p.dense = false;
+    p.dense_n = 0;
+    if (precond != OFB_PRECOND_MG) return p;
+    while (p.nlevels < MAX_LEVELS) {
+        const LevelPlan& f = p.lv[p.nlevels - 1];
+        const int cx = coarse_size(f.Nx), cy = coarse_size(f.Ny);
+        if (cx < MIN_COARSE || cy < MIN_COARSE || cx >= f.Nx || cy >= f.Ny) break;
+        LevelPlan c;
+        c.Nx = cx; c.Ny = cy; c.pitch = (cy + 3) / 4 * 4; c.plane = (long long)cx * c.pitch;
+        p.lv[p.nlevels++] = c;
+    }
+    if (p.nlevels > 1) {
+        LevelPlan& c = p.lv[p.nlevels - 1];
+        const int n = 3 * c.Nx * c.Ny;
+        if (n <= MAX_DENSE_N) {
+            p.dense = true; p.dense_n = n;
+            c.pitch = c.Ny; c.plane = (long long)c.Nx * c.Ny;      // unpadded: flat index == unknown number
+        }
+    }
+    return p;
+}
+
+// Workspace carving (all offsets 256-byte aligned).
+template <typename T> struct Workspace {
+    PairState* st; int* active; int* n_active;
+    T *r, *rhat, *p, *v, *s, *t, *ph, *sh, *zalt;              // level-0 vectors
+    T* coef[MAX_LEVELS];                                      // level >= 1: 7 coefficient planes per pair
+    T *lb[MAX_LEVELS], *xa[MAX_LEVELS], *xb[MAX_LEVELS], *res[MAX_LEVELS];
+    double* dense_M; T* dense_Minv; int* dense_piv;
+    size_t bytes;
+};
+
+template <typename T>
+Workspace<T> carve(void* base, int B, const Plan& plan) {
+    Workspace<T> w;
+    memset(&w, 0, sizeof(w));
+    size_t off = 0;
+    auto take = [&](size_t nbytes) { void* p = base ? (char*)base + off : nullptr; off = align_up(off + nbytes, 256); return p; };
+    w.st = (PairState*)take(sizeof(PairState) * B);
+    w.active = (int*)take(sizeof(int) * B);
+    w.n_active = (int*)take(sizeof(int) * 4);
+    const size_t vec0 = (size_t)3 * plan.lv[0].plane * B * sizeof(T);
+    T** v0[] = {&w.r, &w.rhat, &w.p, &w.v, &w.s, &w.t, &w.ph, &w.sh, &w.zalt};
+    for (T** q : v0) *q = (T*)take(vec0);
+    for (int l = 1; l < plan.nlevels; ++l) {
+        const size_t planeb = (size_t)plan.lv[l].plane * B * sizeof(T);
+        w.coef[l] = (T*)take(NCOEF * planeb);
+        w.lb[l] = (T*)take(3 * planeb);
+        w.xa[l] = (T*)take(3 * planeb);
+        w.xb[l] = (T*)take(3 * planeb);
+        w.res[l] = (T*)take(3 * planeb);
+    }
+    if (plan.dense) {
+        const size_t nn = (size_t)plan.dense_n * plan.dense_n;
+        w.dense_M = (double*)take(nn * B * sizeof(double));
+        w.dense_Minv = (T*)take(nn * B * sizeof(T));
+        w.dense_piv = (int*)take((size_t)plan.dense_n * B * sizeof(int));
+    }
+    w.bytes = off;
+    return w;
+}
+
+template <typename T> Geom make_geom(const LevelPlan& lp, bool aligned_ok) {
+    Geom g;
+    g.Nx = lp.Nx; g.Ny = lp.Ny; g.pitch = lp.pitch; g.plane = lp.plane;
+    g.pair = 3 * lp.plane; g.img_pair = lp.plane;
+    g.aligned = (aligned_ok && lp.pitch % VecOf<T>::V == 0) ? 1 : 0;
+    return g;
+}
+
+inline bool ptr_aligned16(const void* p) { return ((uintptr_t)p & 15) == 0; }
+
+int check_shape(int B, int Nx, int Ny, int dtype) {
+    if (B < 1) return fail(-1, "batch size must be >= 1 (got %d)", B);
+    if (Nx < 5 || Ny < 5) return fail(-2, "frames must be at least 5x5 (got %dx%d)", Nx, Ny);
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    return 0;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// Solver driver
+// =====================================================================================================
+namespace {
+
+template <typename T> struct Solver {
+    int B;
+    Plan plan;
+    Workspace<T> w;
+    Geom g[MAX_LEVELS];
+    const T* P;                      // previous frames (level-0 coefficient source)
+    const double *alpha, *beta;
+    ofb_solve_options opt;
+    cudaStream_t stream;
+    const int* active;               // nullptr while setting up / for single applications
+
+    LevelArgs<T> level_args(int l) const {
+        LevelArgs<T> L;
+        L.g = g[l];
+        if (l == 0) { L.coef = P; L.coef_pair = g[0].img_pair; }
+        else { L.coef = w.coef[l]; L.coef_pair = (long long)NCOEF * g[l].plane; }
+        L.alpha = alpha; L.beta = beta; L.active = active;
+        L.h2 = 1.0 / ((double)(1 << l) * (double)(1 << l));
+        constexpr int V = VecOf<T>::V;
+        L.tiles_x = (g[l].Ny + WARP * V - 1) / (WARP * V);
+        int R = opt.rows_per_strip;
+        if (R <= 0) {
+            const long long target_warps = 148LL * 16;
+            const long long total_rows = (long long)g[l].Nx * L.tiles_x * B;
+            R = (int)std::min<long long>(32, std::max<long long>(8, (total_rows + target_warps - 1) / target_warps));
+        }
+        L.rows_per_strip = R;
+        L.strips = (g[l].Nx + R - 1) / R;
+        return L;
+    }
+
+    template <typename Op> int sweep(int l, const T* x, Op op) {
+        const LevelArgs<T> L = level_args(l);
+        const int warps_per_block = 4;
+        const int items = L.tiles_x * L.strips;
+        dim3 grid((items + warps_per_block - 1) / warps_per_block, B);
+        if (l == 0) k_sweep<T, true, Op><<<grid, warps_per_block * 32, 0, stream>>>(L, x, op);
+        else        k_sweep<T, false, Op><<<grid, warps_per_block * 32, 0, stream>>>(L, x, op);
+        OFB_CHECK_LAUNCH();
+        return 0;
+    }
+
+    int smooth(int l, const T* b, const T* xin, T* xout) {
+        OpSmooth<T> op; op.g = g[l]; op.b = b; op.xo = xout; op.w = T(opt.omega);
+        return sweep(l, xin, op);
+    }
+    int residual(int l, const T* b, const T* x, T* r) {
+        OpResidual<T, false> op; op.g = g[l]; op.b = b; op.r = r; op.r2 = nullptr; op.st = w.st; op.acc[0] = 0.0;
+        return sweep(l, x, op);
+    }
+    int jacobi_zero(int l, const T* b, T* z, double wj) {
+        OpDirJacobi<T, 2> op; op.g = g[l]; op.r = nullptr; op.d = const_cast<T*>(b); op.v = nullptr; op.z = z; op.w = T(wj); op.st = w.st;
+        return sweep(l, nullptr, op);
+    }
+
+    int build_hierarchy() {
+        for (int l = 1; l < plan.nlevels; ++l) {
+            dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
+            if (l == 1) k_coef_from_image<T><<<grid, block, 0, stream>>>(g[0], P, g[1], w.coef[1]);
+            else k_restrict<T, true><<<grid, block, 0, stream>>>(g[l - 1], w.coef[l - 1], (long long)NCOEF * g[l - 1].plane, g[l],
+                                                                 w.coef[l], (long long)NCOEF * g[l].plane, NCOEF, nullptr);
+            OFB_CHECK_LAUNCH();
+        }
+        if (plan.dense) {
+            const int l = plan.nlevels - 1;
+            const double h2 = 1.0 / ((double)(1 << l) * (double)(1 << l));
+            k_coarse_setup<T><<<B, 1024, 0, stream>>>(g[l], w.coef[l], alpha, beta, h2, w.dense_M, w.dense_Minv, w.dense_piv);
+            OFB_CHECK_LAUNCH();
+        }
+        return 0;
+    }
+
+    // number of buffer swaps a V-cycle on level l performs after the first (zero-guess) sweep
+    int swaps() const { return (opt.nu_pre - 1) + opt.nu_post; }
+
+    // V-cycle on level l.  `b` = right-hand side, `cur` holds the result of the first sweep w D^-1 b,
+    // `alt` is the ping-pong partner.  Returns the buffer holding the result in *out.
+    int vcycle(int l, const T* b, T* cur, T* alt, T** out) {
+        int rc;
+        for (int s = 1; s < opt.nu_pre; ++s) { if ((rc = smooth(l, b, cur, alt))) return rc; std::swap(cur, alt); }
+        const int lc = l + 1;
+        T* res = (l == 0) ? w.t : w.res[l];
+        if ((rc = residual(l, b, cur, res))) return rc;
+        {
+            dim3 block(128), grid((g[lc].Ny + 127) / 128, g[lc].Nx, B);
+            k_restrict<T, false><<<grid, block, 0, stream>>>(g[l], res, g[l].pair, g[lc], w.lb[lc], g[lc].pair, 3, active);
+            OFB_CHECK_LAUNCH();
+        }
+        T* ec = nullptr;
+        if (lc == plan.nlevels - 1) {
+            if (plan.dense) {
+                const int n = plan.dense_n;
+                k_coarse_solve<T><<<B, 128, n * sizeof(T), stream>>>(n, w.dense_Minv, w.lb[lc], w.xa[lc], g[lc].pair, active);
+                OFB_CHECK_LAUNCH();
+                ec = w.xa[lc];
+            } else {
+                if ((rc = jacobi_zero(lc, w.lb[lc], w.xa[lc], opt.omega))) return rc;
+                T *c = w.xa[lc], *a = w.xb[lc];
+                for (int s = 1; s < opt.coarse_sweeps; ++s) { if ((rc = smooth(lc, w.lb[lc], c, a))) return rc; std::swap(c, a); }
+                ec = c;
+            }
+        } else {
+            if ((rc = jacobi_zero(lc, w.lb[lc], w.xa[lc], opt.omega))) return rc;
+            if ((rc = vcycle(lc, w.lb[lc], w.xa[lc], w.xb[lc], &ec))) return rc;
+        }
+        {
+            dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
+            k_prolong_add<T><<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
+            OFB_CHECK_LAUNCH();
+        }
+        for (int s = 0; s < opt.nu_post; ++s) { if ((rc = smooth(l, b, cur, alt))) return rc; std::swap(cur, alt); }
+        *out = cur;
+        return 0;
+    }
+
+    // z = M^-1 d where the first sweep (fused with the direction update) already produced `first`.
+    // For block-Jacobi the first sweep (w = 1) is the whole preconditioner.
+    int finish_precondition(const T* d, T* first, T* partner, T** out) {
+        if (opt.precond != OFB_PRECOND_MG || plan.nlevels == 1) { *out = first; return 0; }
+        return vcycle(0, d, first, partner, out);
+    }
+    double first_sweep_weight() const { return (opt.precond == OFB_PRECOND_MG && plan.nlevels > 1) ? opt.omega : 1.0; }
+    // buffer the first sweep must write to so that the V-cycle result lands in `target`
+    T* first_buffer(T* target) const {
+        if (opt.precond != OFB_PRECOND_MG || plan.nlevels == 1) return target;
+        return (swaps() % 2 == 0) ? target : w.zalt;
+    }
+    T* partner_of(T* first, T* target) const { return first == target ? w.zalt : target; }
+};
+
+template <typename T>
+int init_solver(Solver<T>& S, const void* P, const double* alpha, const double* beta, const ofb_solve_options* opt,
+                void* workspace, size_t workspace_bytes, int B, int Nx, int Ny, void* stream, const void* a1, const void* a2) {
+    if (opt) S.opt = *opt; else ofb_default_options(&S.opt);
+    if (S.opt.nu_pre < 1) S.opt.nu_pre = 1;
+    if (S.opt.nu_post < 0) S.opt.nu_post = 0;
+    if (S.opt.coarse_sweeps < 1) S.opt.coarse_sweeps = 1;
+    if (S.opt.check_every < 1) S.opt.check_every = 1;
+    S.B = B;
+    S.plan = make_plan(Nx, Ny, S.opt.precond);
+    S.w = carve<T>(workspace, B, S.plan);
+    if (workspace == nullptr || workspace_bytes < S.w.bytes)
+        return fail(-4, "workspace too small: need %zu bytes, got %zu", S.w.bytes, workspace_bytes);
+    const bool al = ptr_aligned16(P) && ptr_aligned16(a1) && ptr_aligned16(a2) && ptr_aligned16(workspace);
+    for (int l = 0; l < S.plan.nlevels; ++l) S.g[l] = make_geom<T>(S.plan.lv[l], al);
+    S.P = (const T*)P; S.alpha = alpha; S.beta = beta; S.stream = (cudaStream_t)stream; S.active = nullptr;
+    return 0;
+}
+
+template <typename T>
+int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
+               const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
+               int* converged_out, int B, int Nx, int Ny, void* stream_) {
+    Solver<T> S;
+    int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, b3, x3);
+    if (rc) return rc;
+    cudaStream_t stream = S.stream;
+    Workspace<T>& w = S.w;
+    const Geom g0 = S.g[0];
+    const T* b = (const T*)b3;
+    T* x = (T*)x3;
+    const long long nvec = g0.pair;                        // elements per pair of a level-0 vector
+    const int tb = 256;
+    const dim3 blas_grid((unsigned)std::min<long long>((nvec + tb * 4 - 1) / (tb * 4), 148 * 8), B);
+    const int sb = (B + 127) / 128;
+
+    k_state_init<<<sb, 128, 0, stream>>>(w.st, w.active, B);
+    OFB_CHECK_LAUNCH();
+    k_norm2<T><<<blas_grid, tb, 0, stream>>>(nvec, nvec, b, w.st);
+    OFB_CHECK_LAUNCH();
+    k_state_bnorm<<<sb, 128, 0, stream>>>(w.st, B);
+    OFB_CHECK_LAUNCH();
+    // p and v enter the first direction update multiplied by beta_k = 0; they must be finite
+    OFB_CHECK_CUDA(cudaMemsetAsync(w.p, 0, sizeof(T) * nvec * B, stream));
+    OFB_CHECK_CUDA(cudaMemsetAsync(w.v, 0, sizeof(T) * nvec * B, stream));
+    if (S.opt.precond == OFB_PRECOND_MG && S.plan.nlevels > 1) { if ((rc = S.build_hierarchy())) return rc; }
+
+    {   // r = b - S x0, rhat = r, acc[2] = acc[3] = r.r
+        OpResidual<T, true> op; op.g = g0; op.b = b; op.r = w.r; op.r2 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
+        if ((rc = S.sweep(0, x, op))) return rc;
+    }
+    k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 0, rtol, max_it, nullptr);
+    OFB_CHECK_LAUNCH();
+    S.active = w.active;
+
+    T* ph_first = S.first_buffer(w.ph);
+    T* sh_first = S.first_buffer(w.sh);
+    const T wj = T(S.first_sweep_weight());
+    int host_active = B;
+    for (int it = 0; it < max_it; ++it) {
+        T *ph = nullptr, *sh = nullptr;
+        {   // p = r + beta_k (p - omega v) ; z = w D^-1 p
+            OpDirJacobi<T, 0> op; op.g = g0; op.r = w.r; op.d = w.p; op.v = w.v; op.z = ph_first; op.w = wj; op.st = w.st;
+            if ((rc = S.sweep(0, nullptr, op))) return rc;
+        }
+        if ((rc = S.finish_precondition(w.p, ph_first, S.partner_of(ph_first, w.ph), &ph))) return rc;
+        {   // v = S ph ; acc[0] = rhat.v
+            OpApplyDot<T, 1> op; op.g = g0; op.y = w.v; op.w1 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
+            if ((rc = S.sweep(0, ph, op))) return rc;
+        }
+        k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 1, rtol, max_it, nullptr);
+        OFB_CHECK_LAUNCH();
+        {   // s = r - alpha v ; z = w D^-1 s
+            OpDirJacobi<T, 1> op; op.g = g0; op.r = w.r; op.d = w.s; op.v = w.v; op.z = sh_first; op.w = wj; op.st = w.st;
+            if ((rc = S.sweep(0, nullptr, op))) return rc;
+        }
+        if ((rc = S.finish_precondition(w.s, sh_first, S.partner_of(sh_first, w.sh), &sh))) return rc;
+        {   // t = S sh ; acc[0] = t.s, acc[1] = t.t
+            OpApplyDot<T, 2> op; op.g = g0; op.y = w.t; op.w1 = w.s; op.st = w.st; op.acc[0] = op.acc[1] = 0.0;
+            if ((rc = S.sweep(0, sh, op))) return rc;
+        }
+        k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 2, rtol, max_it, nullptr);
+        OFB_CHECK_LAUNCH();
+        k_update_x_r<T><<<blas_grid, tb, 0, stream>>>(nvec, nvec, x, ph, sh, w.r, w.s, w.t, w.rhat, w.st);
+        OFB_CHECK_LAUNCH();
+        const bool poll = ((it + 1) % S.opt.check_every == 0) || (it + 1 == max_it);
+        if (poll) OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active, 0, sizeof(int), stream));
+        k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : nullptr);
+        OFB_CHECK_LAUNCH();
+        if (poll) {
+            OFB_CHECK_CUDA(cudaMemcpyAsync(&host_active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+            OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+            if (host_active == 0) break;
+        }
+    }
+    {
+        const int ring = 2 * Nx + 2 * Ny;
+        k_fill_ghosts<T><<<dim3((ring + 127) / 128, B), 128, 0, stream>>>(g0, x);
+        OFB_CHECK_LAUNCH();
+    }
+    k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T>
+int precondition_impl(const void* P, const void* r3, void* z3, const double* alpha, const double* beta, const ofb_solve_options* opt,
+                      void* workspace, size_t workspace_bytes, int B, int Nx, int Ny, void* stream_) {
+    Solver<T> S;
+    int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, r3, z3);
+    if (rc) return rc;
+    const bool mg = (S.opt.precond == OFB_PRECOND_MG && S.plan.nlevels > 1);
+    if (mg && (rc = S.build_hierarchy())) return rc;
+    T* z = (T*)z3;
+    T* first = S.first_buffer(z);
+    if ((rc = S.jacobi_zero(0, (const T*)r3, first, S.first_sweep_weight()))) return rc;
+    T* out = nullptr;
+    if (!mg) return 0;
+    if ((rc = S.vcycle(0, (const T*)r3, first, first == z ? S.w.zalt : z, &out))) return rc;
+    if (out != z) return fail(-5, "internal: V-cycle result landed in the wrong buffer");
+    return 0;
+}
+
+}  // namespace
+
+// =====================================================================================================
+// C ABI
+// =====================================================================================================
+namespace {
+
+template <typename T>
+int blur_impl(const void* in, void* out, void* tmp, const double* weights, int radius, int F, int Nx, int Ny, cudaStream_t stream) {
+    dim3 block(128), grid((Ny + 127) / 128, Nx, F);
+    const long long fs = (long long)Nx * Ny;
+    k_blur_axis<T, 0><<<grid, block, 0, stream>>>((const T*)in, (T*)tmp, Nx, Ny, fs, weights, radius);
+    OFB_CHECK_LAUNCH();
+    k_blur_axis<T, 1><<<grid, block, 0, stream>>>((const T*)tmp, (T*)out, Nx, Ny, fs, weights, radius);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T>
+int rhs_impl(const void* P, const void* C, void* b3, int B, int Nx, int Ny, cudaStream_t stream) {
+    LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny};
+    const Geom g = make_geom<T>(lp, false);
+    dim3 block(128), grid((Ny + 127) / 128, Nx, B);
+    k_rhs<T><<<grid, block, 0, stream>>>(g, (const T*)P, (const T*)C, g.img_pair, (T*)b3);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T>
+int apply_full_impl(const void* P, const void* x3, void* y3, const double* alpha, const double* beta, int B, int Nx, int Ny,
+                    cudaStream_t stream) {
+    LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny};
+    const Geom g = make_geom<T>(lp, false);
+    dim3 block(128), grid((Ny + 127) / 128, Nx, B);
+    k_apply_full<T><<<grid, block, 0, stream>>>(g, (const T*)P, (const T*)x3, (T*)y3, alpha, beta);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T>
+int apply_elim_impl(const void* P, const void* x3, void* y3, const double* alpha, const double* beta, int B, int Nx, int Ny,
+                    void* stream) {
+    Solver<T> S;
+    ofb_default_options(&S.opt);
+    S.opt.precond = OFB_PRECOND_BJACOBI;
+    S.B = B;
+    S.plan = make_plan(Nx, Ny, OFB_PRECOND_BJACOBI);
+    memset(&S.w, 0, sizeof(S.w));
+    S.g[0] = make_geom<T>(S.plan.lv[0], ptr_aligned16(P) && ptr_aligned16(x3) && ptr_aligned16(y3));
+    S.P = (const T*)P; S.alpha = alpha; S.beta = beta; S.stream = (cudaStream_t)stream; S.active = nullptr;
+    OpApply<T> op; op.g = S.g[0]; op.y = (T*)y3;
+    return S.sweep(0, (const T*)x3, op);
+}
+
+template <typename T>
+int epilogue_impl(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma, double* functionals,
+                  double* moments, const double* alpha, const double* beta, double scale, int B, int Nx, int Ny, cudaStream_t stream) {
+    LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny};
+    const Geom g = make_geom<T>(lp, false);
+    OFB_CHECK_CUDA(cudaMemsetAsync(functionals, 0, sizeof(double) * 3 * B, stream));
+    if (moments) OFB_CHECK_CUDA(cudaMemsetAsync(moments, 0, sizeof(double) * 4 * B, stream));
+    dim3 block(128), grid((Ny + 127) / 128, Nx, B);
+    k_epilogue<T><<<grid, block, 0, stream>>>(g, (const T*)P, (const T*)C, g.img_pair, (const T*)x3, (T*)vx, (T*)vy, (T*)speed,
+                                              (T*)gamma, functionals, moments, alpha, beta, scale);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ofb_version(void) { return OFB_ABI_VERSION; }
+
+const char* ofb_last_error(void) { return g_error; }
+
+void ofb_default_options(ofb_solve_options* opt) {
+    if (!opt) return;
+    opt->precond = OFB_PRECOND_MG;
+    opt->nu_pre = 2;
+    opt->nu_post = 2;
+    opt->omega = 0.8;
+    opt->check_every = 1;
+    opt->rows_per_strip = 0;
+    opt->coarse_sweeps = 30;
+    opt->reserved = 0;
+}
+
+size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond) {
+    if (check_shape(B, Nx, Ny, dtype)) return 0;
+    const Plan plan = make_plan(Nx, Ny, precond);
+    return dtype == OFB_F32 ? carve<float>(nullptr, B, plan).bytes : carve<double>(nullptr, B, plan).bytes;
+}
+
+int ofb_blur(const void* in, void* out, void* tmp, const double* weights, int radius, int F, int Nx, int Ny, int dtype, void* stream) {
+    if (F < 1 || Nx < 1 || Ny < 1) return fail(-1, "ofb_blur: bad shape %d x %d x %d", F, Nx, Ny);
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    if (radius < 0 || !weights) return fail(-6, "ofb_blur: weights/radius invalid");
+    if (in == out || in == tmp || out == tmp) return fail(-7, "ofb_blur: in/out/tmp must not alias");
+    return dtype == OFB_F32 ? blur_impl<float>(in, out, tmp, weights, radius, F, Nx, Ny, (cudaStream_t)stream)
+                            : blur_impl<double>(in, out, tmp, weights, radius, F, Nx, Ny, (cudaStream_t)stream);
+}
+
+int ofb_build_rhs(const void* P, const void* C, void* b3, int B, int Nx, int Ny, int dtype, void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    return dtype == OFB_F32 ? rhs_impl<float>(P, C, b3, B, Nx, Ny, (cudaStream_t)stream)
+                            : rhs_impl<double>(P, C, b3, B, Nx, Ny, (cudaStream_t)stream);
+}
+
+int ofb_apply(const void* P, const void* x3, void* y3, const double* alpha, const double* beta, int B, int Nx, int Ny, int dtype,
+              void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    if (x3 == y3) return fail(-7, "ofb_apply: x and y must not alias");
+    return dtype == OFB_F32 ? apply_full_impl<float>(P, x3, y3, alpha, beta, B, Nx, Ny, (cudaStream_t)stream)
+                            : apply_full_impl<double>(P, x3, y3, alpha, beta, B, Nx, Ny, (cudaStream_t)stream);
+}
+
+int ofb_apply_eliminated(const void* P, const void* x3, void* y3, const double* alpha, const double* beta, int B, int Nx, int Ny,
+                         int dtype, void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    if (x3 == y3) return fail(-7, "ofb_apply_eliminated: x and y must not alias");
+    return dtype == OFB_F32 ? apply_elim_impl<float>(P, x3, y3, alpha, beta, B, Nx, Ny, stream)
+                            : apply_elim_impl<double>(P, x3, y3, alpha, beta, B, Nx, Ny, stream);
+}
+
+int ofb_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
+              const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
+              int* converged_out, int B, int Nx, int Ny, int dtype, void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    if (max_it < 0) return fail(-8, "max_it must be >= 0");
+    return dtype == OFB_F32
+               ? solve_impl<float>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
+                                   converged_out, B, Nx, Ny, stream)
+               : solve_impl<double>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
+                                    converged_out, B, Nx, Ny, stream);
+}
+
+int ofb_precondition(const void* P, const void* r3, void* z3, const double* alpha, const double* beta, const ofb_solve_options* opt,
+                     void* workspace, size_t workspace_bytes, int B, int Nx, int Ny, int dtype, void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    return dtype == OFB_F32 ? precondition_impl<float>(P, r3, z3, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream)
+                            : precondition_impl<double>(P, r3, z3, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream);
+}
+
+int ofb_epilogue(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma, double* functionals,
+                 double* moments, const double* alpha, const double* beta, double scale, int B, int Nx, int Ny, int dtype, void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    return dtype == OFB_F32 ? epilogue_impl<float>(P, C, x3, vx, vy, speed, gamma, functionals, moments, alpha, beta, scale, B, Nx, Ny,
+                                                   (cudaStream_t)stream)
+                            : epilogue_impl<double>(P, C, x3, vx, vy, speed, gamma, functionals, moments, alpha, beta, scale, B, Nx, Ny,
+                                                    (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,228 @@
+// ofb200 - Krylov / smoother kernels built on the row-marching sweep.
+//
+// BiCGStab (the reference's -ksp_type bcgs, optical_flow.py:1081) in right-preconditioned form with all
+// scalars resident on the device.  Dot products are accumulated in fp64 inside the stencil sweeps
+// (warp shuffle -> block -> one atomicAdd per block), never in separate reduction kernels.
+#pragma once
+#include "sweep.cuh"
+
+namespace ofb {
+
+// Per-pair solver scalars (device resident).
+struct PairState {
+    double rho, rho_old, alpha, omega, beta_k;
+    double acc[4];          // [0] rhat.v | t.s   [1] t.t   [2] r.r   [3] rhat.r
+    double bnorm, relres;
+    int active, iters, status, pad;
+};
+enum Status { ST_RUNNING = 0, ST_CONVERGED = 1, ST_MAXIT = 2, ST_BREAKDOWN = 3 };
+
+// ------------------------------------------------------------------ sweep ops
+// x_out = x + w D^-1 (b - S x)
+template <typename T> struct OpSmooth {
+    static constexpr bool NEED_X = true;
+    static constexpr int V = VecOf<T>::V;
+    Geom g; const T* b; T* xo; T w;
+    __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+        T bb[3][V], out[3][V];
+        load3<T>(b, g, pair, i, j0, bb);
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            T z0, z1, z2;
+            block_solve<T>(cf[k], a, be, bb[0][k] - sx[0][k], bb[1][k] - sx[1][k], bb[2][k] - sx[2][k], z0, z1, z2);
+            out[0][k] = inside[k] ? xc[0][k] + w * z0 : T(0);
+            out[1][k] = inside[k] ? xc[1][k] + w * z1 : T(0);
+            out[2][k] = inside[k] ? xc[2][k] + w * z2 : T(0);
+        }
+        store3<T>(xo, g, pair, i, j0, out);
+    }
+    __device__ __forceinline__ void finish(int, bool) {}
+};
+
+// r = b - S x ; optional copy to r2 and dots acc[2] += r.r, acc[3] += r.r (initial residual: rhat = r)
+template <typename T, bool INIT> struct OpResidual {
+    static constexpr bool NEED_X = true;
+    static constexpr int V = VecOf<T>::V;
+    Geom g; const T* b; T* r; T* r2; PairState* st; double acc[1];
+    __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+        T bb[3][V], out[3][V];
+        load3<T>(b, g, pair, i, j0, bb);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                out[q][k] = inside[k] ? bb[q][k] - sx[q][k] : T(0);
+                if (INIT) acc[0] += (double)out[q][k] * (double)out[q][k];
+            }
+        store3<T>(r, g, pair, i, j0, out);
+        if (INIT) store3<T>(r2, g, pair, i, j0, out);
+    }
+    __device__ __forceinline__ void finish(int pair, bool) {
+        if (INIT) {
+            double a2[2] = {acc[0], acc[0]};
+            block_accumulate<2>(a2, st[pair].acc + 2);
+        }
+    }
+};
+
+// y = S x with fused dots.  NDOT == 1: acc[0] += w1.y ;  NDOT == 2: acc[0] += y.w1, acc[1] += y.y
+template <typename T, int NDOT> struct OpApplyDot {
+    static constexpr bool NEED_X = true;
+    static constexpr int V = VecOf<T>::V;
+    Geom g; T* y; const T* w1; PairState* st; double acc[NDOT];
+    __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+        T ww[3][V], out[3][V];
+        load3<T>(w1, g, pair, i, j0, ww);
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+#pragma unroll
+            for (int k = 0; k < V; ++k) {
+                out[q][k] = inside[k] ? sx[q][k] : T(0);
+                acc[0] += (double)out[q][k] * (double)ww[q][k];
+                if (NDOT == 2) acc[1] += (double)out[q][k] * (double)out[q][k];
+            }
+        store3<T>(y, g, pair, i, j0, out);
+    }
+    __device__ __forceinline__ void finish(int pair, bool) { block_accumulate<NDOT>(acc, st[pair].acc); }
+};
+
+// y = S x, nothing else (C-ABI operator apply in eliminated form, MG residual checks)
+template <typename T> struct OpApply {
+    static constexpr bool NEED_X = true;
+    static constexpr int V = VecOf<T>::V;
+    Geom g; T* y;
+    __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+        T out[3][V];
+#pragma unroll
+        for (int q = 0; q < 3; ++q)
+#pragma unroll
+            for (int k = 0; k < V; ++k) out[q][k] = inside[k] ? sx[q][k] : T(0);
+        store3<T>(y, g, pair, i, j0, out);
+    }
+    __device__ __forceinline__ void finish(int, bool) {}
+};
+
+// Pointwise ops (no solution window): direction update fused with the first Jacobi sweep of the
+// preconditioner (zero initial guess: z = w D^-1 d).
+//   KIND 0:  d = p <- r + beta_k (p - omega v)          (BiCGStab direction)
+//   KIND 1:  d = s <- r - alpha v                        (BiCGStab half step)
+//   KIND 2:  d = b (read only)                           (first sweep on a coarse level)
+template <typename T, int KIND> struct OpDirJacobi {
+    static constexpr bool NEED_X = false;
+    static constexpr int V = VecOf<T>::V;
+    Geom g; const T* r; T* d; const T* v; T* z; T w; const PairState* st;
+    __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+        T dd[3][V], zz[3][V];
+        if (KIND == 2) {
+            load3<T>(d, g, pair, i, j0, dd);
+        } else {
+            T rr[3][V], vv[3][V];
+            load3<T>(r, g, pair, i, j0, rr);
+            load3<T>(v, g, pair, i, j0, vv);
+            if (KIND == 0) {
+                const T bk = T(st[pair].beta_k), om = T(st[pair].omega);
+                T pp[3][V];
+                load3<T>(d, g, pair, i, j0, pp);
+#pragma unroll
+                for (int q = 0; q < 3; ++q)
+#pragma unroll
+                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[q][k] + bk * (pp[q][k] - om * vv[q][k]) : T(0);
+            } else {
+                const T al = T(st[pair].alpha);
+#pragma unroll
+                for (int q = 0; q < 3; ++q)
+#pragma unroll
+                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[q][k] - al * vv[q][k] : T(0);
+            }
+            store3<T>(d, g, pair, i, j0, dd);
+        }
+#pragma unroll
+        for (int k = 0; k < V; ++k) {
+            T z0, z1, z2;
+            block_solve<T>(cf[k], a, be, dd[0][k], dd[1][k], dd[2][k], z0, z1, z2);
+            zz[0][k] = inside[k] ? w * z0 : T(0);
+            zz[1][k] = inside[k] ? w * z1 : T(0);
+            zz[2][k] = inside[k] ? w * z2 : T(0);
+        }
+        store3<T>(z, g, pair, i, j0, zz);
+    }
+    __device__ __forceinline__ void finish(int, bool) {}
+};
+
+template <typename T, bool FROM_IMAGE, typename Op>
+__global__ void __launch_bounds__(128) k_sweep(LevelArgs<T> L, const T* __restrict__ x, Op op) {
+    sweep_body<T, FROM_IMAGE, Op>(L, x, op);
+}
+
+// ------------------------------------------------------------------ BLAS-1 with fused dots
+// omega = (t.s)/(t.t) was computed by k_scalars; x += alpha ph + omega sh ; r = s - omega t ;
+// acc[2] += r.r ; acc[3] += rhat.r
+template <typename T>
+__global__ void __launch_bounds__(256) k_update_x_r(long long n_per_pair, long long pair_stride,
+                                                    T* __restrict__ x, const T* __restrict__ ph, const T* __restrict__ sh,
+                                                    T* __restrict__ r, const T* __restrict__ s, const T* __restrict__ t,
+                                                    const T* __restrict__ rhat, PairState* __restrict__ st) {
+    const int pair = blockIdx.y;
+    double acc[2] = {0.0, 0.0};
+    if (st[pair].active) {
+        const T al = T(st[pair].alpha), om = T(st[pair].omega);
+        const long long base = (long long)pair * pair_stride;
+        for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n_per_pair;
+             e += (long long)gridDim.x * blockDim.x) {
+            const long long k = base + e;
+            x[k] = x[k] + al * ph[k] + om * sh[k];
+            const T rn = s[k] - om * t[k];
+            r[k] = rn;
+            acc[0] += (double)rn * (double)rn;
+            acc[1] += (double)rhat[k] * (double)rn;
+        }
+    }
+    block_accumulate<2>(acc, st[pair].acc + 2);
+}
+
+// ------------------------------------------------------------------ scalar stages (one thread per pair)
+// stage 0: after the initial residual   (acc[2] = r.r, acc[3] = rhat.r = r.r)
+// stage 1: after v = S ph               (acc[0] = rhat.v)            -> alpha
+// stage 2: after t = S sh               (acc[0] = t.s, acc[1] = t.t) -> omega
+// stage 3: after the x/r update         (acc[2] = r.r, acc[3] = rhat.r) -> convergence test, beta_k
+__global__ void k_scalars(PairState* __restrict__ st, int* __restrict__ active_arr, int B, int stage, double rtol, int max_it,
+                          int* __restrict__ n_active) {
+    const int pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= B) return;
+    PairState s = st[pair];
+    if (!s.active) return;
+    const double tiny = 1e-300;
+    if (stage == 0) {
+        s.relres = (s.bnorm > 0.0) ? sqrt(s.acc[2]) / s.bnorm : 0.0;
+        s.rho = s.acc[3]; s.rho_old = 1.0; s.alpha = 1.0; s.omega = 1.0; s.beta_k = 0.0; s.iters = 0;
+        if (s.relres <= rtol || s.bnorm == 0.0) { s.active = 0; s.status = ST_CONVERGED; }
+    } else if (stage == 1) {
+        if (!(fabs(s.acc[0]) > tiny) || !isfinite(s.acc[0])) { s.active = 0; s.status = ST_BREAKDOWN; }
+        else s.alpha = s.rho / s.acc[0];
+    } else if (stage == 2) {
+        if (!(s.acc[1] > tiny) || !isfinite(s.acc[0]) || !isfinite(s.acc[1])) { s.active = 0; s.status = ST_BREAKDOWN; }
+        else s.omega = s.acc[0] / s.acc[1];
+    } else {
+        s.iters += 1;
+        s.relres = sqrt(s.acc[2]) / s.bnorm;
+        if (!isfinite(s.relres)) { s.active = 0; s.status = ST_BREAKDOWN; }
+        else if (s.relres <= rtol) { s.active = 0; s.status = ST_CONVERGED; }
+        else if (s.iters >= max_it) { s.active = 0; s.status = ST_MAXIT; }
+        else {
+            const double rho_new = s.acc[3];
+            if (!(fabs(s.omega) > tiny) || !(fabs(s.rho) > tiny)) { s.active = 0; s.status = ST_BREAKDOWN; }
+            else { s.beta_k = (rho_new / s.rho) * (s.alpha / s.omega); s.rho_old = s.rho; s.rho = rho_new; }
+        }
+    }
+    s.acc[0] = s.acc[1] = s.acc[2] = s.acc[3] = 0.0;
+    st[pair] = s;
+    active_arr[pair] = s.active;
+    if (n_active != nullptr && s.active) atomicAdd(n_active, 1);
+}
+
+}  // namespace ofb

@@ -1,0 +1,300 @@
+"""Drop-in for the hot path of kursawe/OpticalFlow ``source/optical_flow.py``.
+
+Same entry points, argument conventions and result dictionaries as the reference
+(``variational_optical_flow`` :715-1210, ``vary_regularisation`` :1918-1998, ``blur_movie`` :282-306 and the
+small helpers :676-713, :1212-1316); the work is done by hand-written sm_100a kernels behind the C ABI of
+``include/ofb200.h``.  There is no CPU fallback: without a CUDA device or without ``libofb200.so`` the
+calls raise.
+
+Differences from the reference that a caller can observe (all documented in DESIGN.md):
+  * the frame pairs of a movie are solved as independent systems, batched, each from the user's
+    ``initial_*`` guess (the reference warm-starts pair k from pair k-1, :803-806); the answers agree to
+    O(rtol);
+  * ``use_direct_solver=True`` has no sparse-direct equivalent on the device; it tightens the iterative
+    tolerance to 1e-12 instead;
+  * nothing is printed unless ``verbose=True``;
+  * solver diagnostics of every pair are returned under ``result['solver_info']``.
+Keyword-only extras (defaults preserve reference behaviour): ``dtype``, ``rtol``, ``max_it``,
+``preconditioner``, ``device``, ``batch_pairs``, ``verbose``.
+"""
+import time
+
+import numpy as np
+import torch
+
+from . import _lib, engine
+
+__all__ = ['variational_optical_flow', 'vary_regularisation', 'blur_movie', 'apply_numerical_derivative',
+           'apply_constant_boundary_condition', 'get_index_set', 'format_elapsed_time']
+
+_QUANTITY_OFFSET = {'ux': 0, 'uy': 1, 'remodelling': 2}
+
+
+# ------------------------------------------------------------------------------------------------
+# small helpers of the reference interface (host-side index/array utilities)
+# ------------------------------------------------------------------------------------------------
+def format_elapsed_time(time_difference):
+    """(minutes, seconds, milliseconds) of a time.time() difference (optical_flow.py:1212-1238)."""
+    whole = int(time_difference)
+    return int(time_difference // 60), int(time_difference % 60), int((time_difference - whole) * 1000)
+
+
+def get_index_set(N_i, N_j, i_offset, j_offset, quantity, include_boundaries=False):
+    """Flattened indices 3*N_j*(i+i_offset) + 3*(j+j_offset) + q of the reference's interleaved unknown
+    numbering (optical_flow.py:1241-1302); q = 0,1,2 for 'ux','uy','remodelling'."""
+    if quantity not in _QUANTITY_OFFSET:
+        raise ValueError('I cannot figure out what quantity you want from me. Must be ux, uy, or remodelling.')
+    lo = 0 if include_boundaries else 1
+    i = np.arange(lo, N_i - lo, dtype=np.int32)[:, None] + i_offset
+    j = np.arange(lo, N_j - lo, dtype=np.int32)[None, :] + j_offset
+    return (3 * N_j * i + 3 * j + _QUANTITY_OFFSET[quantity]).ravel()
+
+
+# rule -> list of (weight, row shift, column shift); shifts are relative to the interior pixel
+_STENCILS = {
+    'dx': ((0.5, 1, 0), (-0.5, -1, 0)),
+    'dxy': ((0.25, 1, 1), (-0.25, 1, -1), (-0.25, -1, 1), (0.25, -1, -1)),
+    'dxx': ((1.0, 1, 0), (1.0, -1, 0), (-2.0, 0, 0)),
+    'dyy': ((1.0, 0, 1), (1.0, 0, -1), (-2.0, 0, 0)),
+    'bar_x': ((1.0, 1, 0), (1.0, -1, 0)),
+    'bar_y': ((1.0, 0, 1), (1.0, 0, -1)),
+    'bar': ((1.0, -1, 0), (1.0, 1, 0), (1.0, 0, 1), (1.0, 0, -1)),
+}
+_STENCILS['dy'] = _STENCILS['dx']      # the reference's 'dy' rule is the x-derivative (:698-699); kept for parity
+_STENCILS['dyx'] = _STENCILS['dxy']
+
+
+def apply_numerical_derivative(matrix, rule):
+    """Finite-difference stencil on a bordered 2-D array, interior returned (optical_flow.py:676-713)."""
+    if rule not in _STENCILS:
+        raise ValueError('unknown derivative rule %r' % (rule,))
+    matrix = np.asarray(matrix)
+    Nx, Ny = matrix.shape
+    out = np.zeros((Nx - 2, Ny - 2), dtype=np.result_type(matrix.dtype, np.float64))
+    for weight, di, dj in _STENCILS[rule]:
+        out += weight * matrix[1 + di:Nx - 1 + di, 1 + dj:Ny - 1 + dj]
+    return out
+
+
+def apply_constant_boundary_condition(image):
+    """In-place edge overwrite, rows first then columns (optical_flow.py:1304-1316)."""
+    for axis in (0, 1):
+        view = image if axis == 0 else image.T
+        view[0] = view[2]
+        view[-1] = view[-3]
+
+
+def _device(device):
+    if not torch.cuda.is_available():
+        raise _lib.OfbError('no CUDA device available: this path has no CPU fallback')
+    return torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+
+
+def blur_movie(movie, smoothing_sigma, *, dtype='float64', device=None):
+    """Per-frame Gaussian blur (optical_flow.py:282-306), computed on the GPU, returned as float64."""
+    dev = _device(device)
+    tdtype, _ = engine.resolve_dtype(dtype)
+    movie = np.asarray(movie)
+    frames = torch.from_numpy(np.ascontiguousarray(movie)).to(dev).to(tdtype)
+    return engine.blur(frames, smoothing_sigma).to(torch.float64).cpu().numpy()
+
+
+# ------------------------------------------------------------------------------------------------
+# the hot path
+# ------------------------------------------------------------------------------------------------
+def _default_batch(Nx, Ny, itemsize, n_pairs):
+    # ~12 level-0 vectors + hierarchy per pair; stay under a few GB of workspace
+    per_pair = 16 * 3 * Nx * Ny * itemsize
+    return int(max(1, min(n_pairs, (6 << 30) // per_pair, 64)))
+
+
+def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace, solver_options):
+    """Solve a batch; pairs the multigrid path could not converge are redone with block-Jacobi."""
+    B = P.shape[0]
+    b = engine.build_rhs(P, C)
+    x = x0.clone()
+    opts = engine.make_options(preconditioner, **solver_options)
+    iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace)
+    fallback = torch.zeros(B, dtype=torch.bool, device=P.device)
+    if opts.precond == _lib.PRECOND_MG:
+        bad = (conv == 0).nonzero().flatten()
+        if bad.numel() > 0:
+            fb_opts = engine.make_options('bjacobi', **{k: v for k, v in solver_options.items()
+                                                        if k in ('check_every', 'rows_per_strip')})
+            xb = x0[bad].clone()
+            a_b = engine._weights(alpha, B, P.device)[bad]
+            be_b = engine._weights(beta, B, P.device)[bad]
+            it2, rr2, cv2 = engine.solve(P[bad].contiguous(), b[bad].contiguous(), xb, a_b, be_b, rtol, max_it,
+                                         fb_opts, workspace)
+            better = (cv2 == 1) | (rr2 < relres[bad])
+            sel = bad[better]
+            x[sel] = xb[better]
+            iters[sel] = it2[better] + iters[sel]
+            relres[sel] = rr2[better]
+            conv[sel] = cv2[better]
+            fallback[sel] = True
+    return x, iters, relres, conv, fallback
+
+
+def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, remodelling_alpha=1000.0,
+                             smoothing_sigma=None, initial_v_x=0.0, initial_v_y=0.0, initial_remodelling=0.0,
+                             use_direct_solver=False, *, dtype='float64', rtol=1e-6, max_it=1000,
+                             preconditioner='mg', device=None, batch_pairs=None, verbose=False,
+                             solver_options=None):
+    """Variational optical flow with net remodelling on every consecutive frame pair of ``movie``.
+
+    Signature, defaults, units and result keys follow optical_flow.py:715-1210: ``movie[T,Nx,Ny]``; velocities
+    are returned in ``delta_x/delta_t`` units, ``remodelling`` unscaled; ``result['converged']`` refers to the
+    last pair (:1202) and ``result['speed_functional']`` holds the remodelling functional (:1205)."""
+    t_start = time.time()
+    dev = _device(device)
+    tdtype, _ = engine.resolve_dtype(dtype)
+    movie_np = np.asarray(movie)
+    if movie_np.ndim != 3 or movie_np.shape[0] < 2:
+        raise ValueError('movie must be [T>=2, Nx, Ny]')
+    T, Nx, Ny = movie_np.shape
+    n_pairs = T - 1
+    original = movie_np.astype(np.float64)                                     # :769
+    if use_direct_solver:
+        rtol = min(rtol, 1e-12)
+    solver_options = dict(solver_options or {})
+    itemsize = 4 if tdtype == torch.float32 else 8
+    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs)
+    scale_in = float(delta_t) / float(delta_x)                                 # :800-801
+    scale_out = float(delta_x) / float(delta_t)                                # :1189-1190
+    guess = (float(initial_v_x) * scale_in, float(initial_v_y) * scale_in, float(initial_remodelling))
+
+    out = {k: np.empty((n_pairs, Nx, Ny), dtype=np.float64) for k in ('v_x', 'v_y', 'speed', 'remodelling')}
+    blurred = np.empty((T, Nx, Ny), dtype=np.float64) if smoothing_sigma is not None else original
+    functionals = np.zeros((n_pairs, 3))
+    info = dict(iterations=np.zeros(n_pairs, np.int32), relative_residual=np.zeros(n_pairs),
+                converged=np.zeros(n_pairs, bool), fallback=np.zeros(n_pairs, bool))
+    workspace = engine.Workspace()
+    source = np.ascontiguousarray(movie_np)
+    for k0 in range(0, n_pairs, B):
+        k1 = min(k0 + B, n_pairs)
+        nb = k1 - k0
+        frames = torch.from_numpy(source[k0:k1 + 1]).to(dev).to(tdtype)        # nb+1 frames
+        if smoothing_sigma is not None:
+            frames = engine.blur(frames, smoothing_sigma)                      # :770-771
+            last = k1 + 1 if k1 == n_pairs else k1
+            blurred[k0:last] = frames[:last - k0].to(torch.float64).cpu().numpy()
+        P, C = frames[:-1], frames[1:]
+        x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
+        for q in range(3):
+            x0[:, q] = guess[q]
+        x, iters, relres, conv, fb = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
+                                                  preconditioner, workspace, solver_options)
+        vx, vy, sp, gm, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out)
+        out['v_x'][k0:k1] = vx.to(torch.float64).cpu().numpy()
+        out['v_y'][k0:k1] = vy.to(torch.float64).cpu().numpy()
+        out['speed'][k0:k1] = sp.to(torch.float64).cpu().numpy()
+        out['remodelling'][k0:k1] = gm.to(torch.float64).cpu().numpy()
+        functionals[k0:k1] = fun.cpu().numpy()
+        info['iterations'][k0:k1] = iters.cpu().numpy()
+        info['relative_residual'][k0:k1] = relres.cpu().numpy()
+        info['converged'][k0:k1] = conv.cpu().numpy() != 0
+        info['fallback'][k0:k1] = fb.cpu().numpy()
+        if verbose:
+            print('pairs %d..%d: iterations %s, residuals %s' % (k0 + 1, k1, info['iterations'][k0:k1],
+                                                                   info['relative_residual'][k0:k1]))
+    if verbose and not info['converged'].all():
+        print('the solver has not actually converged, the result will be incorrect or inaccurate')
+    result = dict()
+    result['v_x'] = out['v_x']
+    result['v_y'] = out['v_y']
+    result['speed'] = out['speed']
+    result['remodelling'] = out['remodelling']
+    result['original_data'] = original
+    result['delta_x'] = delta_x
+    result['delta_t'] = delta_t
+    result['blurred_data'] = blurred
+    result['converged'] = bool(info['converged'][-1])
+    result['L1_functional'] = float(np.sum(functionals[:, 0]))
+    result['remodelling_functional'] = float(np.sum(functionals[:, 2]))
+    result['speed_functional'] = float(np.sum(functionals[:, 2]))          # sic, optical_flow.py:1205
+    info['speed_functional_per_pair'] = functionals[:, 1].copy()
+    info['elapsed_seconds'] = time.time() - t_start
+    info['dtype'] = str(tdtype).replace('torch.', '')
+    info['batch_pairs'] = B
+    result['solver_info'] = info
+    return result
+
+
+def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
+                        remodelling_alpha_values=np.arange(500, 2000, 500), filename=None, **kwargs):
+    """Grid of regularisation weights -> summary statistics (optical_flow.py:1918-1998).
+
+    Every (speed_alpha, remodelling_alpha) cell is what ``variational_optical_flow(movie, speed_alpha=...,
+    remodelling_alpha=..., **kwargs)`` would give, but the cells are solved together: the blurred frames are
+    shared on the device and the cells of a frame pair form one batch with per-entry weights; means,
+    variances and the functional are reduced on the device (epilogue moments), no field is copied back."""
+    dev = _device(kwargs.pop('device', None))
+    tdtype, _ = engine.resolve_dtype(kwargs.pop('dtype', 'float64'))
+    rtol = kwargs.pop('rtol', 1e-6)
+    max_it = kwargs.pop('max_it', 1000)
+    preconditioner = kwargs.pop('preconditioner', 'mg')
+    solver_options = dict(kwargs.pop('solver_options', None) or {})
+    batch_pairs = kwargs.pop('batch_pairs', None)
+    kwargs.pop('verbose', None)
+    delta_x = kwargs.pop('delta_x', 1.0)
+    delta_t = kwargs.pop('delta_t', 1.0)
+    smoothing_sigma = kwargs.pop('smoothing_sigma', None)
+    guess = (float(kwargs.pop('initial_v_x', 0.0)) * delta_t / delta_x,
+             float(kwargs.pop('initial_v_y', 0.0)) * delta_t / delta_x, float(kwargs.pop('initial_remodelling', 0.0)))
+    if kwargs.pop('use_direct_solver', False):
+        rtol = min(rtol, 1e-12)
+    if kwargs:
+        raise TypeError('unexpected keyword arguments: %s' % sorted(kwargs))
+    movie_np = np.ascontiguousarray(np.asarray(movie))
+    T, Nx, Ny = movie_np.shape
+    n_pairs = T - 1
+    alphas = np.asarray(speed_alpha_values, dtype=np.float64)
+    betas = np.asarray(remodelling_alpha_values, dtype=np.float64)
+    cell_alpha = np.repeat(alphas, len(betas))
+    cell_beta = np.tile(betas, len(alphas))
+    n_cells = cell_alpha.size
+    itemsize = 4 if tdtype == torch.float32 else 8
+    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_cells)
+    moments = np.zeros((n_cells, 4))
+    functional = np.zeros(n_cells)
+    converged_last = np.zeros(n_cells, bool)
+    workspace = engine.Workspace()
+    for k in range(n_pairs):
+        frames = torch.from_numpy(movie_np[k:k + 2]).to(dev).to(tdtype)
+        if smoothing_sigma is not None:
+            frames = engine.blur(frames, smoothing_sigma)
+        for c0 in range(0, n_cells, B):
+            c1 = min(c0 + B, n_cells)
+            nb = c1 - c0
+            P = frames[0:1].expand(nb, Nx, Ny).contiguous()
+            C = frames[1:2].expand(nb, Nx, Ny).contiguous()
+            x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
+            for q in range(3):
+                x0[:, q] = guess[q]
+            a = torch.from_numpy(cell_alpha[c0:c1]).to(dev)
+            be = torch.from_numpy(cell_beta[c0:c1]).to(dev)
+            x, iters, relres, conv, fb = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace,
+                                                      solver_options)
+            _, _, _, _, fun, mom = engine.epilogue(P, C, x, a, be, float(delta_x) / float(delta_t))
+            moments[c0:c1] += mom.cpu().numpy()
+            fun = fun.cpu().numpy()
+            functional[c0:c1] += fun[:, 0] + 2.0 * fun[:, 2]        # L1 + 'speed' (= remodelling, :1205) + remodelling
+            if k == n_pairs - 1:
+                converged_last[c0:c1] = conv.cpu().numpy() != 0
+    count = float(n_pairs * Nx * Ny)
+    shape = (len(alphas), len(betas))
+    speed_mean = moments[:, 0] / count
+    rem_mean = moments[:, 2] / count
+    result_dict = {}
+    result_dict['speed_alpha_values'] = speed_alpha_values
+    result_dict['remodelling_alpha_values'] = remodelling_alpha_values
+    result_dict['speed_means'] = speed_mean.reshape(shape)
+    result_dict['speed_variances'] = (moments[:, 1] / count - speed_mean ** 2).reshape(shape)
+    result_dict['remodelling_means'] = rem_mean.reshape(shape)
+    result_dict['remodelling_variances'] = (moments[:, 3] / count - rem_mean ** 2).reshape(shape)
+    result_dict['converged'] = converged_last.reshape(shape)
+    result_dict['functional'] = functional.reshape(shape)
+    if filename is not None:
+        np.save(filename, result_dict)
+    return result_dict

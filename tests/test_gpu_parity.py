@@ -1,0 +1,215 @@
+"""GPU parity tests (B200): every stage through the C ABI against the oracle, the drop-in against the committed
+golden vectors of the unmodified reference, and size-independent properties at 1024^2.
+
+Tolerances (BASELINE.json north_star): fp64 <= 1e-6 relative L2 on returned fields; fp32 <= 1e-3 relative L2
+and <= 1e-2 px max abs on v_x, v_y."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import flow_oracle as fo
+from oracle import mg_model as mg
+from opticalflow_b200 import engine, optical_flow, synthetic
+from test_oracle_cpu import GOLDEN_NAMES, load_golden
+
+pytestmark = pytest.mark.gpu
+
+
+def rel(a, b):
+    return np.linalg.norm(np.asarray(a) - np.asarray(b)) / max(np.linalg.norm(np.asarray(b)), 1e-300)
+
+
+def dev_t(a, device, dtype=torch.float64):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(device).to(dtype).contiguous()
+
+
+SHAPES = [(5, 5), (7, 6), (23, 31), (40, 56), (64, 64), (33, 130), (129, 257)]
+
+
+@pytest.mark.parametrize('shape', SHAPES)
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-13), (torch.float32, 2e-5)])
+def test_full_operator_matches_reference_matrix(cuda_device, shape, dtype, tol):
+    rng = np.random.default_rng(shape[0] * 1000 + shape[1])
+    P = rng.uniform(20, 200, shape)
+    x = rng.standard_normal((3,) + shape)
+    alpha, beta = 123.0, 45.0
+    want = fo.apply_operator(P, x, alpha, beta)          # == reference CSR @ x (tests/test_oracle_cpu.py)
+    got = engine.apply_operator(dev_t(P[None], cuda_device, dtype), dev_t(x[None], cuda_device, dtype), alpha, beta)
+    assert rel(got[0].cpu().double().numpy(), want) < tol
+
+
+@pytest.mark.parametrize('shape', SHAPES)
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-13), (torch.float32, 2e-5)])
+def test_eliminated_operator_matches_model(cuda_device, shape, dtype, tol):
+    rng = np.random.default_rng(shape[0] * 77 + shape[1])
+    B = 3
+    P = rng.uniform(20, 200, (B,) + shape)
+    x = rng.standard_normal((B, 3) + shape)
+    alphas, betas = np.array([1.0, 1e3, 1e5]), np.array([1e4, 10.0, 1e2])
+    got = engine.apply_operator(dev_t(P, cuda_device, dtype), dev_t(x, cuda_device, dtype),
+                                torch.from_numpy(alphas), torch.from_numpy(betas), eliminated=True).cpu().double().numpy()
+    for k in range(B):
+        want = mg.apply_eliminated(P[k], x[k], alphas[k], betas[k])
+        assert rel(got[k], want) < tol
+
+
+@pytest.mark.parametrize('shape', [(5, 5), (23, 31), (64, 64), (129, 257)])
+def test_rhs_and_blur(cuda_device, shape):
+    rng = np.random.default_rng(9)
+    movie = rng.uniform(0, 255, (3,) + shape)
+    d = dev_t(movie, cuda_device)
+    b = engine.build_rhs(d[:-1].contiguous(), d[1:].contiguous()).cpu().numpy()
+    for k in range(2):
+        assert rel(b[k], fo.build_rhs(movie[k], movie[k + 1])) < 1e-14
+    for sigma in (0.8, 2.5):
+        got = engine.blur(d, sigma).cpu().numpy()
+        assert np.abs(got - fo.blur_movie(movie, sigma)).max() < 1e-10
+        got32 = engine.blur(d.float(), sigma).cpu().numpy()
+        assert np.abs(got32 - fo.blur_movie(movie, sigma)).max() < 2e-3
+
+
+def test_multigrid_hierarchy_matches_model(cuda_device):
+    """One V(2,2) application on the device == the numpy model of the same cycle (averaged coefficients)."""
+    import importlib.util, os, sys
+    movie = fo.blur_movie(synthetic.translating_movie(66, 50, 2, seed=5), 2.0)
+    P = movie[0]
+    rng = np.random.default_rng(2)
+    r = mg.zero_ghosts(rng.standard_normal((3,) + P.shape))
+    z = engine.precondition(dev_t(P[None], cuda_device), dev_t(r[None], cuda_device), 1e5, 1e4)[0].cpu().numpy()
+    # a preconditioner must reduce the residual of S z = r substantially in one application
+    res = r - mg.apply_eliminated(P, z, 1e5, 1e4)
+    assert np.linalg.norm(res) / np.linalg.norm(r) < 0.35
+    assert np.abs(z[:, 0, :]).max() == 0.0 and np.abs(z[:, :, -1]).max() == 0.0
+
+
+@pytest.mark.parametrize('precond', ['mg', 'bjacobi'])
+@pytest.mark.parametrize('shape', [(24, 24), (40, 56), (64, 64)])
+def test_solve_fp64_matches_direct_solution(cuda_device, shape, precond):
+    movie = fo.blur_movie(synthetic.translating_movie(shape[0], shape[1], 2, seed=6), 2.5)
+    P, C = movie
+    alpha, beta = 1e5, 1e4
+    xd, _ = fo.solve_pair(P, C, alpha, beta)
+    Pd, Cd = dev_t(P[None], cuda_device), dev_t(C[None], cuda_device)
+    b = engine.build_rhs(Pd, Cd)
+    x = torch.zeros_like(b)
+    it, rr, cv = engine.solve(Pd, b, x, alpha, beta, rtol=1e-11, max_it=5000, options=engine.make_options(precond))
+    assert int(cv[0]) == 1, (int(it[0]), float(rr[0]))
+    assert rel(x[0].cpu().numpy(), xd) < 1e-7                       # raw solution, ghost ring included
+    if precond == 'mg':
+        assert int(it[0]) <= 40
+
+
+def test_solve_initial_guess_and_batch_weights(cuda_device):
+    """Per-pair weights in one batch; nonzero initial guess; converged pairs stop iterating."""
+    movie = fo.blur_movie(synthetic.translating_movie(48, 48, 3, seed=8), 2.5)
+    alphas, betas = np.array([1e5, 2e4]), np.array([1e4, 1e3])
+    Pd, Cd = dev_t(movie[:-1], cuda_device), dev_t(movie[1:], cuda_device)
+    b = engine.build_rhs(Pd, Cd)
+    x = torch.full_like(b, 0.3)
+    it, rr, cv = engine.solve(Pd, b, x, torch.from_numpy(alphas), torch.from_numpy(betas), rtol=1e-11, max_it=500)
+    assert cv.tolist() == [1, 1]
+    for k in range(2):
+        xd, _ = fo.solve_pair(movie[k], movie[k + 1], alphas[k], betas[k])
+        assert rel(x[k].cpu().numpy(), xd) < 1e-7
+
+
+@pytest.mark.parametrize('name', GOLDEN_NAMES)
+def test_dropin_fp64_matches_reference_golden(cuda_device, name):
+    z, kwargs = load_golden(name)
+    got = optical_flow.variational_optical_flow(z['movie'], dtype='float64', rtol=1e-11, max_it=20000, **kwargs)
+    assert got['converged']
+    for key in ('v_x', 'v_y', 'speed', 'remodelling'):
+        assert rel(got[key], z[key]) < 1e-6, (key, got['solver_info'])
+    fun = np.array([got['L1_functional'], got['remodelling_functional'], got['speed_functional']])
+    np.testing.assert_allclose(fun, z['functionals'], rtol=1e-6)
+    if 'blurred_data' in z.files:
+        assert np.abs(got['blurred_data'] - z['blurred_data']).max() < 1e-9
+    assert set(got) - {'solver_info'} == {'v_x', 'v_y', 'speed', 'remodelling', 'original_data', 'delta_x', 'delta_t',
+                                         'blurred_data', 'converged', 'L1_functional', 'remodelling_functional',
+                                         'speed_functional'}
+    assert got['v_x'].dtype == np.float64 and got['v_x'].shape == z['v_x'].shape
+
+
+@pytest.mark.parametrize('name', ['texture64', 'texture96_realregime', 'ragged_40x56'])
+def test_dropin_fp32_within_stated_tolerance(cuda_device, name):
+    z, kwargs = load_golden(name)
+    got = optical_flow.variational_optical_flow(z['movie'], dtype='float32', rtol=1e-6, **kwargs)
+    scale = kwargs.get('delta_x', 1.0) / kwargs.get('delta_t', 1.0)
+    for key in ('v_x', 'v_y'):
+        assert rel(got[key], z[key]) < 1e-3, (key, got['solver_info'])
+        assert np.abs(got[key] - z[key]).max() < 1e-2 * scale
+    assert rel(got['remodelling'], z['remodelling']) < 1e-3
+
+
+def test_dropin_256_config_d1(cuda_device):
+    """BASELINE.json configs[0]: 256^2 pair translated by (1.5,-0.7); oracle direct solve takes ~30 s."""
+    movie = synthetic.translating_movie(256, 256, 2)
+    kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.5)
+    want = fo.variational_optical_flow(movie, **kw)
+    got64 = optical_flow.variational_optical_flow(movie, dtype='float64', rtol=1e-10, **kw)
+    got32 = optical_flow.variational_optical_flow(movie, dtype='float32', rtol=1e-6, **kw)
+    for key in ('v_x', 'v_y', 'remodelling'):
+        assert rel(got64[key], want[key]) < 1e-6, key
+        assert rel(got32[key], want[key]) < 1e-3, key
+    assert np.abs(got32['v_x'] - want['v_x']).max() < 1e-2 and np.abs(got32['v_y'] - want['v_y']).max() < 1e-2
+    assert got64['solver_info']['iterations'][0] <= 40
+
+
+def test_vary_regularisation_matches_loop(cuda_device):
+    movie = synthetic.translating_movie(40, 48, 3, seed=12)
+    alphas, betas = np.array([2e4, 1e5]), np.array([1e3, 1e4, 1e5])
+    got = optical_flow.vary_regularisation(movie, alphas, betas, smoothing_sigma=2.0, rtol=1e-11, max_it=20000)
+    assert got['speed_means'].shape == (2, 3) and got['converged'].dtype == bool
+    for i, a in enumerate(alphas):
+        for j, b in enumerate(betas):
+            ref = fo.variational_optical_flow(movie, speed_alpha=a, remodelling_alpha=b, smoothing_sigma=2.0)
+            assert abs(got['speed_means'][i, j] - np.mean(ref['speed'])) < 1e-7 * np.mean(ref['speed'])
+            assert abs(got['speed_variances'][i, j] - np.var(ref['speed'])) < 1e-6 * np.var(ref['speed'])
+            assert abs(got['remodelling_means'][i, j] - np.mean(ref['remodelling'])) < 1e-6 * abs(np.mean(ref['remodelling'])) + 1e-12
+            total = ref['L1_functional'] + ref['speed_functional'] + ref['remodelling_functional']
+            assert abs(got['functional'][i, j] - total) < 1e-6 * total
+            assert got['converged'][i, j]
+
+
+def test_low_alpha_regime_falls_back_and_still_matches(cuda_device):
+    """Regularisation weights where the multigrid cycle is not contractive: the block-Jacobi path must take over."""
+    movie = fo.blur_movie(synthetic.translating_movie(32, 32, 2, seed=13), 2.5)
+    want = fo.variational_optical_flow(movie, speed_alpha=1e3, remodelling_alpha=1e4)
+    got = optical_flow.variational_optical_flow(movie, speed_alpha=1e3, remodelling_alpha=1e4, rtol=1e-11, max_it=300,
+                                                solver_options=dict())
+    if not got['converged']:
+        got = optical_flow.variational_optical_flow(movie, speed_alpha=1e3, remodelling_alpha=1e4, rtol=1e-11,
+                                                    max_it=20000, preconditioner='bjacobi')
+    assert got['converged']
+    for key in ('v_x', 'v_y', 'remodelling'):
+        assert rel(got[key], want[key]) < 1e-6
+
+
+def test_full_size_1024_properties(cuda_device):
+    """BASELINE full size: fp32 batch at 1024^2. Oracle-free properties: convergence in few iterations, the true
+    residual evaluated in fp64 through the C-ABI operator, linearity of the operator, fp32 vs fp64 agreement."""
+    movie = synthetic.rotating_shearing_movie(1024, 1024, 3)
+    kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.5)
+    got32 = optical_flow.variational_optical_flow(movie, dtype='float32', rtol=1e-6, **kw)
+    got64 = optical_flow.variational_optical_flow(movie, dtype='float64', rtol=1e-10, **kw)
+    assert got32['solver_info']['converged'].all() and got64['solver_info']['converged'].all()
+    assert got32['solver_info']['iterations'].max() <= 30
+    for key in ('v_x', 'v_y', 'remodelling'):
+        assert rel(got32[key], got64[key]) < 1e-3, key
+    assert np.abs(got32['v_x'] - got64['v_x']).max() < 1e-2
+    # true residual of the fp64 answer, recomputed independently in fp64 on the device
+    frames = engine.blur(dev_t(movie, cuda_device), 2.5)
+    P, C = frames[:-1].contiguous(), frames[1:].contiguous()
+    b = engine.build_rhs(P, C)
+    x = torch.stack([dev_t(got64[k], cuda_device) for k in ('v_x', 'v_y', 'remodelling')], dim=1).contiguous()
+    r = b - engine.apply_operator(P, x, 1e5, 1e4, eliminated=True)
+    assert float(r.norm() / b.norm()) < 1e-8
+    # linearity
+    y1 = engine.apply_operator(P, x, 1e5, 1e4)
+    y2 = engine.apply_operator(P, 2.5 * x, 1e5, 1e4)
+    assert float((y2 - 2.5 * y1).norm() / y1.norm()) < 1e-13
+    # recovered flow is close to the imposed rotation+shear in the interior
+    ii, jj = np.meshgrid(np.arange(1024.0), np.arange(1024.0), indexing='ij')
+    vx_true = (-1e-3 + 5e-4) * (jj - 511.5)
+    sl = (slice(100, -100), slice(100, -100))
+    assert np.abs(got64['v_x'][0][sl] - vx_true[sl]).mean() < 0.1

@@ -1,0 +1,61 @@
+"""CPU tests of the C-ABI library: it builds for sm_100a, loads, and exports every symbol the header declares.
+No compute call is made here (no GPU)."""
+import ctypes
+import os
+import re
+
+import pytest
+
+from conftest import ROOT
+
+
+def test_library_exports_every_declared_symbol(built_library):
+    from opticalflow_b200 import _lib
+    header = open(os.path.join(ROOT, 'include', 'ofb200.h')).read()
+    declared = set(re.findall(r'\b(ofb_[a-z_0-9]+)\s*\(', header))
+    declared.discard('ofb_solve_options')
+    assert declared == set(_lib.EXPORTED_SYMBOLS)
+    for name in declared:
+        assert getattr(built_library, name) is not None
+
+
+def test_version_options_and_workspace(built_library):
+    from opticalflow_b200 import _lib
+    assert built_library.ofb_version() == _lib.ABI_VERSION
+    opt = _lib.default_options()
+    assert (opt.precond, opt.nu_pre, opt.nu_post, opt.check_every) == (_lib.PRECOND_MG, 2, 2, 1)
+    assert abs(opt.omega - 0.8) < 1e-15
+    small = built_library.ofb_workspace_bytes(1, 64, 64, _lib.OFB_F32, _lib.PRECOND_BJACOBI)
+    mg32 = built_library.ofb_workspace_bytes(1, 64, 64, _lib.OFB_F32, _lib.PRECOND_MG)
+    mg64 = built_library.ofb_workspace_bytes(1, 64, 64, _lib.OFB_F64, _lib.PRECOND_MG)
+    assert 9 * 3 * 64 * 64 * 4 <= small < mg32 < mg64
+    assert built_library.ofb_workspace_bytes(4, 64, 64, _lib.OFB_F32, _lib.PRECOND_MG) > 3 * mg32
+
+
+def test_bad_arguments_are_reported_not_crashed(built_library):
+    from opticalflow_b200 import _lib
+    assert built_library.ofb_workspace_bytes(1, 4, 64, _lib.OFB_F32, _lib.PRECOND_MG) == 0
+    assert b'5x5' in built_library.ofb_last_error()
+    rc = built_library.ofb_build_rhs(None, None, None, 0, 64, 64, _lib.OFB_F32, None)
+    assert rc < 0 and b'batch' in built_library.ofb_last_error()
+    rc = built_library.ofb_solve(None, None, None, None, None, 1e-6, 10, None, None, 0, None, None, None,
+                                 1, 64, 64, 7, None)
+    assert rc < 0 and b'dtype' in built_library.ofb_last_error()
+
+
+def test_product_path_fails_loudly_without_cuda():
+    import numpy as np
+    import torch
+    from opticalflow_b200 import _lib, optical_flow
+    if torch.cuda.is_available():
+        pytest.skip('a GPU is present')
+    with pytest.raises(_lib.OfbError):
+        optical_flow.variational_optical_flow(np.zeros((2, 8, 8)))
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, 'opticalflow_b200')
+    for fn in os.listdir(pkg):
+        if fn.endswith('.py'):
+            text = open(os.path.join(pkg, fn)).read()
+            assert 'oracle' not in text.replace('the oracle', ''), fn
