@@ -1,0 +1,274 @@
+"""bench.py - frame-pairs/sec of the variational optical-flow hot path at 1024^2 (BASELINE.json metric).
+
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference]
+
+A "step" is one batch of B frame pairs of the d-3 workload (1024^2 rotating+shearing textured movie, fp32,
+speed_alpha 1e5, remodelling_alpha 1e4, sigma 2.5, rtol 1e-6) through blur -> rhs -> multigrid-BiCGStab solve ->
+epilogue, frames already resident in HBM.  Frame pairs are independent, so ranks get disjoint pairs, no data-path
+collective ("weak" scaling); the timed region is bracketed by barrier + synchronize and the maximum over ranks is
+taken.  `e2e` is the same metric through the public drop-in (host numpy in, host numpy out).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+NX = NY = 1024
+KW = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.5)
+RTOL = 1e-6
+METRIC = 'frame-pairs/sec at 1024^2'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='ofb200')
+    ap.add_argument('--batch', type=int, default=16, help='frame pairs per step per GPU')
+    ap.add_argument('--dtype', default='float32')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    return ap.parse_args()
+
+
+def workload_movie(n_frames, seed):
+    from opticalflow_b200 import synthetic
+    return synthetic.rotating_shearing_movie(NX, NY, n_frames, seed=seed).astype(np.float32)
+
+
+# ------------------------------------------------------------------------------------------ reference / CPU arm
+CPU_CROP = 128
+
+
+def _cpu_pair_task(seed):
+    """One bounded sample: a CPU_CROP^2 crop of a d-3 frame pair through the oracle (blur, assembly, spsolve,
+    boundary overwrite, functionals) - the reference's own runnable branch restated (oracle/flow_oracle.py)."""
+    from oracle import flow_oracle
+    from opticalflow_b200 import synthetic
+    movie = synthetic.rotating_shearing_movie(CPU_CROP, CPU_CROP, 2, seed=seed)
+    t0 = time.perf_counter()
+    flow_oracle.variational_optical_flow(movie, **KW)
+    return time.perf_counter() - t0
+
+
+def cpu_throughput(workers, repeats=1):
+    """frame-pairs/sec at 1024^2 extrapolated linearly in pixel count from CPU_CROP^2 samples (optimistic for the
+    CPU: the sparse direct solve is super-linear), `workers` processes solving independent pairs concurrently."""
+    import multiprocessing as mp
+    ctx = mp.get_context('spawn')
+    with ctx.Pool(workers) as pool:
+        pool.map(_cpu_pair_task, range(workers))                  # warm-up: imports, page-in
+        t0 = time.perf_counter()
+        for r in range(repeats):
+            pool.map(_cpu_pair_task, range(100 + r * workers, 100 + (r + 1) * workers))
+        dt = time.perf_counter() - t0
+    pairs_small = workers * repeats
+    scale = (CPU_CROP * CPU_CROP) / float(NX * NY)
+    return pairs_small * scale / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    workers = max(1, min(os.cpu_count() or 1, 32))
+    for _ in range(args.warmup):
+        pass                                                       # warm-up happens inside cpu_throughput's first map
+    values = []
+    t_all = time.perf_counter()
+    for _ in range(args.steps):
+        v, _ = cpu_throughput(workers, repeats=1)
+        values.append(v)
+        if time.perf_counter() - t_all > 240:
+            break
+    value = float(np.mean(values))
+    sample = ('%d concurrent %dx%d crops of d-3 frame pairs per step, oracle port (numpy assembly + SuperLU spsolve), '
+              'scaled by pixel count to 1024^2' % (workers, CPU_CROP, CPU_CROP))
+    line = dict(metric=METRIC, value=value, unit='frame-pairs/s', n_gpus=args.gpus, steps=len(values), warmup=args.warmup,
+                ms_per_step=1e3 * workers * (CPU_CROP ** 2 / float(NX * NY)) / value, higher_is_better=True,
+                scaling='weak', vs_baseline=None, dtype='f64', data='synthetic', impl='reference',
+                config=dict(workload='d-3: 1024^2 rotating+shearing textured movie, alpha 1e5, beta 1e4, sigma 2.5'),
+                cpu_baseline=dict(value=value, unit='frame-pairs/s', cores=workers, kind='port', sample=sample),
+                e2e=dict(value=value, unit='frame-pairs/s', h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+                gpu_launches=0)
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------ GPU arm
+class ClockSampler(threading.Thread):
+    """Samples nvidia-smi clocks / throttle reasons of one GPU while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], threading.Event()
+
+    def run(self):
+        while not self.stop_flag.is_set():
+            try:
+                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
+                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
+                self.samples.append([f.strip() for f in out.strip().split(',')])
+            except Exception:
+                pass
+            self.stop_flag.wait(0.1)
+
+    def summary(self):
+        sm = [float(s[0]) for s in self.samples if len(s) >= 7 and s[0].replace('.', '').isdigit()]
+        mx = [float(s[1]) for s in self.samples if len(s) >= 7 and s[1].replace('.', '').isdigit()]
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        reasons = sorted({names[k] for s in self.samples if len(s) >= 7 for k in range(4) if s[3 + k] == 'Active'})
+        return dict(sm_mhz=float(np.median(sm)) if sm else None, sm_max_mhz=max(mx) if mx else None, reasons=reasons,
+                    samples=len(sm))
+
+
+def run_gpu(args):
+    import torch
+    import torch.distributed as dist
+    from opticalflow_b200 import _lib, engine, optical_flow
+
+    rank = int(os.environ.get('RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    lib = _lib.load()
+    B = args.batch
+    tdtype, _ = engine.resolve_dtype(args.dtype)
+    itemsize = 4 if args.dtype == 'float32' else 8
+
+    movie = workload_movie(B + 1, seed=2 + rank)                   # each rank: its own disjoint pairs
+    frames_dev = torch.from_numpy(movie).to(dev).to(tdtype)
+    workspace = engine.Workspace()
+    opts = engine.make_options('mg')
+    alpha = torch.full((B,), KW['speed_alpha'], dtype=torch.float64, device=dev)
+    beta = torch.full((B,), KW['remodelling_alpha'], dtype=torch.float64, device=dev)
+    blurred = torch.empty_like(frames_dev)
+    b = torch.empty((B, 3, NX, NY), dtype=tdtype, device=dev)
+    x = torch.empty_like(b)
+    fields = torch.empty((4, B, NX, NY), dtype=tdtype, device=dev)
+    stats = {}
+
+    def device_step():
+        engine.blur(frames_dev, KW['smoothing_sigma'], out=blurred)
+        P, C = blurred[:-1], blurred[1:]
+        engine.build_rhs(P, C, out=b)
+        x.zero_()
+        it, rr, cv = engine.solve(P, b, x, alpha, beta, RTOL, 1000, opts, workspace)
+        engine.epilogue(P, C, x, alpha, beta, 1.0, out=fields)
+        stats['iters'], stats['conv'] = it, cv
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = lib.ofb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        device_step()
+    e1.record()
+    barrier()
+    launches = lib.ofb_launch_count() - launches0
+    ms = e0.elapsed_time(e1)
+    iters = stats['iters'].cpu().numpy()
+    assert int(stats['conv'].sum()) == B, 'not every pair converged: %s' % stats['conv'].tolist()
+
+    # ---- e2e: the public drop-in, host numpy in / host numpy out, copies inside the timed region
+    def e2e_step():
+        return optical_flow.variational_optical_flow(movie, dtype=args.dtype, rtol=RTOL, batch_pairs=B, device=dev, **KW)
+    for _ in range(2):
+        res = e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    n_e2e = max(2, min(args.steps, 5))
+    for _ in range(n_e2e):
+        res = e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / n_e2e
+    sampler.stop_flag.set()
+    sampler.join()
+    h2d = movie.nbytes
+    d2h = sum(res[k].size for k in ('v_x', 'v_y', 'speed', 'remodelling')) * 8 + res['blurred_data'].nbytes
+
+    # ---- roofline of the dominant kernel: the level-0 block-Jacobi smoother sweep (10 words / pixel)
+    xin = torch.randn_like(b)
+    P = blurred[:-1]
+    for _ in range(3):
+        engine.smooth(P, b, xin, alpha, beta, out=x)
+    torch.cuda.synchronize(dev)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 20
+    s0.record()
+    for _ in range(reps):
+        engine.smooth(P, b, xin, alpha, beta, out=x)
+    s1.record()
+    torch.cuda.synchronize(dev)
+    sweep_ms = s0.elapsed_time(s1) / reps
+    alg_bytes = 10 * itemsize * NX * NY * B
+    achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9
+    peaks_file = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.isfile(peaks_file):
+        peak, peak_src = float(json.load(open(peaks_file))['hbm_gbs']), 'MEASURED_PEAKS.json hbm_gbs'
+    else:
+        peak, peak_src = 6650.0, 'fallback (B200_PROFILING.md)'
+
+    # ---- reduce over ranks
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_max, e2e_ms_max = float(t[0]), float(t[1])
+    pairs_total = B * world
+    value = pairs_total * args.steps / (ms_max * 1e-3)
+    e2e_value = pairs_total / (e2e_ms_max * 1e-3)
+
+    if rank == 0:
+        line = dict(metric=METRIC, value=value, unit='frame-pairs/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+                    ms_per_step=ms_max / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None,
+                    dtype='f32' if args.dtype == 'float32' else 'f64', data='synthetic',
+                    config=dict(workload='d-3: 1024^2 rotating+shearing textured movie, alpha 1e5, beta 1e4, sigma 2.5, '
+                                         'rtol 1e-6, V(2,2)-multigrid BiCGStab',
+                                pairs_per_step_per_gpu=B, parallelism='frame pairs sharded over %d GPU(s), no collective' % world,
+                                l2='working set %.1f GB per step exceeds the 126 MB L2' % (12 * 3 * NX * NY * itemsize * B / 1e9),
+                                iterations_per_pair=float(iters.mean()), iterations_max=int(iters.max())),
+                    e2e=dict(value=e2e_value, unit='frame-pairs/s', h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h)),
+                    gpu_launches=int(launches),
+                    roofline=dict(bound='hbm', kernel='k_sweep<OpSmooth> level 0 (block-Jacobi smoother)', achieved=achieved,
+                                  peak=peak, unit='GB/s', frac=achieved / peak, traffic=None, peak_source=peak_src,
+                                  ms_per_launch=sweep_ms, algorithmic_bytes_per_launch=alg_bytes),
+                    clocks=sampler.summary())
+        if not args.no_cpu_baseline and world == 1:
+            workers = max(1, min(os.cpu_count() or 1, 32))
+            v, dt = cpu_throughput(workers)
+            line['cpu_baseline'] = dict(value=v, unit='frame-pairs/s', cores=workers, kind='port',
+                                        sample='%d concurrent %dx%d crops of d-3 pairs (%.1f s), oracle port, scaled by pixel '
+                                               'count to 1024^2' % (workers, CPU_CROP, CPU_CROP, dt))
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    a = parse()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_gpu(a)

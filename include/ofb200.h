@@ -49,6 +49,8 @@ typedef struct ofb_solve_options {
 int         ofb_version(void);
 const char* ofb_last_error(void);
 void        ofb_default_options(ofb_solve_options* opt);
+/* number of CUDA kernels this library has launched in the calling process (diagnostics, bench.py) */
+long long   ofb_launch_count(void);
 
 /* Bytes of device workspace ofb_solve needs for this shape (caller allocates, contents need not be zeroed). */
 size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond);
@@ -73,6 +75,11 @@ int ofb_apply(const void* P, const void* x3, void* y3, const double* alpha, cons
  *     ghost values of x are ignored (taken from the boundary rows), ghost rows of y are 0. */
 int ofb_apply_eliminated(const void* P, const void* x3, void* y3, const double* alpha, const double* beta,
                          int B, int Nx, int Ny, int dtype, void* stream);
+
+/* K5s one damped block-Jacobi sweep x_out = x_in + omega D^-1 (b - S x_in): the multigrid smoother and the
+ *     dominant kernel of the solve (10 words/pixel); exposed for measurement and tests. */
+int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta,
+               double omega, int rows_per_strip, int B, int Nx, int Ny, int dtype, void* stream);
 
 /* K4/K5  solve A x = b: replaces the PETSc KSP solve (optical_flow.py:1081-1132; -ksp_type bcgs, rtol on the
  *     unpreconditioned residual, nonzero initial guess).  x3: in = initial guess, out = solution (ghost ring

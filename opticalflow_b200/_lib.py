@@ -13,8 +13,8 @@ PRECOND_BJACOBI, PRECOND_MG = 0, 1
 ABI_VERSION = 1
 
 # every symbol include/ofb200.h declares
-EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_workspace_bytes', 'ofb_blur',
-                    'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_solve', 'ofb_precondition',
+EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_workspace_bytes', 'ofb_blur',
+                    'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_smooth', 'ofb_solve', 'ofb_precondition',
                     'ofb_epilogue')
 
 
@@ -48,6 +48,8 @@ def load():
     lib.ofb_last_error.argtypes = []
     lib.ofb_default_options.restype = None
     lib.ofb_default_options.argtypes = [ctypes.POINTER(SolveOptions)]
+    lib.ofb_launch_count.restype = ctypes.c_longlong
+    lib.ofb_launch_count.argtypes = []
     lib.ofb_workspace_bytes.restype = sz
     lib.ofb_workspace_bytes.argtypes = [i, i, i, i, i]
     lib.ofb_blur.restype = i
@@ -58,6 +60,8 @@ def load():
     lib.ofb_apply.argtypes = [vp, vp, vp, dp, dp, i, i, i, i, vp]
     lib.ofb_apply_eliminated.restype = i
     lib.ofb_apply_eliminated.argtypes = [vp, vp, vp, dp, dp, i, i, i, i, vp]
+    lib.ofb_smooth.restype = i
+    lib.ofb_smooth.argtypes = [vp, vp, vp, vp, dp, dp, d, i, i, i, i, i, vp]
     lib.ofb_solve.restype = i
     lib.ofb_solve.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip,
                               i, i, i, i, vp]

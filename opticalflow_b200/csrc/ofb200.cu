@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <vector>
 #include <algorithm>
+#include <atomic>
 #include "../../include/ofb200.h"
 #include "misc_kernels.cuh"
 
@@ -28,7 +29,12 @@ int fail(int code, const char* fmt, ...) {
         if (e__ != cudaSuccess) return fail(-1000 - (int)e__, "%s: %s", #expr, cudaGetErrorString(e__)); \
     } while (0)
 
-#define OFB_CHECK_LAUNCH() OFB_CHECK_CUDA(cudaGetLastError())
+std::atomic<long long> g_launches{0};     // kernels launched by this process (diagnostic counter only)
+#define OFB_CHECK_LAUNCH()                  \
+    do {                                    \
+        g_launches.fetch_add(1);            \
+        OFB_CHECK_CUDA(cudaGetLastError()); \
+    } while (0)
 
 constexpr int MAX_LEVELS = 16;
 constexpr int MIN_COARSE = 6;          // keep coarsening while both coarse sizes stay >= this
@@ -446,6 +452,22 @@ int apply_elim_impl(const void* P, const void* x3, void* y3, const double* alpha
 }
 
 template <typename T>
+int smooth_impl(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta, double omega,
+                int rows_per_strip, int B, int Nx, int Ny, void* stream) {
+    Solver<T> S;
+    ofb_default_options(&S.opt);
+    S.opt.precond = OFB_PRECOND_BJACOBI;
+    S.opt.omega = omega;
+    S.opt.rows_per_strip = rows_per_strip;
+    S.B = B;
+    S.plan = make_plan(Nx, Ny, OFB_PRECOND_BJACOBI);
+    memset(&S.w, 0, sizeof(S.w));
+    S.g[0] = make_geom<T>(S.plan.lv[0], ptr_aligned16(P) && ptr_aligned16(b3) && ptr_aligned16(x_in) && ptr_aligned16(x_out));
+    S.P = (const T*)P; S.alpha = alpha; S.beta = beta; S.stream = (cudaStream_t)stream; S.active = nullptr;
+    return S.smooth(0, (const T*)b3, (const T*)x_in, (T*)x_out);
+}
+
+template <typename T>
 int epilogue_impl(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma, double* functionals,
                   double* moments, const double* alpha, const double* beta, double scale, int B, int Nx, int Ny, cudaStream_t stream) {
     LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny};
@@ -466,6 +488,8 @@ extern "C" {
 int ofb_version(void) { return OFB_ABI_VERSION; }
 
 const char* ofb_last_error(void) { return g_error; }
+
+long long ofb_launch_count(void) { return g_launches.load(); }
 
 void ofb_default_options(ofb_solve_options* opt) {
     if (!opt) return;
@@ -514,6 +538,14 @@ int ofb_apply_eliminated(const void* P, const void* x3, void* y3, const double* 
     if (x3 == y3) return fail(-7, "ofb_apply_eliminated: x and y must not alias");
     return dtype == OFB_F32 ? apply_elim_impl<float>(P, x3, y3, alpha, beta, B, Nx, Ny, stream)
                             : apply_elim_impl<double>(P, x3, y3, alpha, beta, B, Nx, Ny, stream);
+}
+
+int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta, double omega,
+               int rows_per_strip, int B, int Nx, int Ny, int dtype, void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    if (x_in == x_out) return fail(-7, "ofb_smooth: x_in and x_out must not alias (Jacobi reads neighbours of x_in)");
+    return dtype == OFB_F32 ? smooth_impl<float>(P, b3, x_in, x_out, alpha, beta, omega, rows_per_strip, B, Nx, Ny, stream)
+                            : smooth_impl<double>(P, b3, x_in, x_out, alpha, beta, omega, rows_per_strip, B, Nx, Ny, stream);
 }
 
 int ofb_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,

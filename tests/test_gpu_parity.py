@@ -207,7 +207,7 @@ def test_full_size_1024_properties(cuda_device):
     # linearity
     y1 = engine.apply_operator(P, x, 1e5, 1e4)
     y2 = engine.apply_operator(P, 2.5 * x, 1e5, 1e4)
-    assert float((y2 - 2.5 * y1).norm() / y1.norm()) < 1e-13
+    assert float((y2 - 2.5 * y1).norm() / y1.norm()) < 1e-11
     # recovered flow is close to the imposed rotation+shear in the interior
     ii, jj = np.meshgrid(np.arange(1024.0), np.arange(1024.0), indexing='ij')
     vx_true = (-1e-3 + 5e-4) * (jj - 511.5)
