@@ -33,6 +33,8 @@ extern "C" {
 #define OFB_PRECOND_BJACOBI 0   /* pointwise 3x3 block-Jacobi */
 #define OFB_PRECOND_MG      1   /* geometric multigrid V-cycle, block-Jacobi smoother, dense coarsest solve */
 
+#define OFB_FLAG_NO_STREAM 1    /* use the register-only sweep on every level (A/B measurements) */
+
 #define OFB_ABI_VERSION 1
 
 typedef struct ofb_solve_options {
@@ -43,7 +45,7 @@ typedef struct ofb_solve_options {
     int    check_every;    /* convergence poll period in iterations (host sync); default 1 */
     int    rows_per_strip; /* 0 = choose from the batch size */
     int    coarse_sweeps;  /* Jacobi sweeps on the coarsest level when it is too large for the dense solve; default 30 */
-    int    reserved;
+    int    flags;          /* OFB_FLAG_* bits; default 0 */
 } ofb_solve_options;
 
 int         ofb_version(void);
@@ -77,9 +79,10 @@ int ofb_apply_eliminated(const void* P, const void* x3, void* y3, const double* 
                          int B, int Nx, int Ny, int dtype, void* stream);
 
 /* K5s one damped block-Jacobi sweep x_out = x_in + omega D^-1 (b - S x_in): the multigrid smoother and the
- *     dominant kernel of the solve (10 words/pixel); exposed for measurement and tests. */
+ *     dominant kernel of the solve (10 words/pixel); exposed for measurement and tests.  omega, rows_per_strip
+ *     and flags are taken from `opt` (NULL = defaults). */
 int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta,
-               double omega, int rows_per_strip, int B, int Nx, int Ny, int dtype, void* stream);
+               const ofb_solve_options* opt, int B, int Nx, int Ny, int dtype, void* stream);
 
 /* K4/K5  solve A x = b: replaces the PETSc KSP solve (optical_flow.py:1081-1132; -ksp_type bcgs, rtol on the
  *     unpreconditioned residual, nonzero initial guess).  x3: in = initial guess, out = solution (ghost ring

@@ -10,6 +10,7 @@ LIBRARY_PATH = os.path.join(_HERE, 'libofb200.so')
 
 OFB_F32, OFB_F64 = 0, 1
 PRECOND_BJACOBI, PRECOND_MG = 0, 1
+FLAG_NO_STREAM = 1
 ABI_VERSION = 1
 
 # every symbol include/ofb200.h declares
@@ -21,7 +22,7 @@ EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb
 class SolveOptions(ctypes.Structure):
     _fields_ = [('precond', ctypes.c_int), ('nu_pre', ctypes.c_int), ('nu_post', ctypes.c_int),
                 ('omega', ctypes.c_double), ('check_every', ctypes.c_int), ('rows_per_strip', ctypes.c_int),
-                ('coarse_sweeps', ctypes.c_int), ('reserved', ctypes.c_int)]
+                ('coarse_sweeps', ctypes.c_int), ('flags', ctypes.c_int)]
 
 
 class OfbError(RuntimeError):
@@ -61,7 +62,7 @@ def load():
     lib.ofb_apply_eliminated.restype = i
     lib.ofb_apply_eliminated.argtypes = [vp, vp, vp, dp, dp, i, i, i, i, vp]
     lib.ofb_smooth.restype = i
-    lib.ofb_smooth.argtypes = [vp, vp, vp, vp, dp, dp, d, i, i, i, i, i, vp]
+    lib.ofb_smooth.argtypes = [vp, vp, vp, vp, dp, dp, ctypes.POINTER(SolveOptions), i, i, i, i, vp]
     lib.ofb_solve.restype = i
     lib.ofb_solve.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip,
                               i, i, i, i, vp]

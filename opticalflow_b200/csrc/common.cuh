@@ -80,39 +80,66 @@ __device__ __forceinline__ void store_own(T* __restrict__ rowptr, int j0, int Ny
     }
 }
 
-// Load row i of a plane with halos. `edge_warp` is warp-uniform: true when the warp's column range
+// Load one row with halos from `rowptr` (rowptr[j] = column j; global memory or a shared-memory row
+// staged by the streamed sweeps).  `edge_warp` is warp-uniform: true when the warp's column range
 // (with halo) touches column 0 or Ny-1, the only place the ghost remap costs anything.
-template <typename T, int MODE>
-__device__ __forceinline__ void load_row(Row<T>& r, const T* __restrict__ plane, int i, int j0,
-                                         const Geom& g, int lane, bool edge_warp) {
+// FULLVEC: the row is 16-byte aligned and readable past Ny (zero-filled staging) - always one vector load.
+template <typename T, int MODE, bool FULLVEC>
+__device__ __forceinline__ void load_row_ptr(Row<T>& r, const T* __restrict__ rowptr, bool ghost_row, int j0,
+                                             const Geom& g, int lane, bool edge_warp) {
     constexpr int V = VecOf<T>::V;
-    int row = i;
-    if (MODE != LOAD_RAW) row = mirror_index(i, g.Nx);
-    row = min(max(row, 0), g.Nx - 1);
-    const T* rowptr = plane + (long long)row * g.pitch;
     T own[V];
-    load_own<T>(rowptr, j0, g.Ny, g.aligned != 0, own);
+    if (FULLVEC) {
+        typename VecOf<T>::type t = *reinterpret_cast<const typename VecOf<T>::type*>(rowptr + j0);
+        const T* p = reinterpret_cast<const T*>(&t);
+#pragma unroll
+        for (int k = 0; k < V; ++k) own[k] = p[k];
+    } else {
+        load_own<T>(rowptr, j0, g.Ny, g.aligned != 0, own);
+    }
 #pragma unroll
     for (int k = 0; k < V; ++k) r.v[k + 1] = own[k];
-    T left = __shfl_up_sync(FULL, own[V - 1], 1);
-    T right = __shfl_down_sync(FULL, own[0], 1);
-    if (lane == 0) left = (j0 > 0) ? rowptr[j0 - 1] : T(0);
-    if (lane == WARP - 1) right = (j0 + V < g.Ny) ? rowptr[j0 + V] : T(0);
-    r.v[0] = left;
-    r.v[V + 1] = right;
+    if (FULLVEC) {
+        // staged row: the halo columns are in shared memory next to the own vector
+        r.v[0] = rowptr[j0 - 1];
+        r.v[V + 1] = rowptr[j0 + V];
+    } else {
+        T left = __shfl_up_sync(FULL, own[V - 1], 1);
+        T right = __shfl_down_sync(FULL, own[0], 1);
+        if (lane == 0) left = (j0 > 0) ? rowptr[j0 - 1] : T(0);
+        if (lane == WARP - 1) right = (j0 + V < g.Ny) ? rowptr[j0 + V] : T(0);
+        r.v[0] = left;
+        r.v[V + 1] = right;
+    }
     if (MODE != LOAD_RAW && edge_warp) {
-        const bool ghost_row = (i == 0) || (i == g.Nx - 1);
+        if (g.Ny % V == 0) {
+            // ghost columns 0 and Ny-1 are the first / last own column of a lane; their mirror columns
+            // 2 and Ny-3 are already in the lane's window
+            if (j0 == 0) r.v[1] = (MODE == LOAD_SOL && ghost_row) ? r.v[3] + r.v[3] : r.v[3];
+            if (j0 + V == g.Ny) r.v[V] = (MODE == LOAD_SOL && ghost_row) ? r.v[V - 2] + r.v[V - 2] : r.v[V - 2];
+        } else {
 #pragma unroll
-        for (int k = 0; k < V + 2; ++k) {
-            int j = j0 - 1 + k;
-            bool ghost_col = (j == 0) || (j == g.Ny - 1);
-            if (ghost_col) {
-                T t = rowptr[mirror_index(j, g.Ny)];
-                if (MODE == LOAD_SOL && ghost_row) t = t + t;
-                r.v[k] = t;
+            for (int k = 0; k < V + 2; ++k) {
+                int j = j0 - 1 + k;
+                bool ghost_col = (j == 0) || (j == g.Ny - 1);
+                if (ghost_col) {
+                    T t = rowptr[mirror_index(j, g.Ny)];
+                    if (MODE == LOAD_SOL && ghost_row) t = t + t;
+                    r.v[k] = t;
+                }
             }
         }
     }
+}
+
+// Load row i of a plane in global memory with halos.
+template <typename T, int MODE>
+__device__ __forceinline__ void load_row(Row<T>& r, const T* __restrict__ plane, int i, int j0,
+                                         const Geom& g, int lane, bool edge_warp) {
+    int row = i;
+    if (MODE != LOAD_RAW) row = mirror_index(i, g.Nx);
+    row = min(max(row, 0), g.Nx - 1);
+    load_row_ptr<T, MODE, false>(r, plane + (long long)row * g.pitch, (i == 0) || (i == g.Nx - 1), j0, g, lane, edge_warp);
 }
 
 // ---------------------------------------------------------------- reductions

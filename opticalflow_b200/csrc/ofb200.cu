@@ -8,6 +8,7 @@
 #include <atomic>
 #include "../../include/ofb200.h"
 #include "misc_kernels.cuh"
+#include "stream_sweep.cuh"
 
 using namespace ofb;
 
@@ -41,6 +42,57 @@ constexpr int MIN_COARSE = 6;          // keep coarsening while both coarse size
 constexpr int MAX_DENSE_N = 768;       // largest coarsest system solved with the dense inverse
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+
+constexpr int MAX_DEVICES = 64;
+
+struct DeviceInfo { int sms; };
+inline int device_sms() {
+    static int sms[MAX_DEVICES] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+    if (sms[dev] == 0) {
+        int v = 0;
+        cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev);
+        sms[dev] = v > 0 ? v : 148;
+    }
+    return sms[dev];
+}
+
+// Streamed (TMA bulk copy + mbarrier ring) sweep: persistent grid of (CTAs per SM) x SMs.
+template <typename T, bool FROM_IMAGE, typename Op>
+int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_strip, cudaStream_t stream) {
+    using C = StreamCfg<T>;
+    using Lay = StreamLayout<T, FROM_IMAGE, Op>;
+    auto kern = k_stream<T, FROM_IMAGE, Op>;
+    static int ctas_per_sm[MAX_DEVICES] = {0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+    if (ctas_per_sm[dev] == 0) {
+        OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Lay::SMEM_BYTES));
+        int nb = 0;
+        OFB_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, C::THREADS, Lay::SMEM_BYTES));
+        if (nb < 1) return fail(-9, "streamed sweep does not fit on an SM (%zu bytes of shared memory)", (size_t)Lay::SMEM_BYTES);
+        ctas_per_sm[dev] = nb;
+    }
+    const int slots = device_sms() * ctas_per_sm[dev];
+    L.tiles_x = (L.g.Ny + C::TW - 1) / C::TW;
+    int R = rows_per_strip;
+    if (R <= 0) {
+        const long long total_rows = (long long)L.g.Nx * L.tiles_x * B;
+        R = (int)std::min<long long>(64, std::max<long long>(16, (total_rows + 4LL * slots - 1) / (4LL * slots)));
+    }
+    L.rows_per_strip = R;
+    L.strips = (L.g.Nx + R - 1) / R;
+    const long long n_items = (long long)L.tiles_x * L.strips * B;
+    if (n_items > 0x7fffffffLL) return fail(-10, "too many work items");
+    const int grid = (int)std::min<long long>(n_items, slots);
+    kern<<<grid, C::THREADS, Lay::SMEM_BYTES, stream>>>(L, x, op, (int)n_items);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
 
 struct LevelPlan {
     int Nx, Ny, pitch;
@@ -166,17 +218,27 @@ template <typename T> struct Solver {
         L.tiles_x = (g[l].Ny + WARP * V - 1) / (WARP * V);
         int R = opt.rows_per_strip;
         if (R <= 0) {
-            const long long target_warps = 148LL * 16;
+            // one wave of warps when the level is small (latency bound: short strips = more rows in flight),
+            // longer strips (fewer halo rows re-read) once the level fills the machine several times over
+            const long long target_warps = (long long)device_sms() * 16;
             const long long total_rows = (long long)g[l].Nx * L.tiles_x * B;
-            R = (int)std::min<long long>(32, std::max<long long>(8, (total_rows + target_warps - 1) / target_warps));
+            R = (int)std::min<long long>(32, std::max<long long>(1, total_rows / target_warps));
         }
         L.rows_per_strip = R;
         L.strips = (g[l].Nx + R - 1) / R;
         return L;
     }
 
+    // streamed sweep for levels wide enough to fill a tile, 16-byte aligned rows required
+    bool use_stream(int l) const {
+        return (opt.flags & OFB_FLAG_NO_STREAM) == 0 && g[l].aligned != 0 && g[l].Ny >= 2 * WARP * VecOf<T>::V;
+    }
     template <typename Op> int sweep(int l, const T* x, Op op) {
         const LevelArgs<T> L = level_args(l);
+        if (use_stream(l)) {
+            if (l == 0) return launch_stream<T, true, Op>(L, x, op, B, opt.rows_per_strip, stream);
+            return launch_stream<T, false, Op>(L, x, op, B, opt.rows_per_strip, stream);
+        }
         const int warps_per_block = 4;
         const int items = L.tiles_x * L.strips;
         dim3 grid((items + warps_per_block - 1) / warps_per_block, B);
@@ -187,15 +249,15 @@ template <typename T> struct Solver {
     }
 
     int smooth(int l, const T* b, const T* xin, T* xout) {
-        OpSmooth<T> op; op.g = g[l]; op.b = b; op.xo = xout; op.w = T(opt.omega);
+        OpSmooth<T> op; op.g = g[l]; op.cen[0] = b; op.xo = xout; op.w = T(opt.omega);
         return sweep(l, xin, op);
     }
     int residual(int l, const T* b, const T* x, T* r) {
-        OpResidual<T, false> op; op.g = g[l]; op.b = b; op.r = r; op.r2 = nullptr; op.st = w.st; op.acc[0] = 0.0;
+        OpResidual<T, false> op; op.g = g[l]; op.cen[0] = b; op.r = r; op.r2 = nullptr; op.st = w.st; op.acc[0] = 0.0;
         return sweep(l, x, op);
     }
     int jacobi_zero(int l, const T* b, T* z, double wj) {
-        OpDirJacobi<T, 2> op; op.g = g[l]; op.r = nullptr; op.d = const_cast<T*>(b); op.v = nullptr; op.z = z; op.w = T(wj); op.st = w.st;
+        OpDirJacobi<T, 2> op; op.g = g[l]; op.cen[0] = b; op.d = nullptr; op.z = z; op.w = T(wj); op.st = w.st;
         return sweep(l, nullptr, op);
     }
 
@@ -322,7 +384,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     if (S.opt.precond == OFB_PRECOND_MG && S.plan.nlevels > 1) { if ((rc = S.build_hierarchy())) return rc; }
 
     {   // r = b - S x0, rhat = r, acc[2] = acc[3] = r.r
-        OpResidual<T, true> op; op.g = g0; op.b = b; op.r = w.r; op.r2 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
+        OpResidual<T, true> op; op.g = g0; op.cen[0] = b; op.r = w.r; op.r2 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
         if ((rc = S.sweep(0, x, op))) return rc;
     }
     k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 0, rtol, max_it, nullptr);
@@ -336,23 +398,23 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     for (int it = 0; it < max_it; ++it) {
         T *ph = nullptr, *sh = nullptr;
         {   // p = r + beta_k (p - omega v) ; z = w D^-1 p
-            OpDirJacobi<T, 0> op; op.g = g0; op.r = w.r; op.d = w.p; op.v = w.v; op.z = ph_first; op.w = wj; op.st = w.st;
+            OpDirJacobi<T, 0> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.cen[2] = w.p; op.d = w.p; op.z = ph_first; op.w = wj; op.st = w.st;
             if ((rc = S.sweep(0, nullptr, op))) return rc;
         }
         if ((rc = S.finish_precondition(w.p, ph_first, S.partner_of(ph_first, w.ph), &ph))) return rc;
         {   // v = S ph ; acc[0] = rhat.v
-            OpApplyDot<T, 1> op; op.g = g0; op.y = w.v; op.w1 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
+            OpApplyDot<T, 1> op; op.g = g0; op.y = w.v; op.cen[0] = w.rhat; op.st = w.st; op.acc[0] = 0.0;
             if ((rc = S.sweep(0, ph, op))) return rc;
         }
         k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 1, rtol, max_it, nullptr);
         OFB_CHECK_LAUNCH();
         {   // s = r - alpha v ; z = w D^-1 s
-            OpDirJacobi<T, 1> op; op.g = g0; op.r = w.r; op.d = w.s; op.v = w.v; op.z = sh_first; op.w = wj; op.st = w.st;
+            OpDirJacobi<T, 1> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.d = w.s; op.z = sh_first; op.w = wj; op.st = w.st;
             if ((rc = S.sweep(0, nullptr, op))) return rc;
         }
         if ((rc = S.finish_precondition(w.s, sh_first, S.partner_of(sh_first, w.sh), &sh))) return rc;
         {   // t = S sh ; acc[0] = t.s, acc[1] = t.t
-            OpApplyDot<T, 2> op; op.g = g0; op.y = w.t; op.w1 = w.s; op.st = w.st; op.acc[0] = op.acc[1] = 0.0;
+            OpApplyDot<T, 2> op; op.g = g0; op.y = w.t; op.cen[0] = w.s; op.st = w.st; op.acc[0] = op.acc[1] = 0.0;
             if ((rc = S.sweep(0, sh, op))) return rc;
         }
         k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 2, rtol, max_it, nullptr);
@@ -447,18 +509,16 @@ int apply_elim_impl(const void* P, const void* x3, void* y3, const double* alpha
     memset(&S.w, 0, sizeof(S.w));
     S.g[0] = make_geom<T>(S.plan.lv[0], ptr_aligned16(P) && ptr_aligned16(x3) && ptr_aligned16(y3));
     S.P = (const T*)P; S.alpha = alpha; S.beta = beta; S.stream = (cudaStream_t)stream; S.active = nullptr;
-    OpApply<T> op; op.g = S.g[0]; op.y = (T*)y3;
+    OpApply<T> op; op.g = S.g[0]; op.y = (T*)y3; op.cen[0] = nullptr;
     return S.sweep(0, (const T*)x3, op);
 }
 
 template <typename T>
-int smooth_impl(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta, double omega,
-                int rows_per_strip, int B, int Nx, int Ny, void* stream) {
+int smooth_impl(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta,
+                const ofb_solve_options* opt, int B, int Nx, int Ny, void* stream) {
     Solver<T> S;
-    ofb_default_options(&S.opt);
+    if (opt) S.opt = *opt; else ofb_default_options(&S.opt);
     S.opt.precond = OFB_PRECOND_BJACOBI;
-    S.opt.omega = omega;
-    S.opt.rows_per_strip = rows_per_strip;
     S.B = B;
     S.plan = make_plan(Nx, Ny, OFB_PRECOND_BJACOBI);
     memset(&S.w, 0, sizeof(S.w));
@@ -500,7 +560,7 @@ void ofb_default_options(ofb_solve_options* opt) {
     opt->check_every = 1;
     opt->rows_per_strip = 0;
     opt->coarse_sweeps = 30;
-    opt->reserved = 0;
+    opt->flags = 0;
 }
 
 size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond) {
@@ -540,12 +600,12 @@ int ofb_apply_eliminated(const void* P, const void* x3, void* y3, const double* 
                             : apply_elim_impl<double>(P, x3, y3, alpha, beta, B, Nx, Ny, stream);
 }
 
-int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta, double omega,
-               int rows_per_strip, int B, int Nx, int Ny, int dtype, void* stream) {
+int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta,
+               const ofb_solve_options* opt, int B, int Nx, int Ny, int dtype, void* stream) {
     if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
     if (x_in == x_out) return fail(-7, "ofb_smooth: x_in and x_out must not alias (Jacobi reads neighbours of x_in)");
-    return dtype == OFB_F32 ? smooth_impl<float>(P, b3, x_in, x_out, alpha, beta, omega, rows_per_strip, B, Nx, Ny, stream)
-                            : smooth_impl<double>(P, b3, x_in, x_out, alpha, beta, omega, rows_per_strip, B, Nx, Ny, stream);
+    return dtype == OFB_F32 ? smooth_impl<float>(P, b3, x_in, x_out, alpha, beta, opt, B, Nx, Ny, stream)
+                            : smooth_impl<double>(P, b3, x_in, x_out, alpha, beta, opt, B, Nx, Ny, stream);
 }
 
 int ofb_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,

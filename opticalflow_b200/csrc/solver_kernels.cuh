@@ -18,19 +18,33 @@ struct PairState {
 enum Status { ST_RUNNING = 0, ST_CONVERGED = 1, ST_MAXIT = 2, ST_BREAKDOWN = 3 };
 
 // ------------------------------------------------------------------ sweep ops
+// warp-level flush of NACC fp64 accumulators: shuffle reduce, one atomicAdd per accumulator per warp, reset
+template <int NACC>
+__device__ __forceinline__ void warp_flush(double (&acc)[NACC], double* __restrict__ dst) {
+#pragma unroll
+    for (int a = 0; a < NACC; ++a) {
+        const double v = warp_sum(acc[a]);
+        if ((threadIdx.x & 31) == 0 && v != 0.0) atomicAdd(dst + a, v);
+        acc[a] = 0.0;
+    }
+}
+
 // x_out = x + w D^-1 (b - S x)
 template <typename T> struct OpSmooth {
     static constexpr bool NEED_X = true;
+    static constexpr int NCEN = 1;
     static constexpr int V = VecOf<T>::V;
-    Geom g; const T* b; T* xo; T w;
+    Geom g; const T* cen[1]; T* xo; T w;      // cen[0] = b
+    template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
-                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
-        T bb[3][V], out[3][V];
-        load3<T>(b, g, pair, i, j0, bb);
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
+        T out[3][V], b0[V], b1[V], b2[V];
+        cv.get(0, 0, b0); cv.get(0, 1, b1); cv.get(0, 2, b2);
+        const T inv_d2 = precond_rcp(T(-1) - T(4) * be);
 #pragma unroll
         for (int k = 0; k < V; ++k) {
             T z0, z1, z2;
-            block_solve<T>(cf[k], a, be, bb[0][k] - sx[0][k], bb[1][k] - sx[1][k], bb[2][k] - sx[2][k], z0, z1, z2);
+            block_solve<T>(cf[k], a, inv_d2, b0[k] - sx[0][k], b1[k] - sx[1][k], b2[k] - sx[2][k], z0, z1, z2);
             out[0][k] = inside[k] ? xc[0][k] + w * z0 : T(0);
             out[1][k] = inside[k] ? xc[1][k] + w * z1 : T(0);
             out[2][k] = inside[k] ? xc[2][k] + w * z2 : T(0);
@@ -38,24 +52,29 @@ template <typename T> struct OpSmooth {
         store3<T>(xo, g, pair, i, j0, out);
     }
     __device__ __forceinline__ void finish(int, bool) {}
+    __device__ __forceinline__ void flush(int) {}
 };
 
-// r = b - S x ; optional copy to r2 and dots acc[2] += r.r, acc[3] += r.r (initial residual: rhat = r)
+// r = b - S x ; INIT: also copy to r2 and dots acc[2] += r.r, acc[3] += r.r (initial residual: rhat = r)
 template <typename T, bool INIT> struct OpResidual {
     static constexpr bool NEED_X = true;
+    static constexpr int NCEN = 1;
     static constexpr int V = VecOf<T>::V;
-    Geom g; const T* b; T* r; T* r2; PairState* st; double acc[1];
+    Geom g; const T* cen[1]; T* r; T* r2; PairState* st; double acc[1];      // cen[0] = b
+    template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
-                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
-        T bb[3][V], out[3][V];
-        load3<T>(b, g, pair, i, j0, bb);
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
+        T out[3][V];
 #pragma unroll
-        for (int q = 0; q < 3; ++q)
+        for (int q = 0; q < 3; ++q) {
+            T bq[V];
+            cv.get(0, q, bq);
 #pragma unroll
             for (int k = 0; k < V; ++k) {
-                out[q][k] = inside[k] ? bb[q][k] - sx[q][k] : T(0);
+                out[q][k] = inside[k] ? bq[k] - sx[q][k] : T(0);
                 if (INIT) acc[0] += (double)out[q][k] * (double)out[q][k];
             }
+        }
         store3<T>(r, g, pair, i, j0, out);
         if (INIT) store3<T>(r2, g, pair, i, j0, out);
     }
@@ -65,37 +84,51 @@ template <typename T, bool INIT> struct OpResidual {
             block_accumulate<2>(a2, st[pair].acc + 2);
         }
     }
+    __device__ __forceinline__ void flush(int pair) {
+        if (INIT) {
+            double a2[2] = {acc[0], acc[0]};
+            warp_flush<2>(a2, st[pair].acc + 2);
+            acc[0] = 0.0;
+        }
+    }
 };
 
 // y = S x with fused dots.  NDOT == 1: acc[0] += w1.y ;  NDOT == 2: acc[0] += y.w1, acc[1] += y.y
 template <typename T, int NDOT> struct OpApplyDot {
     static constexpr bool NEED_X = true;
+    static constexpr int NCEN = 1;
     static constexpr int V = VecOf<T>::V;
-    Geom g; T* y; const T* w1; PairState* st; double acc[NDOT];
+    Geom g; T* y; const T* cen[1]; PairState* st; double acc[NDOT];          // cen[0] = w1
+    template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
-                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
-        T ww[3][V], out[3][V];
-        load3<T>(w1, g, pair, i, j0, ww);
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
+        T out[3][V];
 #pragma unroll
-        for (int q = 0; q < 3; ++q)
+        for (int q = 0; q < 3; ++q) {
+            T wq[V];
+            cv.get(0, q, wq);
 #pragma unroll
             for (int k = 0; k < V; ++k) {
                 out[q][k] = inside[k] ? sx[q][k] : T(0);
-                acc[0] += (double)out[q][k] * (double)ww[q][k];
+                acc[0] += (double)out[q][k] * (double)wq[k];
                 if (NDOT == 2) acc[1] += (double)out[q][k] * (double)out[q][k];
             }
+        }
         store3<T>(y, g, pair, i, j0, out);
     }
     __device__ __forceinline__ void finish(int pair, bool) { block_accumulate<NDOT>(acc, st[pair].acc); }
+    __device__ __forceinline__ void flush(int pair) { warp_flush<NDOT>(acc, st[pair].acc); }
 };
 
 // y = S x, nothing else (C-ABI operator apply in eliminated form, MG residual checks)
 template <typename T> struct OpApply {
     static constexpr bool NEED_X = true;
+    static constexpr int NCEN = 0;
     static constexpr int V = VecOf<T>::V;
-    Geom g; T* y;
+    Geom g; T* y; const T* cen[1];
+    template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
-                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
         T out[3][V];
 #pragma unroll
         for (int q = 0; q < 3; ++q)
@@ -104,47 +137,50 @@ template <typename T> struct OpApply {
         store3<T>(y, g, pair, i, j0, out);
     }
     __device__ __forceinline__ void finish(int, bool) {}
+    __device__ __forceinline__ void flush(int) {}
 };
 
 // Pointwise ops (no solution window): direction update fused with the first Jacobi sweep of the
 // preconditioner (zero initial guess: z = w D^-1 d).
-//   KIND 0:  d = p <- r + beta_k (p - omega v)          (BiCGStab direction)
-//   KIND 1:  d = s <- r - alpha v                        (BiCGStab half step)
-//   KIND 2:  d = b (read only)                           (first sweep on a coarse level)
+//   KIND 0:  d = p <- r + beta_k (p - omega v)          (BiCGStab direction)     cen = {r, v, p}
+//   KIND 1:  d = s <- r - alpha v                        (BiCGStab half step)     cen = {r, v}
+//   KIND 2:  d = b (read only)                           (first sweep on a coarse level)  cen = {b}
 template <typename T, int KIND> struct OpDirJacobi {
     static constexpr bool NEED_X = false;
+    static constexpr int NCEN = KIND == 0 ? 3 : (KIND == 1 ? 2 : 1);
     static constexpr int V = VecOf<T>::V;
-    Geom g; const T* r; T* d; const T* v; T* z; T w; const PairState* st;
+    Geom g; const T* cen[NCEN]; T* d; T* z; T w; const PairState* st;
+    template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
-                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be) {
+                                        const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
         T dd[3][V], zz[3][V];
         if (KIND == 2) {
-            load3<T>(d, g, pair, i, j0, dd);
+#pragma unroll
+            for (int q = 0; q < 3; ++q) cv.get(0, q, dd[q]);
         } else {
-            T rr[3][V], vv[3][V];
-            load3<T>(r, g, pair, i, j0, rr);
-            load3<T>(v, g, pair, i, j0, vv);
-            if (KIND == 0) {
-                const T bk = T(st[pair].beta_k), om = T(st[pair].omega);
-                T pp[3][V];
-                load3<T>(d, g, pair, i, j0, pp);
+            const T bk = T(st[pair].beta_k), om = T(st[pair].omega), al = T(st[pair].alpha);
 #pragma unroll
-                for (int q = 0; q < 3; ++q)
+            for (int q = 0; q < 3; ++q) {
+                T rr[V], vv[V];
+                cv.get(0, q, rr);
+                cv.get(1, q, vv);
+                if (KIND == 0) {
+                    T pp[V];
+                    cv.get(NCEN - 1, q, pp);
 #pragma unroll
-                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[q][k] + bk * (pp[q][k] - om * vv[q][k]) : T(0);
-            } else {
-                const T al = T(st[pair].alpha);
+                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[k] + bk * (pp[k] - om * vv[k]) : T(0);
+                } else {
 #pragma unroll
-                for (int q = 0; q < 3; ++q)
-#pragma unroll
-                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[q][k] - al * vv[q][k] : T(0);
+                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[k] - al * vv[k] : T(0);
+                }
             }
             store3<T>(d, g, pair, i, j0, dd);
         }
+        const T inv_d2 = precond_rcp(T(-1) - T(4) * be);
 #pragma unroll
         for (int k = 0; k < V; ++k) {
             T z0, z1, z2;
-            block_solve<T>(cf[k], a, be, dd[0][k], dd[1][k], dd[2][k], z0, z1, z2);
+            block_solve<T>(cf[k], a, inv_d2, dd[0][k], dd[1][k], dd[2][k], z0, z1, z2);
             zz[0][k] = inside[k] ? w * z0 : T(0);
             zz[1][k] = inside[k] ? w * z1 : T(0);
             zz[2][k] = inside[k] ? w * z2 : T(0);
@@ -152,6 +188,7 @@ template <typename T, int KIND> struct OpDirJacobi {
         store3<T>(z, g, pair, i, j0, zz);
     }
     __device__ __forceinline__ void finish(int, bool) {}
+    __device__ __forceinline__ void flush(int) {}
 };
 
 template <typename T, bool FROM_IMAGE, typename Op>

@@ -1,0 +1,207 @@
+// ofb200 - streamed stencil sweep: the large-level variant of the row-marching sweep (sweep.cuh).
+//
+// One CTA = 4 consumer warps + 1 producer warp, persistent over work items (column tile x row strip x pair).
+// The producer warp streams every input row of the item (solution planes, image or coefficient planes,
+// centre-only vectors) global -> shared with 1-D bulk copies (cp.async.bulk, TMA unit; SASS UBLKCP) into a
+// STAGES-deep ring; completion is signalled on a "full" mbarrier by transaction bytes.  Consumer warps pull a
+// staged row into their rolling 3-row register window, release the stage on an "empty" mbarrier, and compute.
+// The copy engine therefore runs several rows ahead of the arithmetic independent of register pressure,
+// which is what the register-only sweep could not do (16 warps/SM x 7 loads in flight: latency bound).
+// The ring continues across work items, so there is no pipeline drain between items.
+//
+// Requirements (checked on the host, otherwise the register sweep is used): 16-byte aligned plane bases,
+// pitch % V == 0.
+#pragma once
+#include <type_traits>
+#include "pipeline.cuh"
+#include "solver_kernels.cuh"
+
+namespace ofb {
+
+template <typename T> struct StreamCfg {
+    static constexpr int V = VecOf<T>::V;
+    static constexpr int CW = 4;                         // consumer warps per CTA
+    static constexpr int TW = CW * WARP * V;             // columns per tile: 512 (f32) / 256 (f64)
+    static constexpr int HALO = 16 / (int)sizeof(T);     // 16-byte aligned column halo
+    static constexpr int ROW = TW + 2 * HALO;            // elements per staged row (2080 bytes)
+    static constexpr int STAGES = 4;
+    static constexpr int THREADS = (CW + 1) * WARP;
+};
+
+template <typename T, bool FROM_IMAGE, typename Op> struct StreamLayout {
+    using C = StreamCfg<T>;
+    static constexpr int NWIN = (Op::NEED_X ? 3 : 0) + (FROM_IMAGE ? 1 : 0);      // rows staged one row ahead
+    static constexpr int NCENROWS = 3 * Op::NCEN + (FROM_IMAGE ? 0 : NCOEF);      // rows staged at the centre row
+    static constexpr int NROWS = NWIN + NCENROWS;
+    static_assert(NROWS <= WARP, "one producer lane per staged row");
+    static constexpr int STAGE_ELEMS = NROWS * C::ROW;
+    static constexpr size_t RING_BYTES = (size_t)C::STAGES * STAGE_ELEMS * sizeof(T);
+    static constexpr size_t SMEM_BYTES = RING_BYTES + 2 * C::STAGES * sizeof(uint64_t);
+};
+
+template <int N> using IC = std::integral_constant<int, N>;
+
+template <typename T, bool FROM_IMAGE, typename Op>
+__global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T> L, const T* __restrict__ x, Op op, int n_items) {
+    using C = StreamCfg<T>;
+    using Lay = StreamLayout<T, FROM_IMAGE, Op>;
+    constexpr int V = C::V, STAGES = C::STAGES, NROWS = Lay::NROWS, NWIN = Lay::NWIN;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    T* ring = reinterpret_cast<T*>(smem_raw);
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + Lay::RING_BYTES);
+    uint64_t* empty = full + STAGES;
+    const Geom& g = L.g;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    for (int e = threadIdx.x; e < STAGES * Lay::STAGE_ELEMS; e += blockDim.x) ring[e] = T(0);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, C::CW); }
+        mbar_fence_init();
+    }
+    fence_proxy_async();
+    __syncthreads();
+
+    const int items_per_pair = L.tiles_x * L.strips;
+    uint32_t n = 0;                                     // running stage counter (continues across items)
+
+    if (warp == C::CW) {
+        // ------------------------------------------------------------------ producer warp
+        // lane q owns staged row q: [0,3) solution planes (NEED_X), then the image plane (FROM_IMAGE),
+        // then the centre rows: NCEN vectors x 3 planes, then 7 coefficient planes (!FROM_IMAGE).
+        const bool is_win = lane < NWIN;
+        const bool is_sol = Op::NEED_X && lane < 3;
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int pair = item / items_per_pair;
+            if (L.active != nullptr && L.active[pair] == 0) continue;
+            const int rem = item - pair * items_per_pair;
+            const int tile = rem / L.strips, strip = rem - tile * L.strips;
+            const int c0 = tile * C::TW;
+            const int lo = max(c0 - C::HALO, 0), hi = min(c0 + C::TW + C::HALO, g.pitch);
+            const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(T);
+            const int i_begin = strip * L.rows_per_strip;
+            const int i_end = min(i_begin + L.rows_per_strip, g.Nx);
+            const int nk = i_end - i_begin + 2;
+            const T* base = nullptr;
+            if (lane < NROWS) {
+                if (is_sol) base = x + (long long)pair * g.pair + (long long)lane * g.plane;
+                else if (is_win) base = L.coef + (long long)pair * L.coef_pair;               // image plane
+                else {
+                    const int c = lane - NWIN;
+                    if (c < 3 * Op::NCEN) base = op.cen[c / 3] + (long long)pair * g.pair + (long long)(c % 3) * g.plane;
+                    else base = L.coef + (long long)pair * L.coef_pair + (long long)(c - 3 * Op::NCEN) * g.plane;
+                }
+                base += lo;
+            }
+            const int dst_off = lane * C::ROW + (lo - (c0 - C::HALO));
+            for (int k = 0; k < nk; ++k, ++n) {
+                const int s = n % STAGES;
+                const uint32_t ph = (n / STAGES) & 1u;
+                mbar_wait_sleep(empty + s, ph ^ 1u, 256);
+                const bool cen_valid = k >= 2;
+                if (lane == 0) mbar_arrive_expect_tx(full + s, (uint32_t)(cen_valid ? NROWS : NWIN) * bytes);
+                __syncwarp();
+                if (lane < NROWS && (is_win || cen_valid)) {
+                    int row;
+                    if (is_win) {
+                        row = i_begin - 1 + k;
+                        if (is_sol) row = mirror_index(row, g.Nx);
+                        row = min(max(row, 0), g.Nx - 1);
+                    } else {
+                        row = i_begin - 2 + k;
+                    }
+                    bulk_g2s(ring + s * Lay::STAGE_ELEMS + dst_off, base + (long long)row * g.pitch, bytes, full + s);
+                }
+            }
+        }
+    } else {
+        // ------------------------------------------------------------------ consumer warps
+        Row<T> ux[3], uy[3], gg[3], pw[3];
+        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
+            const int pair = item / items_per_pair;
+            if (L.active != nullptr && L.active[pair] == 0) continue;
+            const int rem = item - pair * items_per_pair;
+            const int tile = rem / L.strips, strip = rem - tile * L.strips;
+            const int c0 = tile * C::TW;
+            const int cw0 = c0 + warp * (WARP * V);
+            const int j0 = cw0 + lane * V;
+            const bool warp_has_cols = cw0 < g.Ny;
+            const bool edge_warp = (cw0 == 0) || (cw0 + WARP * V + 1 >= g.Ny - 1);
+            const int i_begin = strip * L.rows_per_strip;
+            const int i_end = min(i_begin + L.rows_per_strip, g.Nx);
+            const int nk = i_end - i_begin + 2;
+            const T a = T(L.alpha[pair] * L.h2), be = T(L.beta[pair] * L.h2);
+
+            auto do_stage = [&](auto SLOT, int k) {
+                constexpr int sp = decltype(SLOT)::value, sm = (sp + 1) % 3, sc = (sp + 2) % 3;
+                const int s = n % STAGES;
+                const uint32_t ph = (n / STAGES) & 1u;
+                ++n;
+                mbar_wait_sleep(full + s, ph, 32);
+                const T* stg = ring + s * Lay::STAGE_ELEMS - (c0 - C::HALO);      // stg[q*ROW + j] = column j of staged row q
+                const int i = i_begin + k - 2;                                    // centre row of this stage
+                const bool compute = warp_has_cols && k >= 2;
+                if (warp_has_cols) {
+                    const int iw = i + 1;                                         // window row delivered by this stage
+                    const bool ghost_row = (iw == 0) || (iw == g.Nx - 1);
+                    if constexpr (Op::NEED_X) {
+                        load_row_ptr<T, LOAD_SOL, true>(ux[sp], stg, ghost_row, j0, g, lane, edge_warp);
+                        load_row_ptr<T, LOAD_SOL, true>(uy[sp], stg + C::ROW, ghost_row, j0, g, lane, edge_warp);
+                        load_row_ptr<T, LOAD_SOL, true>(gg[sp], stg + 2 * C::ROW, ghost_row, j0, g, lane, edge_warp);
+                    }
+                    if constexpr (FROM_IMAGE) load_row_ptr<T, LOAD_RAW, true>(pw[sp], stg + (NWIN - 1) * C::ROW, false, j0, g, lane, false);
+                }
+                if (compute) {
+                    // centre rows (vectors, coefficient planes) are read from the stage at the point of use;
+                    // the stage is released after the row has been computed
+                    Coef<T> cf[V];
+                    bool inside[V];
+                    T sx[3][V], xc[3][V];
+                    const bool row_inside = (i >= 1) && (i <= g.Nx - 2);
+                    if constexpr (!FROM_IMAGE) {
+                        using VT = typename VecOf<T>::type;
+                        T cr[NCOEF][V];
+#pragma unroll
+                        for (int q = 0; q < NCOEF; ++q) {
+                            const VT t = *reinterpret_cast<const VT*>(stg + (NWIN + 3 * Op::NCEN + q) * C::ROW + j0);
+                            const T* p = reinterpret_cast<const T*>(&t);
+#pragma unroll
+                            for (int kk = 0; kk < V; ++kk) cr[q][kk] = p[kk];
+                        }
+#pragma unroll
+                        for (int kk = 0; kk < V; ++kk) {
+                            cf[kk].II = cr[0][kk]; cf[kk].IIx = cr[1][kk]; cf[kk].IIxx = cr[2][kk]; cf[kk].IIyy = cr[3][kk];
+                            cf[kk].IIxy = cr[4][kk]; cf[kk].Ih = cr[5][kk]; cf[kk].Ix = cr[6][kk];
+                        }
+                    }
+#pragma unroll
+                    for (int kk = 0; kk < V; ++kk) {
+                        const int j = j0 + kk;
+                        inside[kk] = row_inside && (j >= 1) && (j <= g.Ny - 2);
+                        if constexpr (FROM_IMAGE) cf[kk] = coef_from_image<T>(pw[sm], pw[sc], pw[sp], kk + 1);
+                        if constexpr (Op::NEED_X) {
+                            Win<T> wx{ux[sm], ux[sc], ux[sp]}, wy{uy[sm], uy[sc], uy[sp]}, wg{gg[sm], gg[sc], gg[sp]};
+                            apply_point<T>(cf[kk], wx, wy, wg, kk + 1, a, be, sx[0][kk], sx[1][kk], sx[2][kk]);
+                            xc[0][kk] = ux[sc].v[kk + 1]; xc[1][kk] = uy[sc].v[kk + 1]; xc[2][kk] = gg[sc].v[kk + 1];
+                        } else {
+                            sx[0][kk] = sx[1][kk] = sx[2][kk] = T(0);
+                            xc[0][kk] = xc[1][kk] = xc[2][kk] = T(0);
+                        }
+                    }
+                    const CenShared<T, C::ROW> cv{stg + NWIN * C::ROW + j0};
+                    op.row(pair, i, j0, cf, sx, xc, inside, a, be, cv);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty + s);
+            };
+            int k = 0;
+            while (k < nk) {
+                do_stage(IC<0>{}, k); if (++k >= nk) break;
+                do_stage(IC<1>{}, k); if (++k >= nk) break;
+                do_stage(IC<2>{}, k); ++k;
+            }
+            op.flush(pair);
+        }
+    }
+}
+
+}  // namespace ofb

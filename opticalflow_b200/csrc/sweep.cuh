@@ -27,11 +27,51 @@ template <typename T, bool FROM_IMAGE> struct CoefRows {
     Row<T> p[3];            // image rows (FROM_IMAGE)
 };
 
+// plain stores of V values into three planes of a vector at row i
+template <typename T>
+__device__ __forceinline__ void store3(T* __restrict__ base, const Geom& g, int pair, int i, int j0,
+                                       const T (&v)[3][VecOf<T>::V]) {
+    T* p = base + (long long)pair * g.pair + (long long)i * g.pitch;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) store_own<T>(p + q * g.plane, j0, g.Ny, g.aligned != 0, v[q]);
+}
+template <typename T>
+__device__ __forceinline__ void load3(const T* __restrict__ base, const Geom& g, int pair, int i, int j0,
+                                      T (&v)[3][VecOf<T>::V]) {
+    const T* p = base + (long long)pair * g.pair + (long long)i * g.pitch;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) load_own<T>(p + q * g.plane, j0, g.Ny, g.aligned != 0, v[q]);
+}
+
+// Centre-row inputs of an op (NCEN three-plane vectors read at the row's own pixels only) are fetched
+// through an accessor at the point of use, so that they never sit in registers across the stencil
+// arithmetic: from global memory in the register sweep, from the staged row in the streamed sweep.
+template <typename T> struct CenGlobal {
+    const T* const* cen; const Geom* g; int pair, i, j0;
+    __device__ __forceinline__ void get(int n, int q, T (&v)[VecOf<T>::V]) const {
+        load_own<T>(cen[n] + (long long)pair * g->pair + (long long)q * g->plane + (long long)i * g->pitch, j0, g->Ny,
+                    g->aligned != 0, v);
+    }
+};
+template <typename T, int ROW> struct CenShared {
+    const T* base;          // staged centre row 0 at this lane's first column
+    __device__ __forceinline__ void get(int n, int q, T (&v)[VecOf<T>::V]) const {
+        using VT = typename VecOf<T>::type;
+        const VT t = *reinterpret_cast<const VT*>(base + (3 * n + q) * ROW);
+        const T* p = reinterpret_cast<const T*>(&t);
+#pragma unroll
+        for (int k = 0; k < VecOf<T>::V; ++k) v[k] = p[k];
+    }
+};
+
 // Op interface (all members __device__):
 //   static constexpr bool NEED_X;          // needs the solution window (false: pointwise ops)
+//   static constexpr int NCEN;             // number of centre-only vector inputs
+//   const T* cen[max(NCEN,1)];             // their base pointers ([B][3][plane] layout)
 //   void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
-//            const T (&xc)[3][V], const bool (&inside)[V], T a, T be);
-//   void finish(int pair);                 // block-level reductions etc. (called by all threads)
+//            const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv);   // cv.get(n, q, v)
+//   void finish(int pair, bool has_work);  // k_sweep: block-level reductions (called by all threads)
+//   void flush(int pair);                  // k_stream: warp-level reductions + reset (called by whole warps)
 template <typename T, bool FROM_IMAGE, typename Op>
 __device__ __forceinline__ void sweep_body(const LevelArgs<T>& L, const T* __restrict__ x, Op& op) {
     constexpr int V = VecOf<T>::V;
@@ -94,7 +134,8 @@ __device__ __forceinline__ void sweep_body(const LevelArgs<T>& L, const T* __res
                     xc[0][k] = xc[1][k] = xc[2][k] = T(0);
                 }
             }
-            op.row(pair, i, j0, cf, sx, xc, inside, a, be);
+            const CenGlobal<T> cv{op.cen, &g, pair, i, j0};
+            op.row(pair, i, j0, cf, sx, xc, inside, a, be, cv);
         };
         load_x(0, i_begin - 1);
         load_x(1, i_begin);
@@ -106,22 +147,6 @@ __device__ __forceinline__ void sweep_body(const LevelArgs<T>& L, const T* __res
         }
     }
     op.finish(pair, has_work);
-}
-
-// plain stores of V values into three planes of a vector at row i
-template <typename T>
-__device__ __forceinline__ void store3(T* __restrict__ base, const Geom& g, int pair, int i, int j0,
-                                       const T (&v)[3][VecOf<T>::V]) {
-    T* p = base + (long long)pair * g.pair + (long long)i * g.pitch;
-#pragma unroll
-    for (int q = 0; q < 3; ++q) store_own<T>(p + q * g.plane, j0, g.Ny, g.aligned != 0, v[q]);
-}
-template <typename T>
-__device__ __forceinline__ void load3(const T* __restrict__ base, const Geom& g, int pair, int i, int j0,
-                                      T (&v)[3][VecOf<T>::V]) {
-    const T* p = base + (long long)pair * g.pair + (long long)i * g.pitch;
-#pragma unroll
-    for (int q = 0; q < 3; ++q) load_own<T>(p + q * g.plane, j0, g.Ny, g.aligned != 0, v[q]);
 }
 
 }  // namespace ofb

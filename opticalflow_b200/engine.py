@@ -95,23 +95,24 @@ def apply_operator(P, x, speed_alpha, remodelling_alpha, eliminated=False):
     return y
 
 
-def smooth(P, b, x_in, speed_alpha, remodelling_alpha, omega=0.8, rows_per_strip=0, out=None):
+def smooth(P, b, x_in, speed_alpha, remodelling_alpha, omega=0.8, rows_per_strip=0, out=None, flags=0):
     """One damped block-Jacobi sweep (the multigrid smoother) -> x_out."""
     _require_cuda(P, b, x_in)
     B, Nx, Ny = P.shape
     a, be = _weights(speed_alpha, B, P.device), _weights(remodelling_alpha, B, P.device)
     out = torch.empty_like(x_in) if out is None else out
-    _lib.check(_lib.load().ofb_smooth(_ptr(P), _ptr(b), _ptr(x_in), _ptr(out), _ptr(a), _ptr(be), float(omega),
-                                      int(rows_per_strip), B, Nx, Ny, _code(P), _stream_ptr(P.device)))
+    opt = make_options('bjacobi', omega=float(omega), rows_per_strip=int(rows_per_strip), flags=int(flags))
+    _lib.check(_lib.load().ofb_smooth(_ptr(P), _ptr(b), _ptr(x_in), _ptr(out), _ptr(a), _ptr(be), ctypes.byref(opt),
+                                      B, Nx, Ny, _code(P), _stream_ptr(P.device)))
     return out
 
 
 def make_options(preconditioner='mg', nu_pre=None, nu_post=None, omega=None, check_every=None, rows_per_strip=None,
-                 coarse_sweeps=None):
+                 coarse_sweeps=None, flags=None):
     opt = _lib.default_options()
     opt.precond = _PRECOND[preconditioner] if isinstance(preconditioner, str) else int(preconditioner)
     for name, value in (('nu_pre', nu_pre), ('nu_post', nu_post), ('omega', omega), ('check_every', check_every),
-                        ('rows_per_strip', rows_per_strip), ('coarse_sweeps', coarse_sweeps)):
+                        ('rows_per_strip', rows_per_strip), ('coarse_sweeps', coarse_sweeps), ('flags', flags)):
         if value is not None:
             setattr(opt, name, value)
     return opt

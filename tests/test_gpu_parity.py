@@ -213,3 +213,61 @@ def test_full_size_1024_properties(cuda_device):
     vx_true = (-1e-3 + 5e-4) * (jj - 511.5)
     sl = (slice(100, -100), slice(100, -100))
     assert np.abs(got64['v_x'][0][sl] - vx_true[sl]).mean() < 0.1
+
+
+# ------------------------------------------------------------------ streamed (TMA bulk copy + mbarrier ring) sweeps
+# shapes wide enough for the streamed path (Ny >= 64 vector lanes, Ny % 4 == 0), with ragged tile ends,
+# single-column last tiles, several strips and strips of one row
+WIDE_SHAPES = [(9, 256), (70, 260), (33, 512), (130, 516), (64, 1024), (21, 1028), (257, 772)]
+
+
+@pytest.mark.parametrize('shape', WIDE_SHAPES)
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-12), (torch.float32, 3e-5)])
+def test_streamed_smoother_matches_model(cuda_device, shape, dtype, tol):
+    """x_out = x + w D^-1 (b - S x) through the streamed sweep == numpy model; and == the register sweep."""
+    from opticalflow_b200 import _lib
+    rng = np.random.default_rng(shape[0] * 31 + shape[1])
+    B = 3
+    P = fo.blur_movie(rng.uniform(20, 200, (B,) + shape), 1.5)          # smooth image: well-conditioned 3x3 blocks
+    x = mg.zero_ghosts(rng.standard_normal((B, 3) + shape))
+    b = mg.zero_ghosts(rng.standard_normal((B, 3) + shape) * 1e4)
+    alphas, betas = np.array([1e5, 1e3, 2e4]), np.array([1e4, 1e2, 1e3])
+    Pd, xd, bd = dev_t(P, cuda_device, dtype), dev_t(x, cuda_device, dtype), dev_t(b, cuda_device, dtype)
+    at, bt = torch.from_numpy(alphas), torch.from_numpy(betas)
+    for rows in (0, 1, 7):
+        got = engine.smooth(Pd, bd, xd, at, bt, omega=0.8, rows_per_strip=rows).cpu().double().numpy()
+        reg = engine.smooth(Pd, bd, xd, at, bt, omega=0.8, rows_per_strip=rows, flags=_lib.FLAG_NO_STREAM).cpu().double().numpy()
+        for k in range(B):
+            r = b[k] - mg.apply_eliminated(P[k], x[k], alphas[k], betas[k])
+            want = mg.zero_ghosts(x[k] + 0.8 * mg.apply_block_jacobi(P[k], r, alphas[k], betas[k]))
+            assert rel(got[k], want) < tol, (rows, k)
+            assert rel(got[k], reg[k]) < tol
+
+
+@pytest.mark.parametrize('shape', [(33, 512), (130, 516), (64, 1024)])
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-13), (torch.float32, 2e-5)])
+def test_streamed_operator_matches_model(cuda_device, shape, dtype, tol):
+    rng = np.random.default_rng(shape[0] * 13 + shape[1])
+    P = rng.uniform(20, 200, (2,) + shape)
+    x = rng.standard_normal((2, 3) + shape)
+    got = engine.apply_operator(dev_t(P, cuda_device, dtype), dev_t(x, cuda_device, dtype), 1e5, 1e4, eliminated=True)
+    got = got.cpu().double().numpy()
+    for k in range(2):
+        assert rel(got[k], mg.apply_eliminated(P[k], x[k], 1e5, 1e4)) < tol
+
+
+@pytest.mark.parametrize('precond', ['mg', 'bjacobi'])
+def test_streamed_solve_matches_register_solve_and_direct(cuda_device, precond):
+    """A wide ragged frame (streamed levels 0 and 1, register sweeps below) against the direct solution."""
+    from opticalflow_b200 import _lib
+    shape = (48, 516)
+    movie = fo.blur_movie(synthetic.translating_movie(shape[0], shape[1], 2, seed=21), 2.5)
+    P, C = movie
+    xd, _ = fo.solve_pair(P, C, 1e5, 1e4)
+    Pd, Cd = dev_t(P[None], cuda_device), dev_t(C[None], cuda_device)
+    b = engine.build_rhs(Pd, Cd)
+    for flags in (0, _lib.FLAG_NO_STREAM):
+        x = torch.zeros_like(b)
+        it, rr, cv = engine.solve(Pd, b, x, 1e5, 1e4, rtol=1e-11, max_it=20000, options=engine.make_options(precond, flags=flags))
+        assert int(cv[0]) == 1, (flags, int(it[0]), float(rr[0]))
+        assert rel(x[0].cpu().numpy(), xd) < 1e-7, flags
