@@ -22,7 +22,7 @@ import time
 import numpy as np
 import torch
 
-from . import _lib, engine
+from . import _lib, engine, hostio
 
 __all__ = ['variational_optical_flow', 'vary_regularisation', 'blur_movie', 'apply_numerical_derivative',
            'apply_constant_boundary_condition', 'get_index_set', 'format_elapsed_time']
@@ -102,10 +102,25 @@ def blur_movie(movie, smoothing_sigma, *, dtype='float64', device=None):
 # ------------------------------------------------------------------------------------------------
 # the hot path
 # ------------------------------------------------------------------------------------------------
+_copy_streams = {}
+
+
+def _copy_stream(dev):
+    key = str(dev)
+    if key not in _copy_streams:
+        _copy_streams[key] = torch.cuda.Stream(dev)
+    return _copy_streams[key]
+
+
 def _default_batch(Nx, Ny, itemsize, n_pairs):
     # ~12 level-0 vectors + hierarchy per pair; stay under a few GB of workspace
     per_pair = 16 * 3 * Nx * Ny * itemsize
-    return int(max(1, min(n_pairs, (6 << 30) // per_pair, 64)))
+    B = int(max(1, min(n_pairs, (4 << 30) // per_pair, 64)))
+    # one chunk would leave nothing to overlap the device->host egress with: split in two when both halves
+    # still fill the machine (>= 4 Mpixel per launch)
+    if B >= n_pairs and n_pairs * Nx * Ny >= (8 << 20):
+        B = max((n_pairs + 1) // 2, -(-(4 << 20) // (Nx * Ny)))
+    return B
 
 
 def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace, solver_options):
@@ -145,7 +160,10 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
 
     Signature, defaults, units and result keys follow optical_flow.py:715-1210: ``movie[T,Nx,Ny]``; velocities
     are returned in ``delta_x/delta_t`` units, ``remodelling`` unscaled; ``result['converged']`` refers to the
-    last pair (:1202) and ``result['speed_functional']`` holds the remodelling functional (:1205)."""
+    last pair (:1202) and ``result['speed_functional']`` holds the remodelling functional (:1205).
+
+    The frame pairs are processed in chunks of ``batch_pairs``: while the device solves chunk k+1, chunk k's
+    planes travel device -> pinned memory on a copy stream and are widened to float64 by a worker thread."""
     t_start = time.time()
     dev = _device(device)
     tdtype, _ = engine.resolve_dtype(dtype)
@@ -154,50 +172,85 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         raise ValueError('movie must be [T>=2, Nx, Ny]')
     T, Nx, Ny = movie_np.shape
     n_pairs = T - 1
-    original = movie_np.astype(np.float64)                                     # :769
     if use_direct_solver:
         rtol = min(rtol, 1e-12)
     solver_options = dict(solver_options or {})
     itemsize = 4 if tdtype == torch.float32 else 8
     B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs)
+    B = max(1, min(B, n_pairs))
     scale_in = float(delta_t) / float(delta_x)                                 # :800-801
     scale_out = float(delta_x) / float(delta_t)                                # :1189-1190
     guess = (float(initial_v_x) * scale_in, float(initial_v_y) * scale_in, float(initial_remodelling))
+    blur = smoothing_sigma is not None
 
+    source = np.ascontiguousarray(movie_np)
+    original = np.empty((T, Nx, Ny), dtype=np.float64)                         # :769
     out = {k: np.empty((n_pairs, Nx, Ny), dtype=np.float64) for k in ('v_x', 'v_y', 'speed', 'remodelling')}
-    blurred = np.empty((T, Nx, Ny), dtype=np.float64) if smoothing_sigma is not None else original
+    blurred = np.empty((T, Nx, Ny), dtype=np.float64) if blur else original
     functionals = np.zeros((n_pairs, 3))
     info = dict(iterations=np.zeros(n_pairs, np.int32), relative_residual=np.zeros(n_pairs),
                 converged=np.zeros(n_pairs, bool), fallback=np.zeros(n_pairs, bool))
     workspace = engine.Workspace()
-    source = np.ascontiguousarray(movie_np)
-    for k0 in range(0, n_pairs, B):
-        k1 = min(k0 + B, n_pairs)
-        nb = k1 - k0
-        frames = torch.from_numpy(source[k0:k1 + 1]).to(dev).to(tdtype)        # nb+1 frames
-        if smoothing_sigma is not None:
-            frames = engine.blur(frames, smoothing_sigma)                      # :770-771
-            last = k1 + 1 if k1 == n_pairs else k1
-            blurred[k0:last] = frames[:last - k0].to(torch.float64).cpu().numpy()
-        P, C = frames[:-1], frames[1:]
-        x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
-        for q in range(3):
-            x0[:, q] = guess[q]
-        x, iters, relres, conv, fb = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
-                                                  preconditioner, workspace, solver_options)
-        vx, vy, sp, gm, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out)
-        out['v_x'][k0:k1] = vx.to(torch.float64).cpu().numpy()
-        out['v_y'][k0:k1] = vy.to(torch.float64).cpu().numpy()
-        out['speed'][k0:k1] = sp.to(torch.float64).cpu().numpy()
-        out['remodelling'][k0:k1] = gm.to(torch.float64).cpu().numpy()
-        functionals[k0:k1] = fun.cpu().numpy()
-        info['iterations'][k0:k1] = iters.cpu().numpy()
-        info['relative_residual'][k0:k1] = relres.cpu().numpy()
-        info['converged'][k0:k1] = conv.cpu().numpy() != 0
-        info['fallback'][k0:k1] = fb.cpu().numpy()
-        if verbose:
-            print('pairs %d..%d: iterations %s, residuals %s' % (k0 + 1, k1, info['iterations'][k0:k1],
-                                                                   info['relative_residual'][k0:k1]))
+    nplanes = 5 if blur else 4                                                 # v_x, v_y, speed, remodelling (, blurred)
+    main_stream = torch.cuda.current_stream(dev)
+    copy_stream = _copy_stream(dev)
+    worker = hostio.EgressWorker()
+    slots = []                                                                 # double-buffered device + pinned planes
+    for s in range(2):
+        slots.append(dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev),
+                          pin=hostio.pinned_buffer(('egress', s, str(dev)), (nplanes, B + 1, Nx, Ny), tdtype),
+                          busy=None))
+    try:
+        pending = worker.submit(None, [(original, hostio.as_native_tensor(source))])
+        stats = []
+        for c, k0 in enumerate(range(0, n_pairs, B)):
+            k1 = min(k0 + B, n_pairs)
+            nb = k1 - k0
+            slot = slots[c % 2]
+            if slot['busy'] is not None:
+                slot['busy'].wait()                                            # worker has drained this slot's pinned planes
+            frames = hostio.upload_frames(source[k0:k1 + 1], dev, tdtype)      # nb+1 frames
+            if blur:
+                frames = engine.blur(frames, smoothing_sigma, out=slot['dev'][4, :nb + 1])     # :770-771
+            P, C = frames[:-1], frames[1:]
+            x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
+            for q in range(3):
+                x0[:, q] = guess[q]
+            x, iters, relres, conv, fb = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
+                                                      preconditioner, workspace, solver_options)
+            fields = slot['dev'][:4, :nb]
+            _, _, _, _, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out, out=fields)
+            ready = torch.cuda.Event()
+            ready.record(main_stream)
+            last_frame = nb + 1 if k1 == n_pairs else nb
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(ready)
+                for q in range(4):
+                    slot['pin'][q, :nb].copy_(slot['dev'][q, :nb], non_blocking=True)
+                if blur:
+                    slot['pin'][4, :last_frame].copy_(slot['dev'][4, :last_frame], non_blocking=True)
+                copied = torch.cuda.Event()
+                copied.record(copy_stream)
+            copies = [(out[name][k0:k1], slot['pin'][q, :nb]) for q, name in enumerate(('v_x', 'v_y', 'speed', 'remodelling'))]
+            if blur:
+                copies.append((blurred[k0:k0 + last_frame], slot['pin'][4, :last_frame]))
+            slot['busy'] = worker.submit(copied, copies)       # slot reuse (two chunks later) waits for this on the host
+            stats.append((k0, k1, fun, iters, relres, conv, fb))
+        for k0, k1, fun, iters, relres, conv, fb in stats:
+            functionals[k0:k1] = fun.cpu().numpy()
+            info['iterations'][k0:k1] = iters.cpu().numpy()
+            info['relative_residual'][k0:k1] = relres.cpu().numpy()
+            info['converged'][k0:k1] = conv.cpu().numpy() != 0
+            info['fallback'][k0:k1] = fb.cpu().numpy()
+            if verbose:
+                print('pairs %d..%d: iterations %s, residuals %s' % (k0 + 1, k1, info['iterations'][k0:k1],
+                                                                       info['relative_residual'][k0:k1]))
+        pending.wait()
+        for slot in slots:
+            if slot['busy'] is not None:
+                slot['busy'].wait()
+    finally:
+        worker.close()
     if verbose and not info['converged'].all():
         print('the solver has not actually converged, the result will be incorrect or inaccurate')
     result = dict()
@@ -217,6 +270,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info['elapsed_seconds'] = time.time() - t_start
     info['dtype'] = str(tdtype).replace('torch.', '')
     info['batch_pairs'] = B
+    info['h2d_bytes'] = int(sum(min(k0 + B, n_pairs) - k0 + 1 for k0 in range(0, n_pairs, B)) * source[0].nbytes)
+    info['d2h_bytes'] = int((4 * n_pairs + (T if blur else 0)) * Nx * Ny * itemsize)
     result['solver_info'] = info
     return result
 
