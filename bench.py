@@ -36,6 +36,7 @@ def parse():
     ap.add_argument('--batch', type=int, default=16, help='frame pairs per step per GPU')
     ap.add_argument('--dtype', default='float32')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true', help='profiling runs only: skip the end-to-end leg')
     return ap.parse_args()
 
 
@@ -202,20 +203,25 @@ def run_gpu(args):
 
     def e2e_step():
         return optical_flow.variational_optical_flow(movie_e2e, dtype=args.dtype, rtol=RTOL, batch_pairs=B, device=dev, **KW)
-    for _ in range(2):
-        res = e2e_step()
-    barrier()
-    t0 = time.perf_counter()
-    n_e2e = max(2, min(args.steps, 3))
-    for _ in range(n_e2e):
-        res = e2e_step()
-    barrier()
-    e2e_s = (time.perf_counter() - t0) / n_e2e
-    sampler.stop_flag.set()
-    sampler.join()
-    assert res['solver_info']['converged'].all()
-    h2d = res['solver_info']['h2d_bytes'] * B // pairs_e2e          # per step of B pairs
-    d2h = res['solver_info']['d2h_bytes'] * B // pairs_e2e
+    if args.no_e2e:
+        sampler.stop_flag.set()
+        sampler.join()
+        e2e_s, h2d, d2h = float('nan'), 0, 0
+    else:
+        for _ in range(2):
+            res = e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        n_e2e = max(2, min(args.steps, 3))
+        for _ in range(n_e2e):
+            res = e2e_step()
+        barrier()
+        e2e_s = (time.perf_counter() - t0) / n_e2e
+        sampler.stop_flag.set()
+        sampler.join()
+        assert res['solver_info']['converged'].all()
+        h2d = res['solver_info']['h2d_bytes'] * B // pairs_e2e          # per step of B pairs
+        d2h = res['solver_info']['d2h_bytes'] * B // pairs_e2e
 
     # ---- roofline of the dominant kernel: the level-0 block-Jacobi smoother sweep (10 words / pixel)
     xin = torch.randn_like(b)

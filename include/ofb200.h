@@ -35,7 +35,7 @@ extern "C" {
 
 #define OFB_FLAG_NO_STREAM 1    /* use the register-only sweep on every level (A/B measurements) */
 
-#define OFB_ABI_VERSION 1
+#define OFB_ABI_VERSION 2
 
 typedef struct ofb_solve_options {
     int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
@@ -46,6 +46,10 @@ typedef struct ofb_solve_options {
     int    rows_per_strip; /* 0 = choose from the batch size */
     int    coarse_sweeps;  /* Jacobi sweeps on the coarsest level when it is too large for the dense solve; default 30 */
     int    flags;          /* OFB_FLAG_* bits; default 0 */
+    double omega_pre[4];   /* damping of pre-smoothing sweep s (0 = use omega); sweep 0 is the zero-guess sweep */
+    double omega_post[4];  /* damping of post-smoothing sweep s (0 = use omega) */
+    int    max_levels;     /* cap on the number of multigrid levels (0 = coarsen as far as possible) */
+    int    reserved;
 } ofb_solve_options;
 
 int         ofb_version(void);

@@ -11,7 +11,7 @@ LIBRARY_PATH = os.path.join(_HERE, 'libofb200.so')
 OFB_F32, OFB_F64 = 0, 1
 PRECOND_BJACOBI, PRECOND_MG = 0, 1
 FLAG_NO_STREAM = 1
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 # every symbol include/ofb200.h declares
 EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_workspace_bytes', 'ofb_blur',
@@ -22,7 +22,9 @@ EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb
 class SolveOptions(ctypes.Structure):
     _fields_ = [('precond', ctypes.c_int), ('nu_pre', ctypes.c_int), ('nu_post', ctypes.c_int),
                 ('omega', ctypes.c_double), ('check_every', ctypes.c_int), ('rows_per_strip', ctypes.c_int),
-                ('coarse_sweeps', ctypes.c_int), ('flags', ctypes.c_int)]
+                ('coarse_sweeps', ctypes.c_int), ('flags', ctypes.c_int),
+                ('omega_pre', ctypes.c_double * 4), ('omega_post', ctypes.c_double * 4),
+                ('max_levels', ctypes.c_int), ('reserved', ctypes.c_int)]
 
 
 class OfbError(RuntimeError):

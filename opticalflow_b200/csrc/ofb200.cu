@@ -106,14 +106,15 @@ struct Plan {
     int dense_n;
 };
 
-Plan make_plan(int Nx, int Ny, int precond) {
+Plan make_plan(int Nx, int Ny, int precond, int max_levels = 0) {
     Plan p;
     p.nlevels = 1;
     p.lv[0] = {Nx, Ny, Ny, (long long)Nx * Ny};
     p.dense = false;
     p.dense_n = 0;
     if (precond != OFB_PRECOND_MG) return p;
-    while (p.nlevels < MAX_LEVELS) {
+    const int level_cap = (max_levels > 0) ? std::min(max_levels, MAX_LEVELS) : MAX_LEVELS;
+    while (p.nlevels < level_cap) {
         const LevelPlan& f = p.lv[p.nlevels - 1];
         const int cx = coarse_size(f.Nx), cy = coarse_size(f.Ny);
         if (cx < MIN_COARSE || cy < MIN_COARSE || cx >= f.Nx || cy >= f.Ny) break;
@@ -248,8 +249,10 @@ template <typename T> struct Solver {
         return 0;
     }
 
-    int smooth(int l, const T* b, const T* xin, T* xout) {
-        OpSmooth<T> op; op.g = g[l]; op.cen[0] = b; op.xo = xout; op.w = T(opt.omega);
+    double w_pre(int s) const { return (s < 4 && opt.omega_pre[s] > 0.0) ? opt.omega_pre[s] : opt.omega; }
+    double w_post(int s) const { return (s < 4 && opt.omega_post[s] > 0.0) ? opt.omega_post[s] : opt.omega; }
+    int smooth(int l, const T* b, const T* xin, T* xout, double wj) {
+        OpSmooth<T> op; op.g = g[l]; op.cen[0] = b; op.xo = xout; op.w = T(wj);
         return sweep(l, xin, op);
     }
     int residual(int l, const T* b, const T* x, T* r) {
@@ -285,7 +288,7 @@ template <typename T> struct Solver {
     // `alt` is the ping-pong partner.  Returns the buffer holding the result in *out.
     int vcycle(int l, const T* b, T* cur, T* alt, T** out) {
         int rc;
-        for (int s = 1; s < opt.nu_pre; ++s) { if ((rc = smooth(l, b, cur, alt))) return rc; std::swap(cur, alt); }
+        for (int s = 1; s < opt.nu_pre; ++s) { if ((rc = smooth(l, b, cur, alt, w_pre(s)))) return rc; std::swap(cur, alt); }
         const int lc = l + 1;
         T* res = (l == 0) ? w.t : w.res[l];
         if ((rc = residual(l, b, cur, res))) return rc;
@@ -304,11 +307,11 @@ template <typename T> struct Solver {
             } else {
                 if ((rc = jacobi_zero(lc, w.lb[lc], w.xa[lc], opt.omega))) return rc;
                 T *c = w.xa[lc], *a = w.xb[lc];
-                for (int s = 1; s < opt.coarse_sweeps; ++s) { if ((rc = smooth(lc, w.lb[lc], c, a))) return rc; std::swap(c, a); }
+                for (int s = 1; s < opt.coarse_sweeps; ++s) { if ((rc = smooth(lc, w.lb[lc], c, a, opt.omega))) return rc; std::swap(c, a); }
                 ec = c;
             }
         } else {
-            if ((rc = jacobi_zero(lc, w.lb[lc], w.xa[lc], opt.omega))) return rc;
+            if ((rc = jacobi_zero(lc, w.lb[lc], w.xa[lc], w_pre(0)))) return rc;
             if ((rc = vcycle(lc, w.lb[lc], w.xa[lc], w.xb[lc], &ec))) return rc;
         }
         {
@@ -316,7 +319,7 @@ template <typename T> struct Solver {
             k_prolong_add<T><<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
             OFB_CHECK_LAUNCH();
         }
-        for (int s = 0; s < opt.nu_post; ++s) { if ((rc = smooth(l, b, cur, alt))) return rc; std::swap(cur, alt); }
+        for (int s = 0; s < opt.nu_post; ++s) { if ((rc = smooth(l, b, cur, alt, w_post(s)))) return rc; std::swap(cur, alt); }
         *out = cur;
         return 0;
     }
@@ -327,7 +330,7 @@ template <typename T> struct Solver {
         if (opt.precond != OFB_PRECOND_MG || plan.nlevels == 1) { *out = first; return 0; }
         return vcycle(0, d, first, partner, out);
     }
-    double first_sweep_weight() const { return (opt.precond == OFB_PRECOND_MG && plan.nlevels > 1) ? opt.omega : 1.0; }
+    double first_sweep_weight() const { return (opt.precond == OFB_PRECOND_MG && plan.nlevels > 1) ? w_pre(0) : 1.0; }
     // buffer the first sweep must write to so that the V-cycle result lands in `target`
     T* first_buffer(T* target) const {
         if (opt.precond != OFB_PRECOND_MG || plan.nlevels == 1) return target;
@@ -345,7 +348,7 @@ int init_solver(Solver<T>& S, const void* P, const double* alpha, const double* 
     if (S.opt.coarse_sweeps < 1) S.opt.coarse_sweeps = 1;
     if (S.opt.check_every < 1) S.opt.check_every = 1;
     S.B = B;
-    S.plan = make_plan(Nx, Ny, S.opt.precond);
+    S.plan = make_plan(Nx, Ny, S.opt.precond, S.opt.max_levels);
     S.w = carve<T>(workspace, B, S.plan);
     if (workspace == nullptr || workspace_bytes < S.w.bytes)
         return fail(-4, "workspace too small: need %zu bytes, got %zu", S.w.bytes, workspace_bytes);
@@ -524,7 +527,7 @@ int smooth_impl(const void* P, const void* b3, const void* x_in, void* x_out, co
     memset(&S.w, 0, sizeof(S.w));
     S.g[0] = make_geom<T>(S.plan.lv[0], ptr_aligned16(P) && ptr_aligned16(b3) && ptr_aligned16(x_in) && ptr_aligned16(x_out));
     S.P = (const T*)P; S.alpha = alpha; S.beta = beta; S.stream = (cudaStream_t)stream; S.active = nullptr;
-    return S.smooth(0, (const T*)b3, (const T*)x_in, (T*)x_out);
+    return S.smooth(0, (const T*)b3, (const T*)x_in, (T*)x_out, S.opt.omega);
 }
 
 template <typename T>
@@ -561,6 +564,9 @@ void ofb_default_options(ofb_solve_options* opt) {
     opt->rows_per_strip = 0;
     opt->coarse_sweeps = 30;
     opt->flags = 0;
+    for (int s = 0; s < 4; ++s) opt->omega_pre[s] = opt->omega_post[s] = 0.0;
+    opt->max_levels = 0;
+    opt->reserved = 0;
 }
 
 size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond) {

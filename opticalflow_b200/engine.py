@@ -108,13 +108,17 @@ def smooth(P, b, x_in, speed_alpha, remodelling_alpha, omega=0.8, rows_per_strip
 
 
 def make_options(preconditioner='mg', nu_pre=None, nu_post=None, omega=None, check_every=None, rows_per_strip=None,
-                 coarse_sweeps=None, flags=None):
+                 coarse_sweeps=None, flags=None, omega_pre=None, omega_post=None, max_levels=None):
     opt = _lib.default_options()
     opt.precond = _PRECOND[preconditioner] if isinstance(preconditioner, str) else int(preconditioner)
     for name, value in (('nu_pre', nu_pre), ('nu_post', nu_post), ('omega', omega), ('check_every', check_every),
-                        ('rows_per_strip', rows_per_strip), ('coarse_sweeps', coarse_sweeps), ('flags', flags)):
+                        ('rows_per_strip', rows_per_strip), ('coarse_sweeps', coarse_sweeps), ('flags', flags),
+                        ('max_levels', max_levels)):
         if value is not None:
             setattr(opt, name, value)
+    for name, values in (('omega_pre', omega_pre), ('omega_post', omega_post)):
+        for s, value in enumerate(values or ()):
+            getattr(opt, name)[s] = float(value)
     return opt
 
 
