@@ -259,7 +259,7 @@ def run_gpu(args):
                     ms_per_step=ms_max / args.steps, higher_is_better=True, scaling='weak', vs_baseline=None,
                     dtype='f32' if args.dtype == 'float32' else 'f64', data='synthetic',
                     config=dict(workload='d-3: 1024^2 rotating+shearing textured movie, alpha 1e5, beta 1e4, sigma 2.5, '
-                                         'rtol 1e-6, V(2,2)-multigrid BiCGStab',
+                                         'rtol 1e-6, BiCGStab + V(1,2) multigrid (block-Jacobi smoother)',
                                 pairs_per_step_per_gpu=B, parallelism='frame pairs sharded over %d GPU(s), no collective' % world,
                                 l2='working set %.1f GB per step exceeds the 126 MB L2' % (12 * 3 * NX * NY * itemsize * B / 1e9),
                                 iterations_per_pair=float(iters.mean()), iterations_max=int(iters.max())),

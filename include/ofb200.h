@@ -39,15 +39,15 @@ extern "C" {
 
 typedef struct ofb_solve_options {
     int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
-    int    nu_pre;         /* pre-smoothing sweeps      default 2 */
+    int    nu_pre;         /* pre-smoothing sweeps      default 1 */
     int    nu_post;        /* post-smoothing sweeps     default 2 */
-    double omega;          /* Jacobi damping            default 0.8 */
+    double omega;          /* Jacobi damping where no per-sweep value is given; default 0.8 */
     int    check_every;    /* convergence poll period in iterations (host sync); default 1 */
     int    rows_per_strip; /* 0 = choose from the batch size */
     int    coarse_sweeps;  /* Jacobi sweeps on the coarsest level when it is too large for the dense solve; default 30 */
     int    flags;          /* OFB_FLAG_* bits; default 0 */
-    double omega_pre[4];   /* damping of pre-smoothing sweep s (0 = use omega); sweep 0 is the zero-guess sweep */
-    double omega_post[4];  /* damping of post-smoothing sweep s (0 = use omega) */
+    double omega_pre[4];   /* damping of pre-smoothing sweep s (0 = use omega); sweep 0 is the zero-guess sweep; default {1.0} */
+    double omega_post[4];  /* damping of post-smoothing sweep s (0 = use omega); default {1.3, 0.5} */
     int    max_levels;     /* cap on the number of multigrid levels (0 = coarsen as far as possible) */
     int    reserved;
 } ofb_solve_options;

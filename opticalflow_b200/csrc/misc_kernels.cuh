@@ -176,11 +176,11 @@ __global__ void __launch_bounds__(128) k_epilogue(Geom g, const T* __restrict__ 
                                                   double* __restrict__ moments,
                                                   const double* __restrict__ alpha, const double* __restrict__ beta, double scale) {
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = blockIdx.y;
     const int pair = blockIdx.z;
     double acc[3] = {0.0, 0.0, 0.0};
     double mom[4] = {0.0, 0.0, 0.0, 0.0};
-    if (j < g.Ny) {
+    // rows are strided over gridDim.y so that each block ends with ONE round of atomics
+    if (j < g.Ny) for (int i = blockIdx.y; i < g.Nx; i += gridDim.y) {
         const T* xb = x + (long long)pair * g.pair;
         const int mi = mirror_index(i, g.Nx), mj = mirror_index(j, g.Ny);
         const long long o = (long long)mi * g.pitch + mj;
@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(128) k_epilogue(Geom g, const T* __restrict__ 
         vx[oo] = ux * T(scale); vy[oo] = uy * T(scale); gamma[oo] = gm;
         const T sp = T(sqrt((double)(ux * T(scale)) * (double)(ux * T(scale)) + (double)(uy * T(scale)) * (double)(uy * T(scale))));
         speed[oo] = sp;
-        mom[0] = (double)sp; mom[1] = (double)sp * (double)sp; mom[2] = (double)gm; mom[3] = (double)gm * (double)gm;
+        mom[0] += (double)sp; mom[1] += (double)sp * (double)sp; mom[2] += (double)gm; mom[3] += (double)gm * (double)gm;
         if (i >= 1 && i <= g.Nx - 2 && j >= 1 && j <= g.Ny - 2) {
             const int ip = mirror_index(i + 1, g.Nx), im = mirror_index(i - 1, g.Nx);
             const long long op = (long long)ip * g.pitch + mj, om = (long long)im * g.pitch + mj;
@@ -203,9 +203,9 @@ __global__ void __launch_bounds__(128) k_epilogue(Geom g, const T* __restrict__ 
             const double Ix = 0.5 * ((double)p[q + g.pitch] - (double)p[q - g.pitch]);
             const double It = (double)c[q] - I;
             const double e = It + (double)ux * Ix + (double)uy * Ix + I * dux + I * duy - (double)gm;
-            acc[0] = e * e;
-            acc[1] = alpha[pair] * 2.0 * (dux * dux + duy * duy);
-            acc[2] = beta[pair] * 2.0 * dg * dg;
+            acc[0] += e * e;
+            acc[1] += alpha[pair] * 2.0 * (dux * dux + duy * duy);
+            acc[2] += beta[pair] * 2.0 * dg * dg;
         }
     }
     block_accumulate<3>(acc, functionals + 3 * pair);

@@ -62,7 +62,7 @@ inline int device_sms() {
 
 // Streamed (TMA bulk copy + mbarrier ring) sweep: persistent grid of (CTAs per SM) x SMs.
 template <typename T, bool FROM_IMAGE, typename Op>
-int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_strip, cudaStream_t stream) {
+int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_strip, bool skip_last_ghost, cudaStream_t stream) {
     using C = StreamCfg<T>;
     using Lay = StreamLayout<T, FROM_IMAGE, Op>;
     auto kern = k_stream<T, FROM_IMAGE, Op>;
@@ -78,7 +78,9 @@ int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_
         ctas_per_sm[dev] = nb;
     }
     const int slots = device_sms() * ctas_per_sm[dev];
-    L.tiles_x = (L.g.Ny + C::TW - 1) / C::TW;
+    // On coarse levels the last column is a ghost column that no kernel ever reads from memory (every reader
+    // mirrors it from column Ny-3), so tiles need not cover it: 513 columns are one 512-wide tile, not two.
+    L.tiles_x = ((skip_last_ghost ? L.g.Ny - 1 : L.g.Ny) + C::TW - 1) / C::TW;
     int R = rows_per_strip;
     if (R <= 0) {
         const long long total_rows = (long long)L.g.Nx * L.tiles_x * B;
@@ -237,8 +239,8 @@ template <typename T> struct Solver {
     template <typename Op> int sweep(int l, const T* x, Op op) {
         const LevelArgs<T> L = level_args(l);
         if (use_stream(l)) {
-            if (l == 0) return launch_stream<T, true, Op>(L, x, op, B, opt.rows_per_strip, stream);
-            return launch_stream<T, false, Op>(L, x, op, B, opt.rows_per_strip, stream);
+            if (l == 0) return launch_stream<T, true, Op>(L, x, op, B, opt.rows_per_strip, false, stream);
+            return launch_stream<T, false, Op>(L, x, op, B, opt.rows_per_strip, true, stream);
         }
         const int warps_per_block = 4;
         const int items = L.tiles_x * L.strips;
@@ -537,7 +539,7 @@ int epilogue_impl(const void* P, const void* C, const void* x3, void* vx, void* 
     const Geom g = make_geom<T>(lp, false);
     OFB_CHECK_CUDA(cudaMemsetAsync(functionals, 0, sizeof(double) * 3 * B, stream));
     if (moments) OFB_CHECK_CUDA(cudaMemsetAsync(moments, 0, sizeof(double) * 4 * B, stream));
-    dim3 block(128), grid((Ny + 127) / 128, Nx, B);
+    dim3 block(128), grid((Ny + 127) / 128, std::min(Nx, 32), B);
     k_epilogue<T><<<grid, block, 0, stream>>>(g, (const T*)P, (const T*)C, g.img_pair, (const T*)x3, (T*)vx, (T*)vy, (T*)speed,
                                               (T*)gamma, functionals, moments, alpha, beta, scale);
     OFB_CHECK_LAUNCH();
@@ -556,8 +558,11 @@ long long ofb_launch_count(void) { return g_launches.load(); }
 
 void ofb_default_options(ofb_solve_options* opt) {
     if (!opt) return;
+    // V(1,2) cycle: plain block-Jacobi first sweep on the zero guess, two post-sweeps with Chebyshev-like
+    // damping (1.3, 0.5).  Scanned on the B200 against V(2,2)/0.8 (tools/solver_scan.py, profiles/): 30% less
+    // time per solve at the headline regime.  OFB_CYCLE_ROBUST is the slower, more forgiving V(2,2)/0.8.
     opt->precond = OFB_PRECOND_MG;
-    opt->nu_pre = 2;
+    opt->nu_pre = 1;
     opt->nu_post = 2;
     opt->omega = 0.8;
     opt->check_every = 1;
@@ -565,6 +570,9 @@ void ofb_default_options(ofb_solve_options* opt) {
     opt->coarse_sweeps = 30;
     opt->flags = 0;
     for (int s = 0; s < 4; ++s) opt->omega_pre[s] = opt->omega_post[s] = 0.0;
+    opt->omega_pre[0] = 1.0;
+    opt->omega_post[0] = 1.3;
+    opt->omega_post[1] = 0.5;
     opt->max_levels = 0;
     opt->reserved = 0;
 }

@@ -117,8 +117,11 @@ def make_options(preconditioner='mg', nu_pre=None, nu_post=None, omega=None, che
         if value is not None:
             setattr(opt, name, value)
     for name, values in (('omega_pre', omega_pre), ('omega_post', omega_post)):
-        for s, value in enumerate(values or ()):
-            getattr(opt, name)[s] = float(value)
+        if values is None and (omega is not None or nu_pre is not None or nu_post is not None):
+            values = ()                                   # an explicit cycle shape / omega replaces the default per-sweep weights
+        if values is not None:
+            for s in range(4):
+                getattr(opt, name)[s] = float(values[s]) if s < len(values) else 0.0
     return opt
 
 

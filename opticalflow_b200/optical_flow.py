@@ -124,30 +124,37 @@ def _default_batch(Nx, Ny, itemsize, n_pairs):
 
 
 def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace, solver_options):
-    """Solve a batch; pairs the multigrid path could not converge are redone with block-Jacobi."""
+    """Solve a batch.  Pairs the default multigrid cycle does not converge are redone with the robust V(2,2)
+    cycle and, failing that, with plain block-Jacobi BiCGStab (always convergent, slowly)."""
     B = P.shape[0]
     b = engine.build_rhs(P, C)
     x = x0.clone()
     opts = engine.make_options(preconditioner, **solver_options)
     iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace)
     fallback = torch.zeros(B, dtype=torch.bool, device=P.device)
-    if opts.precond == _lib.PRECOND_MG:
+    if opts.precond != _lib.PRECOND_MG:
+        return x, iters, relres, conv, fallback
+    passthrough = {k: v for k, v in solver_options.items() if k in ('check_every', 'rows_per_strip', 'flags')}
+    chain = []
+    if not any(k in solver_options for k in ('nu_pre', 'nu_post', 'omega', 'omega_pre', 'omega_post')):
+        chain.append(engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8, omega_pre=(0.8, 0.8), omega_post=(0.8, 0.8),
+                                         **passthrough))
+    chain.append(engine.make_options('bjacobi', **passthrough))
+    for fb_opts in chain:
         bad = (conv == 0).nonzero().flatten()
-        if bad.numel() > 0:
-            fb_opts = engine.make_options('bjacobi', **{k: v for k, v in solver_options.items()
-                                                        if k in ('check_every', 'rows_per_strip')})
-            xb = x0[bad].clone()
-            a_b = engine._weights(alpha, B, P.device)[bad]
-            be_b = engine._weights(beta, B, P.device)[bad]
-            it2, rr2, cv2 = engine.solve(P[bad].contiguous(), b[bad].contiguous(), xb, a_b, be_b, rtol, max_it,
-                                         fb_opts, workspace)
-            better = (cv2 == 1) | (rr2 < relres[bad])
-            sel = bad[better]
-            x[sel] = xb[better]
-            iters[sel] = it2[better] + iters[sel]
-            relres[sel] = rr2[better]
-            conv[sel] = cv2[better]
-            fallback[sel] = True
+        if bad.numel() == 0:
+            break
+        xb = x0[bad].clone()
+        a_b = engine._weights(alpha, B, P.device)[bad]
+        be_b = engine._weights(beta, B, P.device)[bad]
+        it2, rr2, cv2 = engine.solve(P[bad].contiguous(), b[bad].contiguous(), xb, a_b, be_b, rtol, max_it, fb_opts, workspace)
+        better = (cv2 == 1) | (rr2 < relres[bad])
+        sel = bad[better]
+        x[sel] = xb[better]
+        iters[sel] = it2[better] + iters[sel]
+        relres[sel] = rr2[better]
+        conv[sel] = cv2[better]
+        fallback[sel] = True
     return x, iters, relres, conv, fallback
 
 

@@ -23,7 +23,8 @@ def test_version_options_and_workspace(built_library):
     from opticalflow_b200 import _lib
     assert built_library.ofb_version() == _lib.ABI_VERSION
     opt = _lib.default_options()
-    assert (opt.precond, opt.nu_pre, opt.nu_post, opt.check_every) == (_lib.PRECOND_MG, 2, 2, 1)
+    assert (opt.precond, opt.nu_pre, opt.nu_post, opt.check_every) == (_lib.PRECOND_MG, 1, 2, 1)
+    assert list(opt.omega_pre)[:2] == [1.0, 0.0] and list(opt.omega_post)[:3] == [1.3, 0.5, 0.0]
     assert abs(opt.omega - 0.8) < 1e-15
     small = built_library.ofb_workspace_bytes(1, 64, 64, _lib.OFB_F32, _lib.PRECOND_BJACOBI)
     mg32 = built_library.ofb_workspace_bytes(1, 64, 64, _lib.OFB_F32, _lib.PRECOND_MG)
