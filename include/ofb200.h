@@ -34,6 +34,7 @@ extern "C" {
 #define OFB_PRECOND_MG      1   /* geometric multigrid V-cycle, block-Jacobi smoother, dense coarsest solve */
 
 #define OFB_FLAG_NO_STREAM 1    /* use the register-only sweep on every level (A/B measurements) */
+#define OFB_FLAG_NO_FUSED_TAIL 2 /* run the small multigrid levels as separate launches (A/B measurements) */
 
 #define OFB_ABI_VERSION 2
 

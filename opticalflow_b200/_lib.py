@@ -11,6 +11,7 @@ LIBRARY_PATH = os.path.join(_HERE, 'libofb200.so')
 OFB_F32, OFB_F64 = 0, 1
 PRECOND_BJACOBI, PRECOND_MG = 0, 1
 FLAG_NO_STREAM = 1
+FLAG_NO_FUSED_TAIL = 2
 ABI_VERSION = 2
 
 # every symbol include/ofb200.h declares

@@ -9,6 +9,7 @@
 #include "../../include/ofb200.h"
 #include "misc_kernels.cuh"
 #include "stream_sweep.cuh"
+#include "coarse_fused.cuh"
 
 using namespace ofb;
 
@@ -106,10 +107,16 @@ struct Plan {
     LevelPlan lv[MAX_LEVELS];
     bool dense;                         // coarsest level solved with the dense inverse
     int dense_n;
+    int fused_from;                     // first level of the shared-memory coarse tail (0 = none)
+    size_t fused_smem;                  // bytes of shared memory the tail needs
 };
 
-Plan make_plan(int Nx, int Ny, int precond, int max_levels = 0) {
+constexpr size_t FUSED_SMEM_BUDGET = 220 * 1024;
+
+Plan make_plan(int Nx, int Ny, int precond, int max_levels = 0, size_t elem_size = 4) {
     Plan p;
+    p.fused_from = 0;
+    p.fused_smem = 0;
     p.nlevels = 1;
     p.lv[0] = {Nx, Ny, Ny, (long long)Nx * Ny};
     p.dense = false;
@@ -131,6 +138,13 @@ Plan make_plan(int Nx, int Ny, int precond, int max_levels = 0) {
             p.dense = true; p.dense_n = n;
             c.pitch = c.Ny; c.plane = (long long)c.Nx * c.Ny;      // unpadded: flat index == unknown number
         }
+    }
+    // coarse tail: the longest suffix of levels (>= 2 levels, level >= 1) whose vectors fit in shared memory
+    size_t bytes = 0;
+    for (int l = p.nlevels - 1; l >= 1 && p.nlevels - l <= FUSED_MAX_LEVELS; --l) {
+        bytes += (size_t)9 * p.lv[l].Nx * p.lv[l].Ny * elem_size;
+        if (bytes > FUSED_SMEM_BUDGET) break;
+        if (p.nlevels - l >= 2) { p.fused_from = l; p.fused_smem = bytes; }
     }
     return p;
 }
@@ -283,6 +297,43 @@ template <typename T> struct Solver {
         return 0;
     }
 
+    // levels lc .. coarsest in one launch, one CTA per pair: w.lb[lc] -> w.xa[lc]
+    int fused_tail(int lc) {
+        FusedArgs<T> A;
+        memset(&A, 0, sizeof(A));
+        A.nlev = plan.nlevels - lc;
+        int off = 0;
+        for (int k = 0; k < A.nlev; ++k) {
+            const int l = lc + k;
+            FusedLevel<T>& L = A.lv[k];
+            L.Nx = g[l].Nx; L.Ny = g[l].Ny; L.pitch = g[l].pitch; L.plane = g[l].plane;
+            L.coef = w.coef[l];
+            L.h2 = 1.0 / ((double)(1 << l) * (double)(1 << l));
+            L.npix = g[l].Nx * g[l].Ny;
+            L.smem_off = off;
+            off += 9 * L.npix;
+        }
+        A.b_in = w.lb[lc]; A.x_out = w.xa[lc];
+        A.alpha = alpha; A.beta = beta; A.active = active;
+        A.nu_pre = opt.nu_pre; A.nu_post = opt.nu_post;
+        for (int s = 0; s < 4; ++s) { A.w_pre[s] = w_pre(s); A.w_post[s] = w_post(s); }
+        A.dense = plan.dense ? 1 : 0; A.dense_n = plan.dense_n; A.Minv = w.dense_Minv;
+        A.coarse_sweeps = opt.coarse_sweeps; A.w_coarse = opt.omega;
+        auto kern = k_coarse_vcycle<T>;
+        static bool configured[MAX_DEVICES] = {false};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+        if (!configured[dev]) {
+            OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FUSED_SMEM_BUDGET));
+            configured[dev] = true;
+        }
+        const size_t smem = (size_t)off * sizeof(T);
+        kern<<<B, 1024, smem, stream>>>(A);
+        OFB_CHECK_LAUNCH();
+        return 0;
+    }
+
     // number of buffer swaps a V-cycle on level l performs after the first (zero-guess) sweep
     int swaps() const { return (opt.nu_pre - 1) + opt.nu_post; }
 
@@ -300,7 +351,10 @@ template <typename T> struct Solver {
             OFB_CHECK_LAUNCH();
         }
         T* ec = nullptr;
-        if (lc == plan.nlevels - 1) {
+        if (plan.fused_from > 0 && lc == plan.fused_from) {
+            if ((rc = fused_tail(lc))) return rc;
+            ec = w.xa[lc];
+        } else if (lc == plan.nlevels - 1) {
             if (plan.dense) {
                 const int n = plan.dense_n;
                 k_coarse_solve<T><<<B, 128, n * sizeof(T), stream>>>(n, w.dense_Minv, w.lb[lc], w.xa[lc], g[lc].pair, active);
@@ -350,7 +404,8 @@ int init_solver(Solver<T>& S, const void* P, const double* alpha, const double* 
     if (S.opt.coarse_sweeps < 1) S.opt.coarse_sweeps = 1;
     if (S.opt.check_every < 1) S.opt.check_every = 1;
     S.B = B;
-    S.plan = make_plan(Nx, Ny, S.opt.precond, S.opt.max_levels);
+    S.plan = make_plan(Nx, Ny, S.opt.precond, S.opt.max_levels, sizeof(T));
+    if (S.opt.flags & OFB_FLAG_NO_FUSED_TAIL) S.plan.fused_from = 0;
     S.w = carve<T>(workspace, B, S.plan);
     if (workspace == nullptr || workspace_bytes < S.w.bytes)
         return fail(-4, "workspace too small: need %zu bytes, got %zu", S.w.bytes, workspace_bytes);

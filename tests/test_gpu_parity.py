@@ -271,3 +271,20 @@ def test_streamed_solve_matches_register_solve_and_direct(cuda_device, precond):
         it, rr, cv = engine.solve(Pd, b, x, 1e5, 1e4, rtol=1e-11, max_it=20000, options=engine.make_options(precond, flags=flags))
         assert int(cv[0]) == 1, (flags, int(it[0]), float(rr[0]))
         assert rel(x[0].cpu().numpy(), xd) < 1e-7, flags
+
+
+@pytest.mark.parametrize('shape', [(66, 66), (130, 98), (258, 516)])
+@pytest.mark.parametrize('dtype,tol', [(torch.float64, 1e-11), (torch.float32, 2e-4)])
+def test_fused_coarse_tail_matches_per_level_kernels(cuda_device, shape, dtype, tol):
+    """One V-cycle application with the shared-memory coarse tail == the same cycle run level by level."""
+    from opticalflow_b200 import _lib
+    movie = fo.blur_movie(synthetic.translating_movie(shape[0], shape[1], 3, seed=31), 2.0)
+    rng = np.random.default_rng(4)
+    r = mg.zero_ghosts(rng.standard_normal((2, 3) + shape))
+    Pd, rd = dev_t(movie[:2], cuda_device, dtype), dev_t(r, cuda_device, dtype)
+    alphas, betas = torch.tensor([1e5, 2e4], dtype=torch.float64), torch.tensor([1e4, 1e3], dtype=torch.float64)
+    for cycle in (dict(), dict(nu_pre=2, nu_post=2, omega=0.8)):
+        z_fused = engine.precondition(Pd, rd, alphas, betas, options=engine.make_options('mg', **cycle))
+        z_plain = engine.precondition(Pd, rd, alphas, betas,
+                                      options=engine.make_options('mg', flags=_lib.FLAG_NO_FUSED_TAIL, **cycle))
+        assert rel(z_fused.cpu().double().numpy(), z_plain.cpu().double().numpy()) < tol, cycle

@@ -25,6 +25,8 @@ def main():
     ap.add_argument('--workload', default='rot')
     ap.add_argument('--cycles', default='', help='explicit cycles: "wpre0,wpre1|wpost0,wpost1;..." (per-sweep damping)')
     ap.add_argument('--max-levels', type=int, default=0)
+    ap.add_argument('--coarse-sweeps', type=int, default=30)
+    ap.add_argument('--max-it', type=int, default=200)
     ap.add_argument('--alpha', type=float, default=1e5)
     ap.add_argument('--beta', type=float, default=1e4)
     a = ap.parse_args()
@@ -57,14 +59,14 @@ def main():
     for pre, post, pre_w, post_w in configs:
         om = pre_w[0]
         opts = engine.make_options('mg', nu_pre=pre, nu_post=post, omega=om, omega_pre=pre_w, omega_post=post_w,
-                                   max_levels=a.max_levels)
+                                   max_levels=a.max_levels, coarse_sweeps=a.coarse_sweeps)
         times = []
         for rep in range(3):
             x = torch.zeros_like(b)
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
-            it, rr, cv = engine.solve(P, b, x, alpha, beta, a.rtol, 200, opts, ws)
+            it, rr, cv = engine.solve(P, b, x, alpha, beta, a.rtol, a.max_it, opts, ws)
             e1.record()
             torch.cuda.synchronize()
             times.append(e0.elapsed_time(e1))
