@@ -142,6 +142,8 @@ def run_gpu(args):
     local = int(os.environ.get('LOCAL_RANK', '0'))
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
+    if world > 1:       # one process per GPU shares the host cores: do not oversubscribe them with CPU copy threads
+        torch.set_num_threads(max(2, (os.cpu_count() or 8) // world))
     if world > 1:
         dist.init_process_group('nccl', device_id=dev)
     lib = _lib.load()

@@ -22,7 +22,7 @@ import time
 import numpy as np
 import torch
 
-from . import _lib, engine, hostio
+from . import _lib, engine, hostio, sharding
 
 __all__ = ['variational_optical_flow', 'vary_regularisation', 'blur_movie', 'apply_numerical_derivative',
            'apply_constant_boundary_condition', 'get_index_set', 'format_elapsed_time']
@@ -162,7 +162,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                              smoothing_sigma=None, initial_v_x=0.0, initial_v_y=0.0, initial_remodelling=0.0,
                              use_direct_solver=False, *, dtype='float64', rtol=1e-6, max_it=1000,
                              preconditioner='mg', device=None, batch_pairs=None, verbose=False,
-                             solver_options=None):
+                             solver_options=None, devices=None):
     """Variational optical flow with net remodelling on every consecutive frame pair of ``movie``.
 
     Signature, defaults, units and result keys follow optical_flow.py:715-1210: ``movie[T,Nx,Ny]``; velocities
@@ -170,7 +170,19 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     last pair (:1202) and ``result['speed_functional']`` holds the remodelling functional (:1205).
 
     The frame pairs are processed in chunks of ``batch_pairs``: while the device solves chunk k+1, chunk k's
-    planes travel device -> pinned memory on a copy stream and are widened to float64 by a worker thread."""
+    planes travel device -> pinned memory on a copy stream and are widened to float64 by a worker thread.
+    ``devices=[...]`` shards the pairs over several GPUs (contiguous ranges, one host thread per device, no
+    collective; sharding.py)."""
+    if devices is not None and len(devices) > 1:
+        kw = dict(delta_x=delta_x, delta_t=delta_t, speed_alpha=speed_alpha, remodelling_alpha=remodelling_alpha,
+                  smoothing_sigma=smoothing_sigma, initial_v_x=initial_v_x, initial_v_y=initial_v_y,
+                  initial_remodelling=initial_remodelling, use_direct_solver=use_direct_solver, dtype=dtype, rtol=rtol,
+                  max_it=max_it, preconditioner=preconditioner, batch_pairs=batch_pairs, verbose=verbose,
+                  solver_options=solver_options)
+        return sharding.solve_on_devices(movie, list(devices), lambda frames, dev: variational_optical_flow(frames, device=dev, **kw),
+                                         delta_x, delta_t)
+    if devices is not None and len(devices) == 1:
+        device = devices[0]
     t_start = time.time()
     dev = _device(device)
     tdtype, _ = engine.resolve_dtype(dtype)

@@ -288,3 +288,16 @@ def test_fused_coarse_tail_matches_per_level_kernels(cuda_device, shape, dtype, 
         z_plain = engine.precondition(Pd, rd, alphas, betas,
                                       options=engine.make_options('mg', flags=_lib.FLAG_NO_FUSED_TAIL, **cycle))
         assert rel(z_fused.cpu().double().numpy(), z_plain.cpu().double().numpy()) < tol, cycle
+
+
+def test_devices_argument_shards_pairs_over_threads(cuda_device):
+    """devices=[...] (one host thread per device; here twice the same GPU) == the unsharded call."""
+    movie = synthetic.translating_movie(48, 64, 6, seed=17)
+    kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.0, dtype='float64', rtol=1e-11, max_it=2000)
+    one = optical_flow.variational_optical_flow(movie, **kw)
+    two = optical_flow.variational_optical_flow(movie, devices=['cuda:0', 'cuda:0'], **kw)
+    for key in ('v_x', 'v_y', 'speed', 'remodelling', 'blurred_data', 'original_data'):
+        assert two[key].shape == one[key].shape
+        assert rel(two[key], one[key]) < 1e-9, key
+    assert two['solver_info']['shards'] == [3, 2] and two['converged']
+    assert abs(two['L1_functional'] - one['L1_functional']) < 1e-8 * abs(one['L1_functional'])
