@@ -35,6 +35,7 @@ extern "C" {
 
 #define OFB_FLAG_NO_STREAM 1    /* use the register-only sweep on every level (A/B measurements) */
 #define OFB_FLAG_NO_FUSED_TAIL 2 /* run the small multigrid levels as separate launches (A/B measurements) */
+#define OFB_FLAG_LEGACY_COARSE_BOUNDARY 4 /* node-mirror far boundary on every coarse level (A/B measurements) */
 
 #define OFB_ABI_VERSION 2
 

@@ -12,6 +12,7 @@ OFB_F32, OFB_F64 = 0, 1
 PRECOND_BJACOBI, PRECOND_MG = 0, 1
 FLAG_NO_STREAM = 1
 FLAG_NO_FUSED_TAIL = 2
+FLAG_LEGACY_COARSE_BOUNDARY = 4
 ABI_VERSION = 2
 
 # every symbol include/ofb200.h declares

@@ -24,6 +24,7 @@ template <typename T> struct FusedLevel {
     double h2;                    // hinv^2
     int smem_off;                 // element offset of this level's three vectors (xa, xb, b) in shared memory
     int npix;                     // Nx*Ny (shared-memory planes are unpadded)
+    int far_i, far_j;             // far-side ghost rule (Geom::far_i/far_j)
 };
 
 template <typename T> struct FusedArgs {
@@ -45,9 +46,9 @@ template <typename T> struct FusedArgs {
 
 // store an interior value and its LOAD_SOL ghost copies
 template <typename T>
-__device__ __forceinline__ void store_sol(T* __restrict__ f, int Nx, int Ny, int i, int j, T v) {
+__device__ __forceinline__ void store_sol(T* __restrict__ f, int Nx, int Ny, int far_i, int far_j, int i, int j, T v) {
     f[i * Ny + j] = v;
-    const bool ti = (i == 2), bi = (i == Nx - 3), lj = (j == 2), rj = (j == Ny - 3);
+    const bool ti = (i == 2), bi = (i == Nx - 1 - far_i), lj = (j == 2), rj = (j == Ny - 1 - far_j);
     if (ti) f[j] = v;
     if (bi) f[(Nx - 1) * Ny + j] = v;
     if (lj) f[i * Ny] = v;
@@ -120,9 +121,9 @@ __global__ void __launch_bounds__(1024, 1) k_coarse_vcycle(FusedArgs<T> A) {
             }
             T z0, z1, z2;
             block_solve<T>(cf, a, inv_d2, r0, r1, r2, z0, z1, z2);
-            store_sol<T>(xout, L.Nx, L.Ny, i, j, x0 + w * z0);
-            store_sol<T>(xout + L.npix, L.Nx, L.Ny, i, j, x1 + w * z1);
-            store_sol<T>(xout + 2 * L.npix, L.Nx, L.Ny, i, j, x2 + w * z2);
+            store_sol<T>(xout, L.Nx, L.Ny, L.far_i, L.far_j, i, j, x0 + w * z0);
+            store_sol<T>(xout + L.npix, L.Nx, L.Ny, L.far_i, L.far_j, i, j, x1 + w * z1);
+            store_sol<T>(xout + 2 * L.npix, L.Nx, L.Ny, L.far_i, L.far_j, i, j, x2 + w * z2);
         }
     };
 
@@ -168,10 +169,10 @@ __global__ void __launch_bounds__(1024, 1) k_coarse_vcycle(FusedArgs<T> A) {
                     const T* f = r + q * L.npix;
 #pragma unroll
                     for (int a3 = 0; a3 < 3; ++a3) {
-                        const int ii = reflect_clamped(2 * K - 2 + a3, L.Nx);
+                        const int ii = reflect_clamped(2 * K - 2 + a3, L.Nx, L.far_i);
                         T rowacc = T(0);
 #pragma unroll
-                        for (int b3 = 0; b3 < 3; ++b3) rowacc += w3[b3] * f[ii * L.Ny + reflect_clamped(2 * Lc - 2 + b3, L.Ny)];
+                        for (int b3 = 0; b3 < 3; ++b3) rowacc += w3[b3] * f[ii * L.Ny + reflect_clamped(2 * Lc - 2 + b3, L.Ny, L.far_j)];
                         acc += w3[a3] * rowacc;
                     }
                 }
@@ -215,13 +216,13 @@ __global__ void __launch_bounds__(1024, 1) k_coarse_vcycle(FusedArgs<T> A) {
             const int ni = L.Nx - 2, nj = L.Ny - 2;
             for (int p = tid; p < ni * nj; p += nth) {
                 const int i = 1 + p / nj, j = 1 + p % nj;
-                const int i0 = reflect_clamped((i + 1) >> 1, C.Nx), i1 = reflect_clamped((i + 2) >> 1, C.Nx);
-                const int j0 = reflect_clamped((j + 1) >> 1, C.Ny), j1 = reflect_clamped((j + 2) >> 1, C.Ny);
+                const int i0 = reflect_clamped((i + 1) >> 1, C.Nx, C.far_i), i1 = reflect_clamped((i + 2) >> 1, C.Nx, C.far_i);
+                const int j0 = reflect_clamped((j + 1) >> 1, C.Ny, C.far_j), j1 = reflect_clamped((j + 2) >> 1, C.Ny, C.far_j);
 #pragma unroll
                 for (int q = 0; q < 3; ++q) {
                     const T* c = e + q * C.npix;
                     const T d = T(0.25) * (c[i0 * C.Ny + j0] + c[i0 * C.Ny + j1] + c[i1 * C.Ny + j0] + c[i1 * C.Ny + j1]);
-                    store_sol<T>(x + q * L.npix, L.Nx, L.Ny, i, j, x[q * L.npix + i * L.Ny + j] + d);
+                    store_sol<T>(x + q * L.npix, L.Nx, L.Ny, L.far_i, L.far_j, i, j, x[q * L.npix + i * L.Ny + j] + d);
                 }
             }
         }

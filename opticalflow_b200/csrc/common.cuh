@@ -25,6 +25,9 @@ struct Geom {
     long long pair;              // elements between batch entries (vectors: 3*plane or more)
     long long img_pair;          // elements between batch entries for single-plane images
     int aligned;                 // 1 if every row start is 16-byte aligned (pitch % V == 0 and base aligned)
+    int far_i, far_j;            // far-side ghost rule per axis: ghost(N-1) = q(N-1-far); 2 = mirror about the last
+                                 // interior node (the reference's rule, level 0), 1 = mirror about the half point
+                                 // beyond it (coarse levels whose fine parent has an even number of interior nodes)
 };
 
 // ghost-ring handling when a plane is read
@@ -35,6 +38,9 @@ enum LoadMode { LOAD_RAW = 0,    // values as stored (images, right-hand sides)
 
 __device__ __forceinline__ int mirror_index(int i, int N) {
     return i == 0 ? 2 : (i == N - 1 ? N - 3 : i);
+}
+__device__ __forceinline__ int mirror_far(int i, int N, int far) {
+    return i == 0 ? 2 : (i == N - 1 ? N - 1 - far : i);
 }
 
 // One row of one plane as seen by a lane: v[0] = left halo (column j0-1), v[1..V] own columns,
@@ -112,23 +118,17 @@ __device__ __forceinline__ void load_row_ptr(Row<T>& r, const T* __restrict__ ro
         r.v[V + 1] = right;
     }
     if (MODE != LOAD_RAW && edge_warp) {
-        if (g.Ny % V == 0) {
-            // ghost columns 0 and Ny-1 are the first / last own column of a lane; their mirror columns
-            // 2 and Ny-3 are already in the lane's window
-            if (j0 == 0) r.v[1] = (MODE == LOAD_SOL && ghost_row) ? r.v[3] + r.v[3] : r.v[3];
-            if (j0 + V == g.Ny) r.v[V] = (MODE == LOAD_SOL && ghost_row) ? r.v[V - 2] + r.v[V - 2] : r.v[V - 2];
-        } else {
+        // ghost columns are patched in registers from the lane's own window: column 0 <- column 2,
+        // column Ny-1 <- column Ny-1-far_j (window index kg = Ny - j0, mirror at kg - far_j)
+        if (j0 == 0) r.v[1] = (MODE == LOAD_SOL && ghost_row) ? r.v[3] + r.v[3] : r.v[3];
+        if (j0 == 1) r.v[0] = (MODE == LOAD_SOL && ghost_row) ? r.v[2] + r.v[2] : r.v[2];
+        const int kg = g.Ny - j0;
 #pragma unroll
-            for (int k = 0; k < V + 2; ++k) {
-                int j = j0 - 1 + k;
-                bool ghost_col = (j == 0) || (j == g.Ny - 1);
-                if (ghost_col) {
-                    T t = rowptr[mirror_index(j, g.Ny)];
-                    if (MODE == LOAD_SOL && ghost_row) t = t + t;
-                    r.v[k] = t;
-                }
+        for (int k = 2; k <= V + 1; ++k)
+            if (kg == k) {
+                const T t = (g.far_j == 2) ? r.v[k - 2] : r.v[k - 1];
+                r.v[k] = (MODE == LOAD_SOL && ghost_row) ? t + t : t;
             }
-        }
     }
 }
 
@@ -137,7 +137,7 @@ template <typename T, int MODE>
 __device__ __forceinline__ void load_row(Row<T>& r, const T* __restrict__ plane, int i, int j0,
                                          const Geom& g, int lane, bool edge_warp) {
     int row = i;
-    if (MODE != LOAD_RAW) row = mirror_index(i, g.Nx);
+    if (MODE != LOAD_RAW) row = mirror_far(i, g.Nx, g.far_i);
     row = min(max(row, 0), g.Nx - 1);
     load_row_ptr<T, MODE, false>(r, plane + (long long)row * g.pitch, (i == 0) || (i == g.Nx - 1), j0, g, lane, edge_warp);
 }

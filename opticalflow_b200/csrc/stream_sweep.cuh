@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                     int row;
                     if (is_win) {
                         row = i_begin - 1 + k;
-                        if (is_sol) row = mirror_index(row, g.Nx);
+                        if (is_sol) row = mirror_far(row, g.Nx, g.far_i);
                         row = min(max(row, 0), g.Nx - 1);
                     } else {
                         row = i_begin - 2 + k;

@@ -8,9 +8,9 @@ namespace ofb {
 
 __host__ __device__ __forceinline__ int coarse_size(int N) { return (N + 3) / 2; }
 
-__device__ __forceinline__ int reflect_clamped(int i, int N) {
+__device__ __forceinline__ int reflect_clamped(int i, int N, int far = 2) {
     i = min(max(i, 0), N - 1);
-    return mirror_index(i, N);
+    return mirror_far(i, N, far);
 }
 
 // Level-1 coefficient planes straight from the image: full weighting (1/4,1/2,1/4)^2 of the
@@ -64,8 +64,8 @@ __global__ void k_restrict(Geom gf, const T* __restrict__ fine, long long fine_p
     int ii[3], jj[3];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-        ii[d] = reflect_clamped(2 * K - 2 + d, gf.Nx);
-        jj[d] = reflect_clamped(2 * L - 2 + d, gf.Ny);
+        ii[d] = reflect_clamped(2 * K - 2 + d, gf.Nx, gf.far_i);
+        jj[d] = reflect_clamped(2 * L - 2 + d, gf.Ny, gf.far_j);
     }
     const T w3[3] = {T(0.25), T(0.5), T(0.25)};
     const T scale[NCOEF] = {T(0.25), T(0.5), T(1), T(1), T(1), T(0.5), T(1)};
@@ -96,8 +96,8 @@ __global__ void k_prolong_add(Geom gc, const T* __restrict__ coarse, Geom gf, T*
     if (j >= gf.Ny) return;
     if (active != nullptr && !active[pair]) return;
     if (i == 0 || i == gf.Nx - 1 || j == 0 || j == gf.Ny - 1) return;
-    const int i0 = reflect_clamped((i + 1) >> 1, gc.Nx), i1 = reflect_clamped((i + 2) >> 1, gc.Nx);
-    const int j0 = reflect_clamped((j + 1) >> 1, gc.Ny), j1 = reflect_clamped((j + 2) >> 1, gc.Ny);
+    const int i0 = reflect_clamped((i + 1) >> 1, gc.Nx, gc.far_i), i1 = reflect_clamped((i + 2) >> 1, gc.Nx, gc.far_i);
+    const int j0 = reflect_clamped((j + 1) >> 1, gc.Ny, gc.far_j), j1 = reflect_clamped((j + 2) >> 1, gc.Ny, gc.far_j);
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
         const T* c = coarse + (long long)pair * gc.pair + (long long)q * gc.plane;
@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(1024) k_coarse_setup(Geom g, const T* __restri
         const bool ghost = (i == 0) || (i == g.Nx - 1) || (j == 0) || (j == g.Ny - 1);
         if (ghost) {
             if (cp == rp) y[cq] = 1.0;
-        } else if (abs(mirror_index(ci, g.Nx) - i) <= 1 || abs(ci - i) <= 1) {
+        } else if (abs(ci - i) <= 2) {
             Coef<double> c;
             const long long o = (long long)i * g.pitch + j;
             c.II = cf[o]; c.IIx = cf[g.plane + o]; c.IIxx = cf[2 * g.plane + o]; c.IIyy = cf[3 * g.plane + o];
@@ -152,7 +152,7 @@ __global__ void __launch_bounds__(1024) k_coarse_setup(Geom g, const T* __restri
                 // value of the unit vector e_col at (q,ii,jj) as the eliminated operator sees it
                 if (q != cq) return 0.0;
                 const bool gr = (ii == 0) || (ii == g.Nx - 1), gc2 = (jj == 0) || (jj == g.Ny - 1);
-                const int mi = mirror_index(ii, g.Nx), mj = mirror_index(jj, g.Ny);
+                const int mi = mirror_far(ii, g.Nx, g.far_i), mj = mirror_far(jj, g.Ny, g.far_j);
                 if (mi != ci || mj != cj) return 0.0;
                 if (ci == 0 || ci == g.Nx - 1 || cj == 0 || cj == g.Ny - 1) return 0.0;   // ghost unknowns are slaved
                 return (gr && gc2) ? 2.0 : 1.0;

@@ -23,21 +23,37 @@ _NATIVE = {np.dtype(np.uint8): torch.uint8, np.dtype(np.int8): torch.int8, np.dt
            np.dtype(np.float32): torch.float32, np.dtype(np.float64): torch.float64,
            np.dtype(np.uint16): torch.uint16, np.dtype(np.bool_): torch.bool}
 
-_pinned_cache = {}
-_pinned_lock = threading.Lock()
+class PinnedPool:
+    """Process-wide pool of pinned staging tensors.  cudaHostAlloc is slow, so buffers are kept and reused across
+    calls; a call checks buffers out and returns them, so concurrent calls (one host thread per device, or two
+    calls on the same device) never share a staging buffer."""
+
+    def __init__(self):
+        self.free = []
+        self.lock = threading.Lock()
+
+    def acquire(self, shape, dtype):
+        nbytes = int(np.prod(shape)) * torch.empty((), dtype=dtype).element_size()
+        with self.lock:
+            best = None
+            for k, buf in enumerate(self.free):
+                if buf.numel() >= nbytes and (best is None or buf.numel() < self.free[best].numel()):
+                    best = k
+            raw = self.free.pop(best) if best is not None else None
+        if raw is None:
+            raw = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        view = raw[:nbytes].view(dtype).view(shape)
+        view._ofb_raw = raw
+        return view
+
+    def release(self, view):
+        raw = getattr(view, '_ofb_raw', None)
+        if raw is not None:
+            with self.lock:
+                self.free.append(raw)
 
 
-def pinned_buffer(tag, shape, dtype):
-    """Process-wide cache of pinned staging tensors (cudaHostAlloc is slow; the buffers are reused across calls).
-
-    Buffers are keyed by `tag`; a larger request replaces the cached one."""
-    n = int(np.prod(shape))
-    with _pinned_lock:
-        buf = _pinned_cache.get((tag, dtype))
-        if buf is None or buf.numel() < n:
-            buf = torch.empty(n, dtype=dtype, pin_memory=True)
-            _pinned_cache[(tag, dtype)] = buf
-    return buf[:n].view(shape)
+pinned_pool = PinnedPool()
 
 
 def as_native_tensor(array):
@@ -51,25 +67,31 @@ def as_native_tensor(array):
     return torch.from_numpy(array.astype(np.float64))
 
 
-_last_upload = {}
+class FrameUploader:
+    """Host frames -> device through one pinned staging buffer owned by the call (native dtype on the wire)."""
 
+    def __init__(self, max_frames, frame_shape, np_dtype, device):
+        probe = as_native_tensor(np.zeros((1,), dtype=np_dtype))
+        self.wire_dtype = torch.int32 if probe.dtype == torch.uint16 else probe.dtype   # no CUDA kernels for uint16
+        self.stage = pinned_pool.acquire((max_frames,) + tuple(frame_shape), self.wire_dtype)
+        self.device = device
+        self.last = None
 
-def upload_frames(frames_np, device, tdtype, tag='ingest'):
-    """Host frames [F,Nx,Ny] (any numeric dtype) -> device tensor of the compute dtype, through pinned staging."""
-    src = as_native_tensor(frames_np)
-    if src.dtype == torch.uint16:                       # no CUDA kernels for uint16 in torch: widen losslessly on the host
-        src = src.to(torch.int32)
-    key = (tag, str(device))
-    previous = _last_upload.get(key)
-    if previous is not None:
-        previous.synchronize()                          # the staging buffer is free once the previous copy has completed
-    stage = pinned_buffer(key, tuple(src.shape), src.dtype)
-    stage.copy_(src)                                    # multi-threaded host copy into pinned memory
-    dev = stage.to(device, non_blocking=True)
-    done = torch.cuda.Event()
-    done.record(torch.cuda.current_stream(device))
-    _last_upload[key] = done
-    return dev if dev.dtype == tdtype else dev.to(tdtype)
+    def upload(self, frames_np, tdtype):
+        src = as_native_tensor(frames_np)
+        if self.last is not None:
+            self.last.synchronize()                     # the staging buffer is free once the previous copy has completed
+        stage = self.stage[:src.shape[0]]
+        stage.copy_(src)                                # (multi-threaded) host copy / widening into pinned memory
+        dev = stage.to(self.device, non_blocking=True)
+        self.last = torch.cuda.Event()
+        self.last.record(torch.cuda.current_stream(self.device))
+        return dev if dev.dtype == tdtype else dev.to(tdtype)
+
+    def close(self):
+        if self.last is not None:
+            self.last.synchronize()
+        pinned_pool.release(self.stage)
 
 
 class EgressWorker:

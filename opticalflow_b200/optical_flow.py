@@ -214,11 +214,11 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     main_stream = torch.cuda.current_stream(dev)
     copy_stream = _copy_stream(dev)
     worker = hostio.EgressWorker()
+    uploader = hostio.FrameUploader(B + 1, (Nx, Ny), source.dtype, dev)
     slots = []                                                                 # double-buffered device + pinned planes
     for s in range(2):
         slots.append(dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev),
-                          pin=hostio.pinned_buffer(('egress', s, str(dev)), (nplanes, B + 1, Nx, Ny), tdtype),
-                          busy=None))
+                          pin=hostio.pinned_pool.acquire((nplanes, B + 1, Nx, Ny), tdtype), busy=None))
     try:
         pending = worker.submit(None, [(original, hostio.as_native_tensor(source))])
         stats = []
@@ -228,7 +228,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
             slot = slots[c % 2]
             if slot['busy'] is not None:
                 slot['busy'].wait()                                            # worker has drained this slot's pinned planes
-            frames = hostio.upload_frames(source[k0:k1 + 1], dev, tdtype)      # nb+1 frames
+            frames = uploader.upload(source[k0:k1 + 1], tdtype)                # nb+1 frames
             if blur:
                 frames = engine.blur(frames, smoothing_sigma, out=slot['dev'][4, :nb + 1])     # :770-771
             P, C = frames[:-1], frames[1:]
@@ -270,6 +270,11 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                 slot['busy'].wait()
     finally:
         worker.close()
+        torch.cuda.current_stream(dev).synchronize()
+        copy_stream.synchronize()
+        uploader.close()
+        for slot in slots:
+            hostio.pinned_pool.release(slot['pin'])
     if verbose and not info['converged'].all():
         print('the solver has not actually converged, the result will be incorrect or inaccurate')
     result = dict()
