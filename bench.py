@@ -196,10 +196,10 @@ def run_gpu(args):
     assert int(stats['conv'].sum()) == B, 'not every pair converged: %s' % stats['conv'].tolist()
 
     # ---- e2e: the public drop-in, host numpy in / host float64 numpy out, every copy inside the timed region.
-    # A 4B+1-frame movie (the B+1 generated frames played forwards and backwards: every pair is a valid d-3 pair)
+    # An 8B+1-frame movie (the B+1 generated frames played forwards and backwards: every pair is a valid d-3 pair)
     # so that the drop-in's chunk pipeline (solve chunk k+1 while chunk k's planes go device -> host) is exercised
     # the way a 500-frame movie would exercise it.
-    zigzag = np.concatenate([np.arange(0, B + 1), np.arange(B - 1, -1, -1), np.arange(1, B + 1), np.arange(B - 1, -1, -1)])
+    zigzag = np.concatenate([np.arange(0, B + 1), np.arange(B - 1, -1, -1)] + [np.arange(1, B + 1), np.arange(B - 1, -1, -1)] * 3)
     movie_e2e = np.ascontiguousarray(movie[zigzag])
     pairs_e2e = movie_e2e.shape[0] - 1
 

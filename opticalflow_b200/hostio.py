@@ -14,6 +14,7 @@ PyTorch is plumbing here (pinned memory, streams, events); no arithmetic of the 
 """
 import queue
 import threading
+import time
 
 import numpy as np
 import torch
@@ -22,6 +23,45 @@ _NATIVE = {np.dtype(np.uint8): torch.uint8, np.dtype(np.int8): torch.int8, np.dt
            np.dtype(np.int32): torch.int32, np.dtype(np.int64): torch.int64, np.dtype(np.float16): torch.float16,
            np.dtype(np.float32): torch.float32, np.dtype(np.float64): torch.float64,
            np.dtype(np.uint16): torch.uint16, np.dtype(np.bool_): torch.bool}
+
+_copy_pool = None
+_copy_pool_lock = threading.Lock()
+
+
+def copy_pool():
+    """Process-wide pool of plain host threads for memory-bound copies/widenings.  numpy releases the GIL inside
+    copyto, and these threads block on a queue when idle - unlike OpenMP teams started from several Python
+    threads, whose spin-waiting starved the thread that launches the kernels."""
+    global _copy_pool
+    with _copy_pool_lock:
+        if _copy_pool is None:
+            import concurrent.futures
+            import os
+            _copy_pool = concurrent.futures.ThreadPoolExecutor(max_workers=max(2, (os.cpu_count() or 8) - 2),
+                                                               thread_name_prefix='ofb-copy')
+    return _copy_pool
+
+
+def parallel_copy(pairs, piece_bytes=4 << 20):
+    """copyto(dst, src, casting='unsafe') for every (dst, src) pair of equally shaped C-contiguous arrays, cut into
+    ~piece_bytes pieces that the copy pool works through concurrently.  Returns when all pieces are done."""
+    pool = copy_pool()
+    futures = []
+    for dst, src in pairs:
+        d, s_ = dst.reshape(-1), src.reshape(-1)
+        step = max(1, piece_bytes // max(1, d.itemsize))
+        for a in range(0, d.size, step):
+            futures.append(pool.submit(np.copyto, d[a:a + step], s_[a:a + step], 'unsafe'))
+    for f in futures:
+        f.result()
+
+
+def _helper_threads(divisor):
+    """CPU copy threads for a helper thread: a share of the cores, so that ingest, egress and the kernel-launching
+    thread do not oversubscribe the host."""
+    import os
+    return max(2, (os.cpu_count() or 8) // divisor)
+
 
 class PinnedPool:
     """Process-wide pool of pinned staging tensors.  cudaHostAlloc is slow, so buffers are kept and reused across
@@ -68,30 +108,63 @@ def as_native_tensor(array):
 
 
 class FrameUploader:
-    """Host frames -> device through one pinned staging buffer owned by the call (native dtype on the wire)."""
+    """Host frames -> device through two pinned staging buffers owned by the call (native dtype on the wire).
+
+    `prefetch(frames)` runs on a helper thread: host copy into pinned memory, then an asynchronous H2D copy on a
+    dedicated upload stream - so the next chunk's frames arrive while the device is still solving the current
+    chunk (the calling thread is blocked inside the solver, which releases the GIL).  `take(tdtype)` hands the
+    prefetched frames to the compute stream."""
 
     def __init__(self, max_frames, frame_shape, np_dtype, device):
         probe = as_native_tensor(np.zeros((1,), dtype=np_dtype))
         self.wire_dtype = torch.int32 if probe.dtype == torch.uint16 else probe.dtype   # no CUDA kernels for uint16
-        self.stage = pinned_pool.acquire((max_frames,) + tuple(frame_shape), self.wire_dtype)
+        self.stages = [pinned_pool.acquire((max_frames,) + tuple(frame_shape), self.wire_dtype) for _ in range(2)]
+        self.events = [None, None]
         self.device = device
-        self.last = None
+        self.stream = torch.cuda.Stream(device)
+        self.turn = 0
+        self.pending = None
+        self.error = None
 
-    def upload(self, frames_np, tdtype):
-        src = as_native_tensor(frames_np)
-        if self.last is not None:
-            self.last.synchronize()                     # the staging buffer is free once the previous copy has completed
-        stage = self.stage[:src.shape[0]]
-        stage.copy_(src)                                # (multi-threaded) host copy / widening into pinned memory
-        dev = stage.to(self.device, non_blocking=True)
-        self.last = torch.cuda.Event()
-        self.last.record(torch.cuda.current_stream(self.device))
+    def _upload(self, frames_np, slot):
+        try:
+            src = np.ascontiguousarray(frames_np)
+            if self.events[slot] is not None:
+                self.events[slot].synchronize()         # the staging buffer is free once its previous copy has completed
+            stage = self.stages[slot][:src.shape[0]]
+            parallel_copy([(stage.numpy(), src)])       # host copy / widening into pinned memory on the copy pool
+            with torch.cuda.stream(self.stream):
+                dev = stage.to(self.device, non_blocking=True)
+                event = torch.cuda.Event()
+                event.record(self.stream)
+            self.events[slot] = event
+            self.result = (dev, event)
+        except Exception as exc:
+            self.error = exc
+
+    def prefetch(self, frames_np):
+        slot = self.turn
+        self.turn ^= 1
+        self.pending = threading.Thread(target=self._upload, args=(frames_np, slot), daemon=True)
+        self.pending.start()
+
+    def take(self, tdtype):
+        self.pending.join()
+        self.pending = None
+        if self.error is not None:
+            raise self.error
+        dev, event = self.result
+        main = torch.cuda.current_stream(self.device)
+        main.wait_event(event)
+        dev.record_stream(main)
         return dev if dev.dtype == tdtype else dev.to(tdtype)
 
     def close(self):
-        if self.last is not None:
-            self.last.synchronize()
-        pinned_pool.release(self.stage)
+        if self.pending is not None:
+            self.pending.join()
+        self.stream.synchronize()
+        for stage in self.stages:
+            pinned_pool.release(stage)
 
 
 class EgressWorker:
@@ -100,6 +173,7 @@ class EgressWorker:
     def __init__(self):
         self.tasks = queue.Queue()
         self.error = None
+        self.log = []                                   # (seconds waiting for the device copy, seconds widening) per task
         self.thread = threading.Thread(target=self._run, daemon=True)
         self.thread.start()
 
@@ -110,10 +184,12 @@ class EgressWorker:
                 return
             event, copies, done = task
             try:
+                t0 = time.perf_counter()
                 if event is not None:
                     event.synchronize()
-                for dst_np, src_t in copies:
-                    torch.from_numpy(dst_np).copy_(src_t)
+                t1 = time.perf_counter()
+                parallel_copy([(dst_np, src_t.numpy() if isinstance(src_t, torch.Tensor) else src_t) for dst_np, src_t in copies])
+                self.log.append((t1 - t0, time.perf_counter() - t1))
             except Exception as exc:                    # surfaced by close()
                 self.error = exc
             finally:

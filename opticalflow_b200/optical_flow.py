@@ -219,8 +219,10 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     for s in range(2):
         slots.append(dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev),
                           pin=hostio.pinned_pool.acquire((nplanes, B + 1, Nx, Ny), tdtype), busy=None))
+    timeline = []
+    t_setup = time.time()
     try:
-        pending = worker.submit(None, [(original, hostio.as_native_tensor(source))])
+        uploader.prefetch(source[0:min(B, n_pairs) + 1])
         stats = []
         for c, k0 in enumerate(range(0, n_pairs, B)):
             k1 = min(k0 + B, n_pairs)
@@ -228,15 +230,21 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
             slot = slots[c % 2]
             if slot['busy'] is not None:
                 slot['busy'].wait()                                            # worker has drained this slot's pinned planes
-            frames = uploader.upload(source[k0:k1 + 1], tdtype)                # nb+1 frames
+            t_chunk = time.perf_counter()
+            frames = uploader.take(tdtype)                                     # nb+1 frames, uploaded during the previous solve
+            t_take = time.perf_counter()
+            if k1 < n_pairs:
+                uploader.prefetch(source[k1:min(k1 + B, n_pairs) + 1])
             if blur:
                 frames = engine.blur(frames, smoothing_sigma, out=slot['dev'][4, :nb + 1])     # :770-771
             P, C = frames[:-1], frames[1:]
             x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
             for q in range(3):
                 x0[:, q] = guess[q]
+            t_prep = time.perf_counter()
             x, iters, relres, conv, fb = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
                                                       preconditioner, workspace, solver_options)
+            t_solve = time.perf_counter()
             fields = slot['dev'][:4, :nb]
             _, _, _, _, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out, out=fields)
             ready = torch.cuda.Event()
@@ -253,21 +261,26 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
             copies = [(out[name][k0:k1], slot['pin'][q, :nb]) for q, name in enumerate(('v_x', 'v_y', 'speed', 'remodelling'))]
             if blur:
                 copies.append((blurred[k0:k0 + last_frame], slot['pin'][4, :last_frame]))
+            copies.append((original[k0:k0 + last_frame], source[k0:k0 + last_frame]))      # float64 copy of the input (:769)
             slot['busy'] = worker.submit(copied, copies)       # slot reuse (two chunks later) waits for this on the host
-            stats.append((k0, k1, fun, iters, relres, conv, fb))
-        for k0, k1, fun, iters, relres, conv, fb in stats:
-            functionals[k0:k1] = fun.cpu().numpy()
-            info['iterations'][k0:k1] = iters.cpu().numpy()
-            info['relative_residual'][k0:k1] = relres.cpu().numpy()
-            info['converged'][k0:k1] = conv.cpu().numpy() != 0
-            info['fallback'][k0:k1] = fb.cpu().numpy()
-            if verbose:
-                print('pairs %d..%d: iterations %s, residuals %s' % (k0 + 1, k1, info['iterations'][k0:k1],
-                                                                       info['relative_residual'][k0:k1]))
-        pending.wait()
+            stats.append(torch.cat([fun, iters.double()[:, None], relres[:, None], conv.double()[:, None],
+                                    fb.double()[:, None]], dim=1))
+            timeline.append(dict(chunk=c, wait_slot_and_frames=t_take - t_chunk, prepare=t_prep - t_take,
+                                 solve=t_solve - t_prep, submit=time.perf_counter() - t_solve))
+        t_loop = time.perf_counter()
+        packed = torch.cat(stats, dim=0).cpu().numpy()                         # one device->host read for all diagnostics
+        functionals[:] = packed[:, 0:3]
+        info['iterations'][:] = packed[:, 3].astype(np.int32)
+        info['relative_residual'][:] = packed[:, 4]
+        info['converged'][:] = packed[:, 5] != 0
+        info['fallback'][:] = packed[:, 6] != 0
+        if verbose:
+            print('iterations %s, residuals %s' % (info['iterations'], info['relative_residual']))
+        t_stats = time.perf_counter()
         for slot in slots:
             if slot['busy'] is not None:
                 slot['busy'].wait()
+        timeline.append(dict(stats=t_stats - t_loop, drain=time.perf_counter() - t_stats, setup=t_setup - t_start))
     finally:
         worker.close()
         torch.cuda.current_stream(dev).synchronize()
@@ -294,6 +307,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info['elapsed_seconds'] = time.time() - t_start
     info['dtype'] = str(tdtype).replace('torch.', '')
     info['batch_pairs'] = B
+    info['timeline'] = timeline
+    info['egress_log'] = list(worker.log)
     info['h2d_bytes'] = int(sum(min(k0 + B, n_pairs) - k0 + 1 for k0 in range(0, n_pairs, B)) * source[0].nbytes)
     info['d2h_bytes'] = int((4 * n_pairs + (T if blur else 0)) * Nx * Ny * itemsize)
     result['solver_info'] = info
