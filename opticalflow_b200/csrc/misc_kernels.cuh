@@ -26,6 +26,76 @@ __global__ void k_blur_axis(const T* __restrict__ in, T* __restrict__ out, int N
     out[(long long)blockIdx.z * frame_stride + (long long)i * Ny + j] = acc;
 }
 
+// Tiled two-pass variant (the path used for radius <= 64): one CTA blurs a 128-column x TH-row tile of one frame.
+// Pass 1: each warp stages one input row segment (+radius halo columns, clamp-to-edge) in shared memory with
+// coalesced loads and writes its horizontally blurred row into the tile buffer H[(TH + 2 radius)][128]
+// (lane-strided columns: conflict-free).  Pass 2: every thread combines 2 radius + 1 rows of H for four adjacent
+// columns with 16-byte shared loads and stores 16 bytes.  The frame is read ~(TH + 2r)/TH times (L2 absorbs the
+// halo rows) and written once; nothing goes to global memory between the passes.
+constexpr int BLUR_BW = 128;        // tile width in columns
+constexpr int BLUR_WARPS = 8;
+template <typename T>
+__global__ void __launch_bounds__(BLUR_WARPS * 32) k_blur_tile(const T* __restrict__ in, T* __restrict__ out, int Nx, int Ny,
+                                                              long long frame_stride, const double* __restrict__ weights,
+                                                              int radius, int TH, int vec_ok) {
+    extern __shared__ __align__(16) unsigned char blur_smem[];
+    const int taps = 2 * radius + 1;
+    const int hrows = TH + 2 * radius;
+    T* H = reinterpret_cast<T*>(blur_smem);                       // [hrows][BLUR_BW]
+    T* rowbuf = H + (size_t)hrows * BLUR_BW;                      // [BLUR_WARPS][BLUR_BW + 2 radius]
+    T* w = rowbuf + (size_t)BLUR_WARPS * (BLUR_BW + 2 * radius);  // [taps]
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = blockIdx.x * BLUR_BW, i0 = blockIdx.y * TH;
+    const T* f = in + (long long)blockIdx.z * frame_stride;
+    for (int k = threadIdx.x; k < taps; k += blockDim.x) w[k] = T(weights[k]);
+    __syncthreads();
+    // ---- pass 1: horizontal
+    T* rb = rowbuf + (size_t)warp * (BLUR_BW + 2 * radius);
+    for (int rr = warp; rr < hrows; rr += BLUR_WARPS) {
+        const int src_row = min(max(i0 - radius + rr, 0), Nx - 1);
+        const T* srow = f + (long long)src_row * Ny;
+        for (int e = lane; e < BLUR_BW + 2 * radius; e += 32) rb[e] = srow[min(max(c0 - radius + e, 0), Ny - 1)];
+        __syncwarp();
+#pragma unroll
+        for (int q = 0; q < BLUR_BW / 32; ++q) {
+            const int col = lane + 32 * q;
+            T acc = T(0);
+            for (int k = 0; k < taps; ++k) acc += w[k] * rb[col + k];
+            H[(size_t)rr * BLUR_BW + col] = acc;
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    // ---- pass 2: vertical, four columns per thread
+    constexpr int V4 = 4;
+    const int cg = threadIdx.x % (BLUR_BW / V4), rg = threadIdx.x / (BLUR_BW / V4);
+    const int rgs = (BLUR_WARPS * 32) / (BLUR_BW / V4);
+    const int j = c0 + cg * V4;
+    for (int r = rg; r < TH; r += rgs) {
+        const int i = i0 + r;
+        if (i >= Nx || j >= Ny) continue;
+        T acc[V4] = {T(0), T(0), T(0), T(0)};
+        for (int k = 0; k < taps; ++k) {
+            const T* hp = H + (size_t)(r + k) * BLUR_BW + cg * V4;
+            const T wk = w[k];
+#pragma unroll
+            for (int c = 0; c < V4; ++c) acc[c] += wk * hp[c];
+        }
+        T* op = out + (long long)blockIdx.z * frame_stride + (long long)i * Ny + j;
+        if (vec_ok && j + V4 <= Ny) {
+            if constexpr (sizeof(T) == 4) {
+                *reinterpret_cast<float4*>(op) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+            } else {
+                *reinterpret_cast<double2*>(op) = make_double2(acc[0], acc[1]);
+                *reinterpret_cast<double2*>(op + 2) = make_double2(acc[2], acc[3]);
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < V4; ++c) if (j + c < Ny) op[c] = acc[c];
+        }
+    }
+}
+
 // ------------------------------------------------------------------ K2 right-hand side
 // b = (-I*Ixt, -I*Iyt, -It) on the interior, 0 on the ghost ring (optical_flow.py:815-823,:889,:938,:962).
 template <typename T>

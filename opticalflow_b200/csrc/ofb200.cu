@@ -315,7 +315,21 @@ template <typename T> struct Solver {
         if (plan.dense) {
             const int l = plan.nlevels - 1;
             const double h2 = 1.0 / ((double)(1 << l) * (double)(1 << l));
-            k_coarse_setup<T><<<B, 1024, 0, stream>>>(g[l], w.coef[l], alpha, beta, h2, w.dense_M, w.dense_Minv, w.dense_piv);
+            const size_t mbytes = (size_t)plan.dense_n * plan.dense_n * sizeof(double);
+            const int use_smem = mbytes <= 200 * 1024 ? 1 : 0;
+            auto kern = k_coarse_setup<T>;
+            if (use_smem) {
+                static bool configured[MAX_DEVICES] = {false};
+                int dev = 0;
+                cudaGetDevice(&dev);
+                dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+                if (!configured[dev]) {
+                    OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+                    configured[dev] = true;
+                }
+            }
+            kern<<<B, 1024, use_smem ? mbytes : 0, stream>>>(g[l], w.coef[l], alpha, beta, h2, w.dense_M, w.dense_Minv, w.dense_piv,
+                                                             use_smem);
             OFB_CHECK_LAUNCH();
         }
         return 0;
@@ -396,9 +410,20 @@ template <typename T> struct Solver {
             if ((rc = vcycle(lc, w.lb[lc], w.xa[lc], w.xb[lc], &ec))) return rc;
         }
         {
-            dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
-            k_prolong_add<T><<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
-            OFB_CHECK_LAUNCH();
+            if constexpr (sizeof(T) == 4) {
+                if (g[l].aligned && g[l].Ny % 4 == 0) {
+                    dim3 block(128), grid((g[l].Ny / 4 + 127) / 128, g[l].Nx, B);
+                    k_prolong_add4<<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
+                    OFB_CHECK_LAUNCH();
+                    goto prolonged;
+                }
+            }
+            {
+                dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
+                k_prolong_add<T><<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
+                OFB_CHECK_LAUNCH();
+            }
+        prolonged:;
         }
         for (int s = 0; s < opt.nu_post; ++s) { if ((rc = smooth(l, b, cur, alt, w_post(s)))) return rc; std::swap(cur, alt); }
         *out = cur;
@@ -553,8 +578,31 @@ namespace {
 
 template <typename T>
 int blur_impl(const void* in, void* out, void* tmp, const double* weights, int radius, int F, int Nx, int Ny, cudaStream_t stream) {
-    dim3 block(128), grid((Ny + 127) / 128, Nx, F);
     const long long fs = (long long)Nx * Ny;
+    if (radius <= 64) {
+        // tiled two-pass kernel: pick the tallest tile whose buffers stay under ~96 KB of shared memory
+        int TH = 64;
+        auto smem_for = [&](int th) {
+            return ((size_t)(th + 2 * radius) * BLUR_BW + (size_t)BLUR_WARPS * (BLUR_BW + 2 * radius) + (2 * radius + 1)) * sizeof(T);
+        };
+        while (TH > 8 && smem_for(TH) > 96 * 1024) TH /= 2;
+        TH = std::min(TH, std::max(8, (Nx + 7) / 8 * 8));
+        auto kern = k_blur_tile<T>;
+        static bool configured[MAX_DEVICES] = {false};
+        int dev = 0;
+        cudaGetDevice(&dev);
+        dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+        if (!configured[dev]) {
+            OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+            configured[dev] = true;
+        }
+        const int vec_ok = (Ny % 4 == 0 && ptr_aligned16(out)) ? 1 : 0;
+        dim3 grid((Ny + BLUR_BW - 1) / BLUR_BW, (Nx + TH - 1) / TH, F);
+        kern<<<grid, BLUR_WARPS * 32, smem_for(TH), stream>>>((const T*)in, (T*)out, Nx, Ny, fs, weights, radius, TH, vec_ok);
+        OFB_CHECK_LAUNCH();
+        return 0;
+    }
+    dim3 block(128), grid((Ny + 127) / 128, Nx, F);
     k_blur_axis<T, 0><<<grid, block, 0, stream>>>((const T*)in, (T*)tmp, Nx, Ny, fs, weights, radius);
     OFB_CHECK_LAUNCH();
     k_blur_axis<T, 1><<<grid, block, 0, stream>>>((const T*)tmp, (T*)out, Nx, Ny, fs, weights, radius);

@@ -68,6 +68,18 @@ def test_rhs_and_blur(cuda_device, shape):
         assert np.abs(got32 - fo.blur_movie(movie, sigma)).max() < 2e-3
 
 
+@pytest.mark.parametrize('shape,sigma', [((150, 300), 5.0), ((70, 131), 9.0), ((96, 260), 17.0), ((1024, 1024), 2.5)])
+def test_blur_tiles_and_wide_kernels(cuda_device, shape, sigma):
+    """Tile seams, ragged right/bottom tiles, radius > tile height, and the radius > 64 two-launch path."""
+    rng = np.random.default_rng(19)
+    movie = rng.uniform(0, 255, (2,) + shape)
+    want = fo.blur_movie(movie, sigma)
+    got = engine.blur(dev_t(movie, cuda_device), sigma).cpu().numpy()
+    assert np.abs(got - want).max() < 1e-10
+    got32 = engine.blur(dev_t(movie, cuda_device).float(), sigma).cpu().numpy()
+    assert np.abs(got32 - want).max() < 2e-3
+
+
 def test_multigrid_hierarchy_matches_model(cuda_device):
     """One V(2,2) application on the device == the numpy model of the same cycle (averaged coefficients)."""
     import importlib.util, os, sys
