@@ -37,7 +37,7 @@ extern "C" {
 #define OFB_FLAG_NO_FUSED_TAIL 2 /* run the small multigrid levels as separate launches (A/B measurements) */
 #define OFB_FLAG_LEGACY_COARSE_BOUNDARY 4 /* node-mirror far boundary on every coarse level (A/B measurements) */
 
-#define OFB_ABI_VERSION 2
+#define OFB_ABI_VERSION 3
 
 typedef struct ofb_solve_options {
     int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
@@ -112,6 +112,49 @@ int ofb_precondition(const void* P, const void* r3, void* z3, const double* alph
 int ofb_epilogue(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma,
                  double* functionals, double* moments, const double* alpha, const double* beta, double scale,
                  int B, int Nx, int Ny, int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Slab decomposition of ONE very large frame pair over the GPUs of a node.
+ * The reference has no counterpart: its only scaling knob is host RAM (optical_flow.py:761).  One process per
+ * GPU; each rank holds a slab of consecutive image rows and the ranks exchange one boundary row per field with
+ * their neighbours before every stencil sweep (NCCL send/recv over NVLink), sum their partial dot products
+ * (all-reduce of 4 doubles per pair) and all-gather the multigrid level `gather_level`, below which every rank
+ * solves the whole coarse grid redundantly.
+ *
+ * Layout on rank r: local planes have owned+2 rows.  Row 0 is the last owned row of rank r-1 (the mirror ghost
+ * row of the frame on rank 0), row owned+1 the first owned row of rank r+1 (ghost row on the last rank).
+ * P (and C for the epilogue) must additionally be readable one row BEFORE row 0 and one row AFTER row owned+1
+ * wherever that row is a neighbour's row: the level-1 coefficients of the first owned coarse row need the image
+ * derivative on the halo row.  b3 must be 0 on rows 0 and owned+1 (ofb_build_rhs on the local slab does that).
+ * ------------------------------------------------------------------------------------------------------- */
+typedef struct ofb_slab {
+    int rank, world;        /* this process, number of slabs */
+    int Nx_global;          /* rows of the whole frame, ghost rows included */
+    int rows_per_rank;      /* interior rows owned by every rank but the last  (ofb_slab_partition) */
+    int gather_level;       /* first multigrid level replicated on every rank   (ofb_slab_partition) */
+    int reserved;
+    void* comm;             /* ofb_comm_create */
+} ofb_slab;
+
+/* Rows per rank (a multiple of 2^gather_level) and gather level for a frame; hint <= 0 = automatic. */
+int ofb_slab_partition(int Nx_global, int Ny, int world, int gather_level_hint, int* rows_per_rank, int* gather_level);
+/* First owned global row and number of owned rows of slab->rank (local Nx = owned + 2). */
+int ofb_slab_local_rows(const ofb_slab* slab, int* first_row, int* owned_rows);
+/* NCCL bootstrap: rank 0 makes the 128-byte id, the host broadcasts it (torch.distributed), every rank creates. */
+int ofb_comm_unique_id(void* id128);
+int ofb_comm_create(const void* id128, int rank, int world, void** comm_out);
+int ofb_comm_destroy(void* comm);
+size_t ofb_slab_workspace_bytes(int B, int Ny, int dtype, const ofb_slab* slab);
+/* ofb_solve on a slab; every rank of slab->comm must make the same call.  Scalars, iteration counts and the
+ * convergence decision are identical on all ranks. */
+int ofb_solve_slab(const void* P, const void* b3, void* x3, const double* alpha, const double* beta,
+                   double rtol, int max_it, const ofb_solve_options* opt, void* workspace, size_t workspace_bytes,
+                   int* iters_out, double* relres_out, int* converged_out,
+                   int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream);
+/* ofb_epilogue on a slab: functionals/moments are this rank's partial sums over its owned rows. */
+int ofb_epilogue_slab(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma,
+                      double* functionals, double* moments, const double* alpha, const double* beta, double scale,
+                      int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream);
 
 #ifdef __cplusplus
 }

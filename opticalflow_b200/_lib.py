@@ -13,12 +13,13 @@ PRECOND_BJACOBI, PRECOND_MG = 0, 1
 FLAG_NO_STREAM = 1
 FLAG_NO_FUSED_TAIL = 2
 FLAG_LEGACY_COARSE_BOUNDARY = 4
-ABI_VERSION = 2
+ABI_VERSION = 3
 
 # every symbol include/ofb200.h declares
 EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_workspace_bytes', 'ofb_blur',
                     'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_smooth', 'ofb_solve', 'ofb_precondition',
-                    'ofb_epilogue')
+                    'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
+                    'ofb_comm_destroy', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab')
 
 
 class SolveOptions(ctypes.Structure):
@@ -27,6 +28,13 @@ class SolveOptions(ctypes.Structure):
                 ('coarse_sweeps', ctypes.c_int), ('flags', ctypes.c_int),
                 ('omega_pre', ctypes.c_double * 4), ('omega_post', ctypes.c_double * 4),
                 ('max_levels', ctypes.c_int), ('reserved', ctypes.c_int)]
+
+
+class Slab(ctypes.Structure):
+    """ofb_slab: one rank's share of a slab-decomposed frame pair (include/ofb200.h)."""
+    _fields_ = [('rank', ctypes.c_int), ('world', ctypes.c_int), ('Nx_global', ctypes.c_int),
+                ('rows_per_rank', ctypes.c_int), ('gather_level', ctypes.c_int), ('reserved', ctypes.c_int),
+                ('comm', ctypes.c_void_p)]
 
 
 class OfbError(RuntimeError):
@@ -74,6 +82,24 @@ def load():
     lib.ofb_precondition.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(SolveOptions), vp, sz, i, i, i, i, vp]
     lib.ofb_epilogue.restype = i
     lib.ofb_epilogue.argtypes = [vp, vp, vp, vp, vp, vp, vp, dp, dp, dp, dp, d, i, i, i, i, vp]
+    intp, slabp = ctypes.POINTER(ctypes.c_int), ctypes.POINTER(Slab)
+    lib.ofb_slab_partition.restype = i
+    lib.ofb_slab_partition.argtypes = [i, i, i, i, intp, intp]
+    lib.ofb_slab_local_rows.restype = i
+    lib.ofb_slab_local_rows.argtypes = [slabp, intp, intp]
+    lib.ofb_comm_unique_id.restype = i
+    lib.ofb_comm_unique_id.argtypes = [vp]
+    lib.ofb_comm_create.restype = i
+    lib.ofb_comm_create.argtypes = [vp, i, i, ctypes.POINTER(ctypes.c_void_p)]
+    lib.ofb_comm_destroy.restype = i
+    lib.ofb_comm_destroy.argtypes = [vp]
+    lib.ofb_slab_workspace_bytes.restype = sz
+    lib.ofb_slab_workspace_bytes.argtypes = [i, i, i, slabp]
+    lib.ofb_solve_slab.restype = i
+    lib.ofb_solve_slab.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip,
+                                   i, i, i, i, slabp, vp]
+    lib.ofb_epilogue_slab.restype = i
+    lib.ofb_epilogue_slab.argtypes = [vp, vp, vp, vp, vp, vp, vp, dp, dp, dp, dp, d, i, i, i, i, slabp, vp]
     if lib.ofb_version() != ABI_VERSION:
         raise OfbError('libofb200.so ABI version %d != expected %d' % (lib.ofb_version(), ABI_VERSION))
     _lib = lib

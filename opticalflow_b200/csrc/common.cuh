@@ -28,6 +28,8 @@ struct Geom {
     int far_i, far_j;            // far-side ghost rule per axis: ghost(N-1) = q(N-1-far); 2 = mirror about the last
                                  // interior node (the reference's rule, level 0), 1 = mirror about the half point
                                  // beyond it (coarse levels whose fine parent has an even number of interior nodes)
+    int halo_lo, halo_hi;        // slab decomposition: row 0 / row Nx-1 hold the neighbouring slab's boundary row (real
+                                 // data, refreshed by the halo exchange) instead of being a mirror ghost row
 };
 
 // ghost-ring handling when a plane is read
@@ -41,6 +43,17 @@ __device__ __forceinline__ int mirror_index(int i, int N) {
 }
 __device__ __forceinline__ int mirror_far(int i, int N, int far) {
     return i == 0 ? 2 : (i == N - 1 ? N - 1 - far : i);
+}
+
+// Row a solution-type plane is read from for logical row i: mirror ghost rows are redirected to their interior
+// image, halo rows of a slab are read as stored.
+__device__ __forceinline__ int sol_row(int i, const Geom& g) {
+    if (i <= 0) return g.halo_lo ? 0 : 2;
+    if (i >= g.Nx - 1) return g.halo_hi ? g.Nx - 1 : g.Nx - 1 - g.far_i;
+    return i;
+}
+__device__ __forceinline__ bool is_ghost_row(int i, const Geom& g) {
+    return (i == 0 && !g.halo_lo) || (i == g.Nx - 1 && !g.halo_hi);
 }
 
 // One row of one plane as seen by a lane: v[0] = left halo (column j0-1), v[1..V] own columns,
@@ -136,10 +149,9 @@ __device__ __forceinline__ void load_row_ptr(Row<T>& r, const T* __restrict__ ro
 template <typename T, int MODE>
 __device__ __forceinline__ void load_row(Row<T>& r, const T* __restrict__ plane, int i, int j0,
                                          const Geom& g, int lane, bool edge_warp) {
-    int row = i;
-    if (MODE != LOAD_RAW) row = mirror_far(i, g.Nx, g.far_i);
-    row = min(max(row, 0), g.Nx - 1);
-    load_row_ptr<T, MODE, false>(r, plane + (long long)row * g.pitch, (i == 0) || (i == g.Nx - 1), j0, g, lane, edge_warp);
+    int row = min(max(i, 0), g.Nx - 1);
+    if (MODE != LOAD_RAW) row = sol_row(i, g);
+    load_row_ptr<T, MODE, false>(r, plane + (long long)row * g.pitch, is_ghost_row(i, g), j0, g, lane, edge_warp);
 }
 
 // ---------------------------------------------------------------- reductions

@@ -185,6 +185,7 @@ __global__ void k_fill_ghosts(Geom g, T* __restrict__ x) {
     else if (t < 2 * g.Ny) { i = g.Nx - 1; j = t - g.Ny; }
     else if (t < 2 * g.Ny + g.Nx) { i = t - 2 * g.Ny; j = 0; }
     else { i = t - 2 * g.Ny - g.Nx; j = g.Ny - 1; }
+    if ((i == 0 && g.halo_lo) || (i == g.Nx - 1 && g.halo_hi)) return;      // slab halo rows come from the neighbour
     const bool gr = (i == 0) || (i == g.Nx - 1), gc = (j == 0) || (j == g.Ny - 1);
     const int mi = mirror_index(i, g.Nx), mj = mirror_index(j, g.Ny);
     T* base = x + (long long)pair * g.pair;
@@ -252,16 +253,17 @@ __global__ void __launch_bounds__(128) k_epilogue(Geom g, const T* __restrict__ 
     // rows are strided over gridDim.y so that each block ends with ONE round of atomics
     if (j < g.Ny) for (int i = blockIdx.y; i < g.Nx; i += gridDim.y) {
         const T* xb = x + (long long)pair * g.pair;
-        const int mi = mirror_index(i, g.Nx), mj = mirror_index(j, g.Ny);
+        const bool halo = (i == 0 && g.halo_lo) || (i == g.Nx - 1 && g.halo_hi);
+        const int mi = halo ? i : mirror_index(i, g.Nx), mj = mirror_index(j, g.Ny);
         const long long o = (long long)mi * g.pitch + mj;
         const T ux = xb[o], uy = xb[g.plane + o], gm = xb[2 * g.plane + o];
         const long long oo = (long long)pair * g.img_pair + (long long)i * g.pitch + j;
         vx[oo] = ux * T(scale); vy[oo] = uy * T(scale); gamma[oo] = gm;
         const T sp = T(sqrt((double)(ux * T(scale)) * (double)(ux * T(scale)) + (double)(uy * T(scale)) * (double)(uy * T(scale))));
         speed[oo] = sp;
-        mom[0] += (double)sp; mom[1] += (double)sp * (double)sp; mom[2] += (double)gm; mom[3] += (double)gm * (double)gm;
+        if (!halo) { mom[0] += (double)sp; mom[1] += (double)sp * (double)sp; mom[2] += (double)gm; mom[3] += (double)gm * (double)gm; }
         if (i >= 1 && i <= g.Nx - 2 && j >= 1 && j <= g.Ny - 2) {
-            const int ip = mirror_index(i + 1, g.Nx), im = mirror_index(i - 1, g.Nx);
+            const int ip = sol_row(i + 1, g), im = sol_row(i - 1, g);
             const long long op = (long long)ip * g.pitch + mj, om = (long long)im * g.pitch + mj;
             const double dux = 0.5 * ((double)xb[op] - (double)xb[om]);
             const double duy = 0.5 * ((double)xb[g.plane + op] - (double)xb[g.plane + om]);

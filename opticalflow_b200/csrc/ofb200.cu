@@ -9,6 +9,7 @@
 #include "../../include/ofb200.h"
 #include "misc_kernels.cuh"
 #include "stream_sweep.cuh"
+#include "comm.h"
 #include "coarse_fused.cuh"
 
 using namespace ofb;
@@ -36,6 +37,12 @@ std::atomic<long long> g_launches{0};     // kernels launched by this process (d
     do {                                    \
         g_launches.fetch_add(1);            \
         OFB_CHECK_CUDA(cudaGetLastError()); \
+    } while (0)
+
+#define OFB_CHECK_NCCL(expr)                                                                        \
+    do {                                                                                            \
+        ncclResult_t r__ = (expr);                                                                  \
+        if (r__ != ncclSuccess) return fail(-2000 - (int)r__, "%s: %s", #expr, nccl_api().GetErrorString(r__)); \
     } while (0)
 
 constexpr int MAX_LEVELS = 16;
@@ -123,6 +130,16 @@ struct Plan {
     int dense_n;
     int fused_from;                     // first level of the shared-memory coarse tail (0 = none)
     size_t fused_smem;                  // bytes of shared memory the tail needs
+    // slab decomposition (ofb_solve_slab): levels < gather_level hold this rank's rows (+2 halo/ghost rows), levels
+    // >= gather_level hold the whole grid, replicated on every rank
+    int gather_level;                   // 0 = not a slab solve
+    int stage_rows;                     // rows of the local staging planes used at the gather level
+};
+
+struct SlabInfo {
+    bool on;
+    int rank, world, R, Lg;
+    Comm* comm;
 };
 
 constexpr size_t FUSED_SMEM_BUDGET = 220 * 1024;
@@ -131,6 +148,8 @@ Plan make_plan(int Nx, int Ny, int precond, int max_levels = 0, size_t elem_size
     Plan p;
     p.fused_from = 0;
     p.fused_smem = 0;
+    p.gather_level = 0;
+    p.stage_rows = 0;
     p.nlevels = 1;
     p.lv[0] = {Nx, Ny, Ny, (long long)Nx * Ny, 2, 2, 0.0, 0.0};
     p.dense = false;
@@ -172,6 +191,60 @@ Plan make_plan(int Nx, int Ny, int precond, int max_levels = 0, size_t elem_size
     return p;
 }
 
+// ---- slab decomposition (config d-5: one very large pair over several GPUs) --------------------------------
+// Rank k owns the interior rows [1 + k R, 1 + (k+1) R) of level 0 (the last rank whatever is left).  Coarse node K
+// sits on fine node 2K-1, so with R a multiple of 2^Lg the same rule holds on every level l <= Lg with R_l = R >> l:
+// local fine row i and local coarse row K are related by i = 2K-1 exactly as on the whole grid, and a slab looks
+// like a smaller frame whose first/last row is the neighbour's boundary row instead of a mirror ghost.
+inline int slab_owned(int N_level, int R_level, int rank) {
+    return std::min(std::max(N_level - 2 - R_level * rank, 0), R_level);
+}
+
+// Chooses the gather level and the rows per rank.  Returns 0 or an error code.
+int slab_partition(int NxG, int Ny, int world, int hint, int* rows_per_rank, int* gather_level) {
+    if (world < 2) return fail(-20, "slab decomposition needs at least 2 ranks (got %d)", world);
+    const Plan pg = make_plan(NxG, Ny, OFB_PRECOND_MG);
+    int max_lg = pg.nlevels - 1;
+    if (pg.dense) max_lg -= 1;                         // the dense coarsest level keeps its unpadded layout
+    if (max_lg < 1) return fail(-21, "frame %dx%d is too small for a slab-decomposed multigrid solve", NxG, Ny);
+    const int per = (NxG - 2 + world - 1) / world;     // interior rows per rank, before rounding
+    int Lg = hint;
+    if (Lg <= 0) {                                     // distribute a level while a rank keeps >= 32 rows of it
+        Lg = 1;
+        while (Lg < max_lg && (per >> Lg) >= 32) ++Lg;
+    }
+    Lg = std::min(Lg, max_lg);
+    for (; Lg >= 1; --Lg) {
+        const int unit = 1 << Lg;
+        const int R = (per + unit - 1) / unit * unit;
+        bool ok = true;
+        for (int l = 0; l <= Lg && ok; ++l) ok = slab_owned(pg.lv[l].Nx, R >> l, world - 1) >= 1;
+        if (ok) { *rows_per_rank = R; *gather_level = Lg; return 0; }
+    }
+    return fail(-22, "cannot split %d rows over %d ranks so that every rank owns rows on every distributed level", NxG, world);
+}
+
+Plan make_plan_slab(const ofb_slab& sl, int Ny, int max_levels, size_t elem_size, bool legacy_boundaries) {
+    Plan p = make_plan(sl.Nx_global, Ny, OFB_PRECOND_MG, max_levels, elem_size, legacy_boundaries);
+    const int Lg = sl.gather_level;
+    p.gather_level = Lg;
+    for (int l = 0; l < Lg; ++l) {
+        const int owned = slab_owned(p.lv[l].Nx, sl.rows_per_rank >> l, sl.rank);
+        p.lv[l].Nx = owned + 2;
+        p.lv[l].plane = (long long)(owned + 2) * p.lv[l].pitch;
+    }
+    // the gathered level receives world x R_Lg rows per plane (the last rank pads): leave room behind the plane
+    const int gathered_rows = sl.world * (sl.rows_per_rank >> Lg) + 2;
+    p.lv[Lg].plane = (long long)std::max(p.lv[Lg].Nx, gathered_rows) * p.lv[Lg].pitch;
+    p.stage_rows = (sl.rows_per_rank >> Lg) + 2;
+    if (p.fused_from > 0 && p.fused_from < Lg) {       // the shared-memory tail must start on a replicated level
+        p.fused_from = (p.nlevels - Lg >= 2) ? Lg : 0;
+        p.fused_smem = 0;
+        for (int l = p.fused_from; p.fused_from > 0 && l < p.nlevels; ++l) p.fused_smem += (size_t)9 * p.lv[l].Nx * p.lv[l].Ny * elem_size;
+    }
+    return p;
+}
+
 // Workspace carving (all offsets 256-byte aligned).
 template <typename T> struct Workspace {
     PairState* st; int* active; int* n_active;
@@ -179,6 +252,7 @@ template <typename T> struct Workspace {
     T* coef[MAX_LEVELS];                                      // level >= 1: 7 coefficient planes per pair
     T *lb[MAX_LEVELS], *xa[MAX_LEVELS], *xb[MAX_LEVELS], *res[MAX_LEVELS];
     double* dense_M; T* dense_Minv; int* dense_piv;
+    T* stage;                                                 // slab solves: local planes at the gather level (7 per pair)
     size_t bytes;
 };
 
@@ -202,6 +276,8 @@ Workspace<T> carve(void* base, int B, const Plan& plan) {
         w.xb[l] = (T*)take(3 * planeb);
         w.res[l] = (T*)take(3 * planeb);
     }
+    if (plan.gather_level > 0)
+        w.stage = (T*)take((size_t)NCOEF * plan.stage_rows * plan.lv[plan.gather_level].pitch * B * sizeof(T));
     if (plan.dense) {
         const size_t nn = (size_t)plan.dense_n * plan.dense_n;
         w.dense_M = (double*)take(nn * B * sizeof(double));
@@ -218,6 +294,7 @@ template <typename T> Geom make_geom(const LevelPlan& lp, bool aligned_ok) {
     g.pair = 3 * lp.plane; g.img_pair = lp.plane;
     g.aligned = (aligned_ok && lp.pitch % VecOf<T>::V == 0) ? 1 : 0;
     g.far_i = lp.far_i; g.far_j = lp.far_j;
+    g.halo_lo = g.halo_hi = 0;
     return g;
 }
 
@@ -247,6 +324,68 @@ template <typename T> struct Solver {
     ofb_solve_options opt;
     cudaStream_t stream;
     const int* active;               // nullptr while setting up / for single applications
+    SlabInfo slab;                   // slab.on: levels < slab.Lg are distributed over the ranks of slab.comm
+    Geom g_stage;                    // local geometry of the staging planes at the gather level
+
+    // ---- slab communication (no-ops for ordinary solves) ------------------------------------------------
+    bool distributed(int l) const { return slab.on && l < slab.Lg; }
+    // refresh the halo rows of `nplanes` planes per pair on level l from the neighbouring slabs
+    int exchange(int l, T* base, int nplanes, long long pair_stride) {
+        if (!distributed(l)) return 0;
+        const Geom& G = g[l];
+        if (!G.halo_lo && !G.halo_hi) return 0;
+        NcclApi& api = nccl_api();
+        const ncclDataType_t dt = NcclType<T>::value;
+        const size_t cnt = (size_t)G.pitch;
+        OFB_CHECK_NCCL(api.GroupStart());
+        for (int pair = 0; pair < B; ++pair)
+            for (int q = 0; q < nplanes; ++q) {
+                T* pl = base + (long long)pair * pair_stride + (long long)q * G.plane;
+                if (G.halo_lo) {
+                    OFB_CHECK_NCCL(api.Send(pl + G.pitch, cnt, dt, slab.rank - 1, slab.comm->comm, stream));
+                    OFB_CHECK_NCCL(api.Recv(pl, cnt, dt, slab.rank - 1, slab.comm->comm, stream));
+                }
+                if (G.halo_hi) {
+                    OFB_CHECK_NCCL(api.Send(pl + (long long)(G.Nx - 2) * G.pitch, cnt, dt, slab.rank + 1, slab.comm->comm, stream));
+                    OFB_CHECK_NCCL(api.Recv(pl + (long long)(G.Nx - 1) * G.pitch, cnt, dt, slab.rank + 1, slab.comm->comm, stream));
+                }
+            }
+        OFB_CHECK_NCCL(api.GroupEnd());
+        return 0;
+    }
+    int exchange_vec(int l, T* v) { return exchange(l, v, 3, g[l].pair); }
+    // sum the partial dot products of all slabs (4 doubles per pair) before a scalar stage
+    int allreduce_acc() {
+        if (!slab.on) return 0;
+        NcclApi& api = nccl_api();
+        OFB_CHECK_NCCL(api.GroupStart());
+        for (int pair = 0; pair < B; ++pair)
+            OFB_CHECK_NCCL(api.AllReduce(w.st[pair].acc, w.st[pair].acc, 4, ncclFloat64, ncclSum, slab.comm->comm, stream));
+        OFB_CHECK_NCCL(api.GroupEnd());
+        return 0;
+    }
+    // staging planes (local rows of the gather level) -> whole-grid planes on every rank
+    int gather_planes(const T* stage, long long stage_pair, T* whole, long long whole_pair, int nplanes) {
+        NcclApi& api = nccl_api();
+        const Geom& G = g[slab.Lg];
+        const size_t cnt = (size_t)(slab.R >> slab.Lg) * G.pitch;
+        OFB_CHECK_NCCL(api.GroupStart());
+        for (int pair = 0; pair < B; ++pair)
+            for (int q = 0; q < nplanes; ++q)
+                OFB_CHECK_NCCL(api.AllGather(stage + (long long)pair * stage_pair + (long long)q * g_stage.plane + G.pitch,
+                                             whole + (long long)pair * whole_pair + (long long)q * G.plane + G.pitch, cnt,
+                                             NcclType<T>::value, slab.comm->comm, stream));
+        OFB_CHECK_NCCL(api.GroupEnd());
+        return 0;
+    }
+    // this rank's window (owned rows + one row either side) of a replicated gather-level vector
+    const T* window(const T* whole) const { return whole + (long long)(slab.R >> slab.Lg) * slab.rank * g[slab.Lg].pitch; }
+    Geom window_geom() const {
+        Geom v = g[slab.Lg];
+        v.Nx = g_stage.Nx;
+        v.halo_lo = g_stage.halo_lo; v.halo_hi = g_stage.halo_hi;
+        return v;
+    }
 
     LevelArgs<T> level_args(int l) const {
         LevelArgs<T> L;
@@ -305,12 +444,20 @@ template <typename T> struct Solver {
     }
 
     int build_hierarchy() {
+        int rc;
         for (int l = 1; l < plan.nlevels; ++l) {
-            dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
-            if (l == 1) k_coef_from_image<T><<<grid, block, 0, stream>>>(g[0], P, g[1], w.coef[1]);
-            else k_restrict<T, true><<<grid, block, 0, stream>>>(g[l - 1], w.coef[l - 1], (long long)NCOEF * g[l - 1].plane, g[l],
-                                                                 w.coef[l], (long long)NCOEF * g[l].plane, NCOEF, nullptr);
+            // on the gather level of a slab solve the local rows go to the staging planes and are then all-gathered
+            const bool to_stage = slab.on && l == slab.Lg;
+            const Geom gc = to_stage ? g_stage : g[l];
+            T* out = to_stage ? w.stage : w.coef[l];
+            const long long out_pair = (long long)NCOEF * gc.plane;
+            dim3 block(128), grid((gc.Ny + 127) / 128, gc.Nx, B);
+            if (l == 1) k_coef_from_image<T><<<grid, block, 0, stream>>>(g[0], P, gc, out);
+            else k_restrict<T, true><<<grid, block, 0, stream>>>(g[l - 1], w.coef[l - 1], (long long)NCOEF * g[l - 1].plane, gc,
+                                                                 out, out_pair, NCOEF, nullptr);
             OFB_CHECK_LAUNCH();
+            if (to_stage) { if ((rc = gather_planes(w.stage, out_pair, w.coef[l], (long long)NCOEF * g[l].plane, NCOEF))) return rc; }
+            else if ((rc = exchange(l, w.coef[l], NCOEF, out_pair))) return rc;
         }
         if (plan.dense) {
             const int l = plan.nlevels - 1;
@@ -380,14 +527,24 @@ template <typename T> struct Solver {
     // `alt` is the ping-pong partner.  Returns the buffer holding the result in *out.
     int vcycle(int l, const T* b, T* cur, T* alt, T** out) {
         int rc;
-        for (int s = 1; s < opt.nu_pre; ++s) { if ((rc = smooth(l, b, cur, alt, w_pre(s)))) return rc; std::swap(cur, alt); }
+        if ((rc = exchange_vec(l, cur))) return rc;
+        for (int s = 1; s < opt.nu_pre; ++s) {
+            if ((rc = smooth(l, b, cur, alt, w_pre(s)))) return rc;
+            std::swap(cur, alt);
+            if ((rc = exchange_vec(l, cur))) return rc;
+        }
         const int lc = l + 1;
+        const bool gather = slab.on && lc == slab.Lg;          // fine level distributed, coarse level replicated
         T* res = (l == 0) ? w.t : w.res[l];
         if ((rc = residual(l, b, cur, res))) return rc;
+        if ((rc = exchange_vec(l, res))) return rc;
         {
-            dim3 block(128), grid((g[lc].Ny + 127) / 128, g[lc].Nx, B);
-            k_restrict<T, false><<<grid, block, 0, stream>>>(g[l], res, g[l].pair, g[lc], w.lb[lc], g[lc].pair, 3, active);
+            const Geom gc = gather ? g_stage : g[lc];
+            T* lb = gather ? w.stage : w.lb[lc];
+            dim3 block(128), grid((gc.Ny + 127) / 128, gc.Nx, B);
+            k_restrict<T, false><<<grid, block, 0, stream>>>(g[l], res, g[l].pair, gc, lb, gc.pair, 3, active);
             OFB_CHECK_LAUNCH();
+            if (gather && (rc = gather_planes(w.stage, gc.pair, w.lb[lc], g[lc].pair, 3))) return rc;
         }
         T* ec = nullptr;
         if (plan.fused_from > 0 && lc == plan.fused_from) {
@@ -410,22 +567,29 @@ template <typename T> struct Solver {
             if ((rc = vcycle(lc, w.lb[lc], w.xa[lc], w.xb[lc], &ec))) return rc;
         }
         {
+            // a distributed fine level below a replicated coarse level interpolates from its window of the coarse grid
+            const Geom gcv = gather ? window_geom() : g[lc];
+            const T* ecv = gather ? window(ec) : ec;
+            bool done = false;
             if constexpr (sizeof(T) == 4) {
                 if (g[l].aligned && g[l].Ny % 4 == 0) {
                     dim3 block(128), grid((g[l].Ny / 4 + 127) / 128, g[l].Nx, B);
-                    k_prolong_add4<<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
+                    k_prolong_add4<<<grid, block, 0, stream>>>(gcv, ecv, g[l], cur, active);
                     OFB_CHECK_LAUNCH();
-                    goto prolonged;
+                    done = true;
                 }
             }
-            {
+            if (!done) {
                 dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
-                k_prolong_add<T><<<grid, block, 0, stream>>>(g[lc], ec, g[l], cur, active);
+                k_prolong_add<T><<<grid, block, 0, stream>>>(gcv, ecv, g[l], cur, active);
                 OFB_CHECK_LAUNCH();
             }
-        prolonged:;
         }
-        for (int s = 0; s < opt.nu_post; ++s) { if ((rc = smooth(l, b, cur, alt, w_post(s)))) return rc; std::swap(cur, alt); }
+        for (int s = 0; s < opt.nu_post; ++s) {
+            if ((rc = smooth(l, b, cur, alt, w_post(s)))) return rc;
+            std::swap(cur, alt);
+            if ((rc = exchange_vec(l, cur))) return rc;
+        }
         *out = cur;
         return 0;
     }
@@ -447,20 +611,47 @@ template <typename T> struct Solver {
 
 template <typename T>
 int init_solver(Solver<T>& S, const void* P, const double* alpha, const double* beta, const ofb_solve_options* opt,
-                void* workspace, size_t workspace_bytes, int B, int Nx, int Ny, void* stream, const void* a1, const void* a2) {
+                void* workspace, size_t workspace_bytes, int B, int Nx, int Ny, void* stream, const void* a1, const void* a2,
+                const ofb_slab* sl = nullptr) {
     if (opt) S.opt = *opt; else ofb_default_options(&S.opt);
     if (S.opt.nu_pre < 1) S.opt.nu_pre = 1;
     if (S.opt.nu_post < 0) S.opt.nu_post = 0;
     if (S.opt.coarse_sweeps < 1) S.opt.coarse_sweeps = 1;
     if (S.opt.check_every < 1) S.opt.check_every = 1;
     S.B = B;
-    S.plan = make_plan(Nx, Ny, S.opt.precond, S.opt.max_levels, sizeof(T), (S.opt.flags & OFB_FLAG_LEGACY_COARSE_BOUNDARY) != 0);
+    memset(&S.slab, 0, sizeof(S.slab));
+    const bool legacy = (S.opt.flags & OFB_FLAG_LEGACY_COARSE_BOUNDARY) != 0;
+    if (sl != nullptr) {
+        if (S.opt.precond != OFB_PRECOND_MG) return fail(-23, "slab solves use the multigrid preconditioner");
+        if (sl->comm == nullptr || sl->world < 2 || sl->rank < 0 || sl->rank >= sl->world) return fail(-24, "bad slab descriptor");
+        S.plan = make_plan_slab(*sl, Ny, S.opt.max_levels, sizeof(T), legacy);
+        const int Lg = sl->gather_level;
+        if (Lg < 1 || Lg > S.plan.nlevels - 1 - (S.plan.dense ? 1 : 0) || sl->rows_per_rank % (1 << Lg) != 0)
+            return fail(-25, "bad slab descriptor: gather level %d, rows per rank %d", Lg, sl->rows_per_rank);
+        if (S.plan.lv[0].Nx != Nx)
+            return fail(-26, "rank %d owns %d rows (+2) of the %d-row frame, but Nx = %d was passed", sl->rank, S.plan.lv[0].Nx - 2,
+                        sl->Nx_global, Nx);
+        S.slab.on = true; S.slab.rank = sl->rank; S.slab.world = sl->world; S.slab.R = sl->rows_per_rank; S.slab.Lg = Lg;
+        S.slab.comm = (Comm*)sl->comm;
+    } else {
+        S.plan = make_plan(Nx, Ny, S.opt.precond, S.opt.max_levels, sizeof(T), legacy);
+    }
     if (S.opt.flags & OFB_FLAG_NO_FUSED_TAIL) S.plan.fused_from = 0;
     S.w = carve<T>(workspace, B, S.plan);
     if (workspace == nullptr || workspace_bytes < S.w.bytes)
         return fail(-4, "workspace too small: need %zu bytes, got %zu", S.w.bytes, workspace_bytes);
     const bool al = ptr_aligned16(P) && ptr_aligned16(a1) && ptr_aligned16(a2) && ptr_aligned16(workspace);
     for (int l = 0; l < S.plan.nlevels; ++l) S.g[l] = make_geom<T>(S.plan.lv[l], al);
+    if (S.slab.on) {
+        const int lo = S.slab.rank > 0 ? 1 : 0, hi = S.slab.rank < S.slab.world - 1 ? 1 : 0;
+        for (int l = 0; l < S.slab.Lg; ++l) { S.g[l].halo_lo = lo; S.g[l].halo_hi = hi; }
+        LevelPlan st = S.plan.lv[S.slab.Lg];
+        const Plan whole = make_plan(sl->Nx_global, Ny, OFB_PRECOND_MG, S.opt.max_levels, sizeof(T), legacy);
+        st.Nx = slab_owned(whole.lv[S.slab.Lg].Nx, S.slab.R >> S.slab.Lg, S.slab.rank) + 2;
+        st.plane = (long long)S.plan.stage_rows * st.pitch;
+        S.g_stage = make_geom<T>(st, al);
+        S.g_stage.halo_lo = lo; S.g_stage.halo_hi = hi;
+    }
     S.P = (const T*)P; S.alpha = alpha; S.beta = beta; S.stream = (cudaStream_t)stream; S.active = nullptr;
     return 0;
 }
@@ -468,9 +659,9 @@ int init_solver(Solver<T>& S, const void* P, const double* alpha, const double* 
 template <typename T>
 int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
                const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
-               int* converged_out, int B, int Nx, int Ny, void* stream_) {
+               int* converged_out, int B, int Nx, int Ny, void* stream_, const ofb_slab* sl = nullptr) {
     Solver<T> S;
-    int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, b3, x3);
+    int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, b3, x3, sl);
     if (rc) return rc;
     cudaStream_t stream = S.stream;
     Workspace<T>& w = S.w;
@@ -486,17 +677,21 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     OFB_CHECK_LAUNCH();
     k_norm2<T><<<blas_grid, tb, 0, stream>>>(nvec, nvec, b, w.st);
     OFB_CHECK_LAUNCH();
+    if ((rc = S.allreduce_acc())) return rc;
     k_state_bnorm<<<sb, 128, 0, stream>>>(w.st, B);
     OFB_CHECK_LAUNCH();
     // p and v enter the first direction update multiplied by beta_k = 0; they must be finite
     OFB_CHECK_CUDA(cudaMemsetAsync(w.p, 0, sizeof(T) * nvec * B, stream));
     OFB_CHECK_CUDA(cudaMemsetAsync(w.v, 0, sizeof(T) * nvec * B, stream));
+    if (S.slab.on) OFB_CHECK_CUDA(cudaMemsetAsync(w.stage, 0, (size_t)NCOEF * S.g_stage.plane * B * sizeof(T), stream));
     if (S.opt.precond == OFB_PRECOND_MG && S.plan.nlevels > 1) { if ((rc = S.build_hierarchy())) return rc; }
+    if ((rc = S.exchange_vec(0, x))) return rc;
 
     {   // r = b - S x0, rhat = r, acc[2] = acc[3] = r.r
         OpResidual<T, true> op; op.g = g0; op.cen[0] = b; op.r = w.r; op.r2 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
         if ((rc = S.sweep(0, x, op))) return rc;
     }
+    if ((rc = S.allreduce_acc())) return rc;
     k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 0, rtol, max_it, nullptr);
     OFB_CHECK_LAUNCH();
     S.active = w.active;
@@ -516,6 +711,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
             OpApplyDot<T, 1> op; op.g = g0; op.y = w.v; op.cen[0] = w.rhat; op.st = w.st; op.acc[0] = 0.0;
             if ((rc = S.sweep(0, ph, op))) return rc;
         }
+        if ((rc = S.allreduce_acc())) return rc;
         k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 1, rtol, max_it, nullptr);
         OFB_CHECK_LAUNCH();
         {   // s = r - alpha v ; z = w D^-1 s
@@ -527,12 +723,14 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
             OpApplyDot<T, 2> op; op.g = g0; op.y = w.t; op.cen[0] = w.s; op.st = w.st; op.acc[0] = op.acc[1] = 0.0;
             if ((rc = S.sweep(0, sh, op))) return rc;
         }
+        if ((rc = S.allreduce_acc())) return rc;
         k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 2, rtol, max_it, nullptr);
         OFB_CHECK_LAUNCH();
         k_update_x_r<T><<<blas_grid, tb, 0, stream>>>(nvec, nvec, x, ph, sh, w.r, w.s, w.t, w.rhat, w.st);
         OFB_CHECK_LAUNCH();
         const bool poll = ((it + 1) % S.opt.check_every == 0) || (it + 1 == max_it);
         if (poll) OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active, 0, sizeof(int), stream));
+        if ((rc = S.allreduce_acc())) return rc;
         k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : nullptr);
         OFB_CHECK_LAUNCH();
         if (poll) {
@@ -545,6 +743,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         const int ring = 2 * Nx + 2 * Ny;
         k_fill_ghosts<T><<<dim3((ring + 127) / 128, B), 128, 0, stream>>>(g0, x);
         OFB_CHECK_LAUNCH();
+        if ((rc = S.exchange_vec(0, x))) return rc;
     }
     k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out);
     OFB_CHECK_LAUNCH();
@@ -662,9 +861,11 @@ int smooth_impl(const void* P, const void* b3, const void* x_in, void* x_out, co
 
 template <typename T>
 int epilogue_impl(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma, double* functionals,
-                  double* moments, const double* alpha, const double* beta, double scale, int B, int Nx, int Ny, cudaStream_t stream) {
+                  double* moments, const double* alpha, const double* beta, double scale, int B, int Nx, int Ny, cudaStream_t stream,
+                  int halo_lo = 0, int halo_hi = 0) {
     LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny, 2, 2, 0.0, 0.0};
-    const Geom g = make_geom<T>(lp, false);
+    Geom g = make_geom<T>(lp, false);
+    g.halo_lo = halo_lo; g.halo_hi = halo_hi;
     OFB_CHECK_CUDA(cudaMemsetAsync(functionals, 0, sizeof(double) * 3 * B, stream));
     if (moments) OFB_CHECK_CUDA(cudaMemsetAsync(moments, 0, sizeof(double) * 4 * B, stream));
     dim3 block(128), grid((Ny + 127) / 128, std::min(Nx, 32), B);
@@ -776,6 +977,86 @@ int ofb_epilogue(const void* P, const void* C, const void* x3, void* vx, void* v
                                                    (cudaStream_t)stream)
                             : epilogue_impl<double>(P, C, x3, vx, vy, speed, gamma, functionals, moments, alpha, beta, scale, B, Nx, Ny,
                                                     (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------- slab decomposition
+int ofb_slab_partition(int Nx_global, int Ny, int world, int gather_level_hint, int* rows_per_rank, int* gather_level) {
+    if (Nx_global < 5 || Ny < 5) return fail(-2, "frames must be at least 5x5 (got %dx%d)", Nx_global, Ny);
+    if (rows_per_rank == nullptr || gather_level == nullptr) return fail(-9, "null output pointer");
+    return slab_partition(Nx_global, Ny, world, gather_level_hint, rows_per_rank, gather_level);
+}
+
+int ofb_slab_local_rows(const ofb_slab* slab, int* first_row, int* owned_rows) {
+    if (slab == nullptr || slab->world < 1 || slab->rank < 0 || slab->rank >= slab->world) return fail(-24, "bad slab descriptor");
+    const int owned = slab_owned(slab->Nx_global, slab->rows_per_rank, slab->rank);
+    if (first_row) *first_row = 1 + slab->rows_per_rank * slab->rank;
+    if (owned_rows) *owned_rows = owned;
+    return 0;
+}
+
+int ofb_comm_unique_id(void* id128) {
+    NcclApi& api = nccl_api();
+    if (!api.ok) return fail(-30, "NCCL is not available in this process (libnccl.so.2 could not be resolved)");
+    static_assert(sizeof(ncclUniqueId) == 128, "ncclUniqueId is 128 bytes");
+    ncclUniqueId id;
+    OFB_CHECK_NCCL(api.GetUniqueId(&id));
+    memcpy(id128, &id, sizeof(id));
+    return 0;
+}
+
+int ofb_comm_create(const void* id128, int rank, int world, void** comm_out) {
+    NcclApi& api = nccl_api();
+    if (!api.ok) return fail(-30, "NCCL is not available in this process (libnccl.so.2 could not be resolved)");
+    if (comm_out == nullptr || id128 == nullptr || world < 1 || rank < 0 || rank >= world) return fail(-31, "bad communicator arguments");
+    ncclUniqueId id;
+    memcpy(&id, id128, sizeof(id));
+    Comm* c = new Comm;
+    c->rank = rank; c->world = world; c->comm = nullptr;
+    ncclResult_t r = api.CommInitRank(&c->comm, world, id, rank);
+    if (r != ncclSuccess) { delete c; return fail(-2000 - (int)r, "ncclCommInitRank: %s", api.GetErrorString(r)); }
+    *comm_out = c;
+    return 0;
+}
+
+int ofb_comm_destroy(void* comm) {
+    if (comm == nullptr) return 0;
+    Comm* c = (Comm*)comm;
+    NcclApi& api = nccl_api();
+    if (api.ok && c->comm) api.CommDestroy(c->comm);
+    delete c;
+    return 0;
+}
+
+size_t ofb_slab_workspace_bytes(int B, int Ny, int dtype, const ofb_slab* slab) {
+    if (slab == nullptr || dtype < OFB_F32 || dtype > OFB_F64 || B < 1) return 0;
+    const size_t es = dtype == OFB_F32 ? 4 : 8;
+    const Plan plan = make_plan_slab(*slab, Ny, 0, es, false);
+    return dtype == OFB_F32 ? carve<float>(nullptr, B, plan).bytes : carve<double>(nullptr, B, plan).bytes;
+}
+
+int ofb_solve_slab(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
+                   const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
+                   int* converged_out, int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream) {
+    if (int rc = check_shape(B, std::max(Nx_local, 5), Ny, dtype)) return rc;
+    if (slab == nullptr) return fail(-24, "bad slab descriptor");
+    if (max_it < 0) return fail(-8, "max_it must be >= 0");
+    return dtype == OFB_F32
+               ? solve_impl<float>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
+                                   converged_out, B, Nx_local, Ny, stream, slab)
+               : solve_impl<double>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
+                                    converged_out, B, Nx_local, Ny, stream, slab);
+}
+
+int ofb_epilogue_slab(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma, double* functionals,
+                      double* moments, const double* alpha, const double* beta, double scale, int B, int Nx_local, int Ny, int dtype,
+                      const ofb_slab* slab, void* stream) {
+    if (int rc = check_shape(B, std::max(Nx_local, 5), Ny, dtype)) return rc;
+    if (slab == nullptr) return fail(-24, "bad slab descriptor");
+    const int lo = slab->rank > 0 ? 1 : 0, hi = slab->rank < slab->world - 1 ? 1 : 0;
+    return dtype == OFB_F32 ? epilogue_impl<float>(P, C, x3, vx, vy, speed, gamma, functionals, moments, alpha, beta, scale, B, Nx_local,
+                                                   Ny, (cudaStream_t)stream, lo, hi)
+                            : epilogue_impl<double>(P, C, x3, vx, vy, speed, gamma, functionals, moments, alpha, beta, scale, B, Nx_local,
+                                                    Ny, (cudaStream_t)stream, lo, hi);
 }
 
 }  // extern "C"

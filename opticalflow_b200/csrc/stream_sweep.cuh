@@ -104,8 +104,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                     int row;
                     if (is_win) {
                         row = i_begin - 1 + k;
-                        if (is_sol) row = mirror_far(row, g.Nx, g.far_i);
-                        row = min(max(row, 0), g.Nx - 1);
+                        row = is_sol ? sol_row(row, g) : min(max(row, 0), g.Nx - 1);
                     } else {
                         row = i_begin - 2 + k;
                     }
@@ -142,7 +141,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                 const bool compute = warp_has_cols && k >= 2;
                 if (warp_has_cols) {
                     const int iw = i + 1;                                         // window row delivered by this stage
-                    const bool ghost_row = (iw == 0) || (iw == g.Nx - 1);
+                    const bool ghost_row = is_ghost_row(iw, g);
                     if constexpr (Op::NEED_X) {
                         load_row_ptr<T, LOAD_SOL, true>(ux[sp], stg, ghost_row, j0, g, lane, edge_warp);
                         load_row_ptr<T, LOAD_SOL, true>(uy[sp], stg + C::ROW, ghost_row, j0, g, lane, edge_warp);

@@ -13,6 +13,9 @@ __device__ __forceinline__ int reflect_clamped(int i, int N, int far = 2) {
     return mirror_far(i, N, far);
 }
 
+// row index for grid transfers: clamp, then ghost rows to their mirror image (halo rows of a slab stay)
+__device__ __forceinline__ int reflect_row(int i, const Geom& g) { return sol_row(min(max(i, 0), g.Nx - 1), g); }
+
 // Level-1 coefficient planes straight from the image: full weighting (1/4,1/2,1/4)^2 of the
 // level-0 coefficient fields (evaluated from P's 3x3 neighbourhood), pre-scaled for hinv = 1/2.
 template <typename T>
@@ -26,7 +29,7 @@ __global__ void k_coef_from_image(Geom gf, const T* __restrict__ P, Geom gc, T* 
 #pragma unroll
     for (int q = 0; q < NCOEF; ++q) acc[q] = T(0);
     for (int di = -1; di <= 1; ++di) {
-        const int i = reflect_clamped(2 * K - 1 + di, gf.Nx);
+        const int i = reflect_row(2 * K - 1 + di, gf);     // slab halo rows: the image carries one more row beyond them
         const T wi = di == 0 ? T(0.5) : T(0.25);
         for (int dj = -1; dj <= 1; ++dj) {
             const int j = reflect_clamped(2 * L - 1 + dj, gf.Ny);
@@ -64,7 +67,7 @@ __global__ void k_restrict(Geom gf, const T* __restrict__ fine, long long fine_p
     int ii[3], jj[3];
 #pragma unroll
     for (int d = 0; d < 3; ++d) {
-        ii[d] = reflect_clamped(2 * K - 2 + d, gf.Nx, gf.far_i);
+        ii[d] = reflect_row(2 * K - 2 + d, gf);
         jj[d] = reflect_clamped(2 * L - 2 + d, gf.Ny, gf.far_j);
     }
     const T w3[3] = {T(0.25), T(0.5), T(0.25)};
@@ -95,8 +98,8 @@ __global__ void k_prolong_add(Geom gc, const T* __restrict__ coarse, Geom gf, T*
     const int pair = blockIdx.z;
     if (j >= gf.Ny) return;
     if (active != nullptr && !active[pair]) return;
-    if (i == 0 || i == gf.Nx - 1 || j == 0 || j == gf.Ny - 1) return;
-    const int i0 = reflect_clamped((i + 1) >> 1, gc.Nx, gc.far_i), i1 = reflect_clamped((i + 2) >> 1, gc.Nx, gc.far_i);
+    if (is_ghost_row(i, gf) || j == 0 || j == gf.Ny - 1) return;      // slab halo rows are corrected like owned rows
+    const int i0 = reflect_row((i + 1) >> 1, gc), i1 = reflect_row((i + 2) >> 1, gc);
     const int j0 = reflect_clamped((j + 1) >> 1, gc.Ny, gc.far_j), j1 = reflect_clamped((j + 2) >> 1, gc.Ny, gc.far_j);
 #pragma unroll
     for (int q = 0; q < 3; ++q) {
@@ -117,8 +120,8 @@ __global__ void __launch_bounds__(128) k_prolong_add4(Geom gc, const float* __re
     const int pair = blockIdx.z;
     if (j4 >= gf.Ny) return;
     if (active != nullptr && !active[pair]) return;
-    if (i == 0 || i == gf.Nx - 1) return;
-    const int i0 = reflect_clamped((i + 1) >> 1, gc.Nx, gc.far_i), i1 = reflect_clamped((i + 2) >> 1, gc.Nx, gc.far_i);
+    if (is_ghost_row(i, gf)) return;
+    const int i0 = reflect_row((i + 1) >> 1, gc), i1 = reflect_row((i + 2) >> 1, gc);
     const int m2 = j4 >> 1;
     const int c0 = reflect_clamped(m2, gc.Ny, gc.far_j), c1 = reflect_clamped(m2 + 1, gc.Ny, gc.far_j),
               c2 = reflect_clamped(m2 + 2, gc.Ny, gc.far_j);
