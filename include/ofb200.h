@@ -37,6 +37,8 @@ extern "C" {
 #define OFB_FLAG_NO_FUSED_TAIL 2 /* run the small multigrid levels as separate launches (A/B measurements) */
 #define OFB_FLAG_LEGACY_COARSE_BOUNDARY 4 /* node-mirror far boundary on every coarse level (A/B measurements) */
 
+#define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
+
 #define OFB_ABI_VERSION 3
 
 typedef struct ofb_solve_options {
@@ -144,6 +146,9 @@ int ofb_slab_local_rows(const ofb_slab* slab, int* first_row, int* owned_rows);
 int ofb_comm_unique_id(void* id128);
 int ofb_comm_create(const void* id128, int rank, int world, void** comm_out);
 int ofb_comm_destroy(void* comm);
+/* 1 if the halo rows travel by peer stores into CUDA-IPC mailboxes (all ranks could map their neighbours),
+ * 0 if the exchanges fall back to ncclSend/ncclRecv. */
+int ofb_comm_peer_halo(void* comm);
 size_t ofb_slab_workspace_bytes(int B, int Ny, int dtype, const ofb_slab* slab);
 /* ofb_solve on a slab; every rank of slab->comm must make the same call.  Scalars, iteration counts and the
  * convergence decision are identical on all ranks. */

@@ -13,13 +13,14 @@ PRECOND_BJACOBI, PRECOND_MG = 0, 1
 FLAG_NO_STREAM = 1
 FLAG_NO_FUSED_TAIL = 2
 FLAG_LEGACY_COARSE_BOUNDARY = 4
+FLAG_SLAB_NCCL_HALO = 8
 ABI_VERSION = 3
 
 # every symbol include/ofb200.h declares
 EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_workspace_bytes', 'ofb_blur',
                     'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_smooth', 'ofb_solve', 'ofb_precondition',
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
-                    'ofb_comm_destroy', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab')
+                    'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab')
 
 
 class SolveOptions(ctypes.Structure):
@@ -93,6 +94,8 @@ def load():
     lib.ofb_comm_create.argtypes = [vp, i, i, ctypes.POINTER(ctypes.c_void_p)]
     lib.ofb_comm_destroy.restype = i
     lib.ofb_comm_destroy.argtypes = [vp]
+    lib.ofb_comm_peer_halo.restype = i
+    lib.ofb_comm_peer_halo.argtypes = [vp]
     lib.ofb_slab_workspace_bytes.restype = sz
     lib.ofb_slab_workspace_bytes.argtypes = [i, i, i, slabp]
     lib.ofb_solve_slab.restype = i

@@ -57,9 +57,25 @@ inline NcclApi& nccl_api() {
     return api;
 }
 
+// Mailbox for halo rows written directly by the neighbouring GPU (peer stores over NVLink, CUDA IPC mapping).
+// Layout of a rank's mailbox:  4 x u64 arrival flags [dir][parity] | int error | pad to 256 | 4 data slots [dir][parity].
+// dir 0 = rows arriving from rank-1, dir 1 = rows arriving from rank+1.  Exchange number `seq` (identical on all
+// ranks) uses the slots of parity seq & 1: a rank can be at most one exchange ahead of its neighbour, so two slots
+// per direction are enough.
+struct PeerBox {
+    unsigned char* local;           // this rank's mailbox
+    unsigned char* peer[2];         // rank-1's / rank+1's mailbox mapped into this process (nullptr: no such neighbour)
+    size_t slot_bytes;
+    unsigned long long seq;         // exchanges issued so far
+    bool ok;
+};
+constexpr size_t PEERBOX_HEADER = 256;
+constexpr size_t PEERBOX_SLOT_BYTES = 4u << 20;      // per (direction, parity): 7 planes x 32768 columns x fp32 and more
+
 struct Comm {
     ncclComm_t comm;
     int rank, world;
+    PeerBox box;
 };
 
 template <typename T> struct NcclType;

@@ -10,6 +10,7 @@
 #include "misc_kernels.cuh"
 #include "stream_sweep.cuh"
 #include "comm.h"
+#include "halo_exchange.cuh"
 #include "coarse_fused.cuh"
 
 using namespace ofb;
@@ -334,6 +335,21 @@ template <typename T> struct Solver {
         if (!distributed(l)) return 0;
         const Geom& G = g[l];
         if (!G.halo_lo && !G.halo_hi) return 0;
+        PeerBox& box = slab.comm->box;
+        if (box.ok && (opt.flags & OFB_FLAG_SLAB_NCCL_HALO) == 0 &&
+            (size_t)B * nplanes * G.pitch * sizeof(T) <= box.slot_bytes) {
+            // rows written straight into the neighbour's mailbox by peer stores (halo_exchange.cuh)
+            HaloArgs<T> A;
+            A.base = base; A.plane = G.plane; A.pair_stride = pair_stride; A.nplanes = nplanes; A.B = B; A.Nx = G.Nx; A.pitch = G.pitch;
+            A.local = box.local;
+            A.peer[0] = G.halo_lo ? box.peer[0] : nullptr;
+            A.peer[1] = G.halo_hi ? box.peer[1] : nullptr;
+            A.seq = ++box.seq; A.header = PEERBOX_HEADER; A.slot_bytes = box.slot_bytes;
+            A.timeout_ns = 4000000000ull;
+            k_halo_exchange<T><<<2, 1024, 0, stream>>>(A);
+            OFB_CHECK_LAUNCH();
+            return 0;
+        }
         NcclApi& api = nccl_api();
         const ncclDataType_t dt = NcclType<T>::value;
         const size_t cnt = (size_t)G.pitch;
@@ -747,6 +763,13 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     }
     k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out);
     OFB_CHECK_LAUNCH();
+    if (S.slab.on && S.slab.comm->box.ok) {
+        int err = 0;
+        OFB_CHECK_CUDA(cudaMemcpyAsync(&err, S.slab.comm->box.local + 4 * sizeof(unsigned long long), sizeof(int),
+                                       cudaMemcpyDeviceToHost, stream));
+        OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+        if (err) return fail(-40, "halo exchange timed out waiting for a neighbouring rank");
+    }
     return 0;
 }
 
@@ -1011,17 +1034,64 @@ int ofb_comm_create(const void* id128, int rank, int world, void** comm_out) {
     ncclUniqueId id;
     memcpy(&id, id128, sizeof(id));
     Comm* c = new Comm;
-    c->rank = rank; c->world = world; c->comm = nullptr;
+    memset(c, 0, sizeof(*c));
+    c->rank = rank; c->world = world;
     ncclResult_t r = api.CommInitRank(&c->comm, world, id, rank);
     if (r != ncclSuccess) { delete c; return fail(-2000 - (int)r, "ncclCommInitRank: %s", api.GetErrorString(r)); }
+    // Peer mailboxes for the halo rows: allocate, publish the IPC handle through the communicator, map the neighbours'.
+    // Any failure on any rank leaves box.ok false everywhere and the exchanges fall back to ncclSend/ncclRecv.
+    PeerBox& box = c->box;
+    box.slot_bytes = PEERBOX_SLOT_BYTES;
+    const size_t total = PEERBOX_HEADER + 4 * box.slot_bytes;
+    int good = 1;
+    cudaIpcMemHandle_t mine;
+    memset(&mine, 0, sizeof(mine));
+    if (cudaMalloc((void**)&box.local, total) != cudaSuccess) { box.local = nullptr; good = 0; }
+    if (good && cudaMemset(box.local, 0, total) != cudaSuccess) good = 0;
+    if (good && cudaIpcGetMemHandle(&mine, box.local) != cudaSuccess) good = 0;
+    cudaGetLastError();
+    unsigned char* dbuf = nullptr;
+    const size_t hb = sizeof(cudaIpcMemHandle_t);
+    std::vector<unsigned char> all(hb * world);
+    if (cudaMalloc((void**)&dbuf, hb * world + 2 * sizeof(int)) != cudaSuccess) {
+        api.CommDestroy(c->comm); delete c;
+        return fail(-32, "cudaMalloc failed while setting up the communicator");
+    }
+    OFB_CHECK_CUDA(cudaMemcpy(dbuf + hb * rank, &mine, hb, cudaMemcpyHostToDevice));
+    OFB_CHECK_NCCL(api.AllGather(dbuf + hb * rank, dbuf, hb, ncclChar, c->comm, 0));
+    OFB_CHECK_CUDA(cudaStreamSynchronize(0));
+    OFB_CHECK_CUDA(cudaMemcpy(all.data(), dbuf, hb * world, cudaMemcpyDeviceToHost));
+    for (int side = 0; side < 2 && good; ++side) {
+        const int nb = side == 0 ? rank - 1 : rank + 1;
+        if (nb < 0 || nb >= world) continue;
+        cudaIpcMemHandle_t h;
+        memcpy(&h, all.data() + hb * nb, hb);
+        void* mapped = nullptr;
+        if (cudaIpcOpenMemHandle(&mapped, h, cudaIpcMemLazyEnablePeerAccess) != cudaSuccess) { good = 0; cudaGetLastError(); }
+        else box.peer[side] = (unsigned char*)mapped;
+    }
+    int* dflag = (int*)(dbuf + hb * world);
+    OFB_CHECK_CUDA(cudaMemcpy(dflag, &good, sizeof(int), cudaMemcpyHostToDevice));
+    OFB_CHECK_NCCL(api.AllReduce(dflag, dflag + 1, 1, ncclInt32, ncclMin, c->comm, 0));
+    OFB_CHECK_CUDA(cudaStreamSynchronize(0));
+    int all_good = 0;
+    OFB_CHECK_CUDA(cudaMemcpy(&all_good, dflag + 1, sizeof(int), cudaMemcpyDeviceToHost));
+    cudaFree(dbuf);
+    box.ok = all_good != 0;
+    box.seq = 0;
     *comm_out = c;
     return 0;
 }
+
+int ofb_comm_peer_halo(void* comm) { return (comm != nullptr && ((Comm*)comm)->box.ok) ? 1 : 0; }
 
 int ofb_comm_destroy(void* comm) {
     if (comm == nullptr) return 0;
     Comm* c = (Comm*)comm;
     NcclApi& api = nccl_api();
+    cudaDeviceSynchronize();
+    for (int side = 0; side < 2; ++side) if (c->box.peer[side]) cudaIpcCloseMemHandle(c->box.peer[side]);
+    if (c->box.local) cudaFree(c->box.local);
     if (api.ok && c->comm) api.CommDestroy(c->comm);
     delete c;
     return 0;

@@ -37,7 +37,10 @@ def copy_pool():
         if _copy_pool is None:
             import concurrent.futures
             import os
-            _copy_pool = concurrent.futures.ThreadPoolExecutor(max_workers=max(2, (os.cpu_count() or 8) - 2),
+            # several ranks on one host (torchrun) share its cores: OFB_COPY_THREADS, else cores / LOCAL_WORLD_SIZE
+            ranks_here = max(1, int(os.environ.get('LOCAL_WORLD_SIZE', '1') or 1))
+            workers = int(os.environ.get('OFB_COPY_THREADS', '0') or 0) or max(2, ((os.cpu_count() or 8) - 2) // ranks_here)
+            _copy_pool = concurrent.futures.ThreadPoolExecutor(max_workers=workers,
                                                                thread_name_prefix='ofb-copy')
     return _copy_pool
 

@@ -55,6 +55,7 @@ class SlabComm:
         handle = ctypes.c_void_p()
         _lib.check(lib.ofb_comm_create(ident, self.rank, self.world, ctypes.byref(handle)))
         self.handle = handle
+        self.peer_halo = bool(lib.ofb_comm_peer_halo(handle))      # halo rows by peer stores (else ncclSend/ncclRecv)
 
     def close(self):
         if self.handle:
@@ -153,7 +154,7 @@ def variational_optical_flow_slab(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1
             its.append(iters); res.append(relres); cvs.append(conv)
         info = {'iterations': torch.cat(its).cpu().numpy(), 'relative_residual': torch.cat(res).cpu().numpy(),
                 'converged': torch.cat(cvs).cpu().numpy().astype(bool), 'rows_per_rank': slab.rows_per_rank,
-                'gather_level': slab.gather_level, 'world': comm.world}
+                'gather_level': slab.gather_level, 'world': comm.world, 'peer_halo': comm.peer_halo}
         dist.all_reduce(fun, group=group)                              # functionals: sum of the ranks' partial sums
         if not gather_result:
             return {'rows': (lo, hi), 'fields': fields, 'functionals': fun.cpu().numpy(), 'solver_info': info}

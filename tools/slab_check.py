@@ -39,7 +39,11 @@ def main():
     ap.add_argument('--cases', default='small')
     ap.add_argument('--time', action='store_true', help='time the slab solve (device events, max over ranks)')
     ap.add_argument('--no-compare', action='store_true')
+    ap.add_argument('--single', action='store_true', help='with --time: also time the whole pair on rank 0 alone')
     ap.add_argument('--gather-level', type=int, default=-1)
+    ap.add_argument('--scan-gather', default='', help='with --time: comma list of gather levels to time')
+    ap.add_argument('--ab', action='store_true', help='with --time: time both halo transports')
+    ap.add_argument('--nccl-halo', action='store_true', help='halo rows by ncclSend/ncclRecv instead of peer stores')
     ap.add_argument('--alpha', type=float, default=1e5)
     ap.add_argument('--beta', type=float, default=1e4)
     ap.add_argument('--repeats', type=int, default=3)
@@ -50,36 +54,66 @@ def main():
     dev = torch.device('cuda', torch.cuda.current_device())
     comm = slab.SlabComm()
     failed = 0
+    from opticalflow_b200 import _lib
+    options = engine.make_options('mg', flags=_lib.FLAG_SLAB_NCCL_HALO) if args.nccl_halo else None
     for (Nx, Ny, dtype, rtol, hint, sigma, tol) in CASES[args.cases]:
         if args.gather_level >= 0:
             hint = args.gather_level
-        movie = synthetic.translating_movie(Nx, Ny, 2, seed=3) if max(Nx, Ny) <= 2048 else synthetic.translating_movie(Nx, Ny, 2, seed=3)
+        movie = synthetic.translating_movie(Nx, Ny, 2, seed=3)
         line = {'case': '%dx%d %s' % (Nx, Ny, dtype), 'world': world, 'sigma': sigma}
         res = slab.variational_optical_flow_slab(movie, speed_alpha=args.alpha, remodelling_alpha=args.beta, smoothing_sigma=sigma,
-                                                 dtype=dtype, rtol=rtol, comm=comm, gather_level=hint,
+                                                 dtype=dtype, rtol=rtol, comm=comm, gather_level=hint, solver_options=options,
                                                  gather_result=not (args.no_compare or args.cases == 'd5'))
         info = res['solver_info'] if res is not None else None
         if rank == 0:
             line.update(iterations=int(info['iterations'][-1]), relres=float(info['relative_residual'][-1]),
-                        converged=bool(info['converged'][-1]), rows_per_rank=info['rows_per_rank'], gather_level=info['gather_level'])
+                        converged=bool(info['converged'][-1]), peer_halo=bool(info['peer_halo']) and not args.nccl_halo, rows_per_rank=info['rows_per_rank'], gather_level=info['gather_level'])
         if args.time:
             tdtype, _ = engine.resolve_dtype(dtype)
-            sl = slab.make_slab(comm, Nx, Ny, hint)
-            frames = slab.local_frames(movie, sl, sigma, tdtype, dev)
-            times = []
-            for _ in range(args.repeats + 1):
-                dist.barrier()
-                torch.cuda.synchronize()
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                x, it, rr, cv = slab.solve_slab(frames[0], frames[1], sl, args.alpha, args.beta, rtol, 1000)
-                e1.record()
-                torch.cuda.synchronize()
-                t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-                dist.all_reduce(t, op=dist.ReduceOp.MAX)
-                times.append(float(t[0]))
-            if rank == 0:
-                line.update(solve_ms=min(times[1:]), solve_ms_all=times[1:], iterations_timed=int(it[0]))
+            scan = [int(v) for v in args.scan_gather.split(',')] if args.scan_gather else [hint]
+            modes = [False, True] if args.ab else [args.nccl_halo]
+            line['timings'] = []
+            for gl in scan:
+                sl = slab.make_slab(comm, Nx, Ny, gl)
+                frames = slab.local_frames(movie, sl, sigma, tdtype, dev)
+                for nccl_mode in modes:
+                    opts = engine.make_options('mg', flags=_lib.FLAG_SLAB_NCCL_HALO) if nccl_mode else None
+                    times = []
+                    for _ in range(args.repeats + 1):
+                        dist.barrier()
+                        torch.cuda.synchronize()
+                        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        e0.record()
+                        x, it, rr, cv = slab.solve_slab(frames[0], frames[1], sl, args.alpha, args.beta, rtol, 1000, opts)
+                        e1.record()
+                        torch.cuda.synchronize()
+                        t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+                        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                        times.append(float(t[0]))
+                    if rank == 0:
+                        line['timings'].append({'gather_level': sl.gather_level, 'halo': 'nccl' if nccl_mode or not comm.peer_halo else 'peer',
+                                                'solve_ms': min(times[1:]), 'all_ms': [round(v, 3) for v in times[1:]],
+                                                'iterations': int(it[0])})
+                del frames
+            if rank == 0 and args.single:
+                # the same pair on one GPU (whole frame), same options: what the slabs are measured against
+                fr = torch.from_numpy(movie).to(device=dev, dtype=tdtype)
+                fr = engine.blur(fr, sigma) if sigma is not None else fr
+                P1, C1 = fr[:1].contiguous(), fr[1:].contiguous()
+                b1 = engine.build_rhs(P1, C1)
+                st = []
+                for _ in range(args.repeats + 1):
+                    x1 = torch.zeros_like(b1)
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    r1 = engine.solve(P1, b1, x1, args.alpha, args.beta, rtol=rtol, max_it=1000)
+                    e1.record()
+                    torch.cuda.synchronize()
+                    st.append(e0.elapsed_time(e1))
+                line.update(single_gpu_solve_ms=min(st[1:]))
+                del fr, P1, C1, b1, x1
+            dist.barrier()
         if rank == 0 and not (args.no_compare or args.cases == 'd5'):
             ref = optical_flow.variational_optical_flow(movie, speed_alpha=args.alpha, remodelling_alpha=args.beta,
                                                         smoothing_sigma=sigma, dtype=dtype, rtol=rtol, device='cuda:0')
@@ -95,8 +129,8 @@ def main():
             failed += 0 if ok else 1
         if rank == 0:
             print(json.dumps(line), flush=True)
-    comm.close()
     dist.barrier()
+    comm.close()
     dist.destroy_process_group()
     sys.exit(1 if failed else 0)
 
