@@ -37,6 +37,10 @@ def parse():
     ap.add_argument('--dtype', default='float32')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true', help='profiling runs only: skip the end-to-end leg')
+    ap.add_argument('--workload', default='d-3', choices=['d-3', 'd-5'],
+                    help="d-3: the headline (1024^2 pairs sharded over the GPUs); d-5: ONE 8192^2 pair slab-decomposed over the "
+                         "GPUs (needs torchrun with >= 2 ranks)")
+    ap.add_argument('--frame', type=int, default=8192, help='d-5: frame size')
     return ap.parse_args()
 
 
@@ -46,7 +50,7 @@ def workload_movie(n_frames, seed):
 
 
 # ------------------------------------------------------------------------------------------ reference / CPU arm
-CPU_CROP = 128
+CPU_CROP = 192
 
 
 def _cpu_pair_task(seed):
@@ -282,9 +286,129 @@ def run_gpu(args):
         dist.destroy_process_group()
 
 
+def run_slab(args):
+    """Config d-5: one 8192^2 frame pair, slab-decomposed over the ranks (halo rows by peer stores, dot products
+    all-reduced, coarse multigrid levels replicated).  A step = blur -> rhs -> solve -> epilogue of that pair."""
+    import torch
+    import torch.distributed as dist
+    from opticalflow_b200 import _lib, engine, slab, synthetic
+    rank, world, local = int(os.environ.get('RANK', '0')), int(os.environ.get('WORLD_SIZE', '1')), int(os.environ.get('LOCAL_RANK', '0'))
+    if world < 2:
+        raise SystemExit('--workload d-5 needs torchrun with at least 2 ranks (one pair is split over the GPUs)')
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    dist.init_process_group('cpu:gloo,cuda:nccl', rank=rank, world_size=world)
+    lib = _lib.load()
+    N = args.frame
+    tdtype, _ = engine.resolve_dtype(args.dtype)
+    itemsize = 4 if args.dtype == 'float32' else 8
+    movie = synthetic.translating_movie(N, N, 2, seed=3).astype(np.float32)
+    comm = slab.SlabComm()
+    sl = slab.make_slab(comm, N, N, 0)
+    sigma, a, be = KW['smoothing_sigma'], KW['speed_alpha'], KW['remodelling_alpha']
+    part, meta = slab.upload_rows(movie, sl, sigma, tdtype, dev)
+    stats = {}
+
+    def device_step():
+        frames = slab.blur_rows(part, meta, sigma)
+        x, it, rr, cv = slab.solve_slab(frames[0], frames[1], sl, a, be, RTOL, 1000)
+        out, fun = slab.epilogue_slab(frames[0], frames[1], x, sl, a, be, 1.0)
+        stats.update(it=it, cv=cv, frames=frames)
+
+    def barrier():
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(max(args.warmup, 3)):
+        device_step()
+    barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = lib.ofb_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        device_step()
+    e1.record()
+    barrier()
+    launches = lib.ofb_launch_count() - launches0
+    ms = e0.elapsed_time(e1)
+    assert int(stats['cv'][0]) == 1, 'the pair did not converge'
+
+    def e2e_step():
+        return slab.variational_optical_flow_slab(movie, speed_alpha=a, remodelling_alpha=be, smoothing_sigma=sigma, dtype=args.dtype,
+                                                  rtol=RTOL, comm=comm, gather_result='local')
+    res = e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    n_e2e = 2
+    for _ in range(n_e2e):
+        res = e2e_step()
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / n_e2e
+    sampler.stop_flag.set()
+    sampler.join()
+    lo, hi = res['rows']
+    h2d = int(part.numel() * itemsize)
+    d2h = int(4 * (hi - lo) * N * itemsize)
+
+    # roofline: the level-0 smoother sweep on this rank's slab
+    frames = stats['frames']
+    Nx_loc = frames.shape[1] - 2
+    P = frames[0][1:Nx_loc + 1].unsqueeze(0)
+    bb = torch.randn((1, 3, Nx_loc, N), dtype=tdtype, device=dev)
+    xin, xo = torch.randn_like(bb), torch.empty_like(bb)
+    for _ in range(3):
+        engine.smooth(P, bb, xin, a, be, out=xo)
+    torch.cuda.synchronize(dev)
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record()
+    for _ in range(20):
+        engine.smooth(P, bb, xin, a, be, out=xo)
+    s1.record()
+    torch.cuda.synchronize(dev)
+    sweep_ms = s0.elapsed_time(s1) / 20
+    alg_bytes = 10 * itemsize * Nx_loc * N
+    achieved = alg_bytes / (sweep_ms * 1e-3) / 1e9
+    peaks_file = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.isfile(peaks_file):
+        peak, peak_src = float(json.load(open(peaks_file))['hbm_gbs']), 'MEASURED_PEAKS.json hbm_gbs'
+    else:
+        peak, peak_src = 6650.0, 'fallback (B200_PROFILING.md)'
+    t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    tot = torch.tensor([float(h2d), float(d2h)], dtype=torch.float64, device=dev)
+    dist.all_reduce(tot)
+    if rank == 0:
+        line = dict(metric='frame-pairs/sec at %d^2 (one pair, slab-decomposed)' % N, value=args.steps / (float(t[0]) * 1e-3),
+                    unit='frame-pairs/s', n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3), ms_per_step=float(t[0]) / args.steps,
+                    higher_is_better=True, scaling='strong', vs_baseline=None, dtype='f32' if args.dtype == 'float32' else 'f64',
+                    data='synthetic',
+                    config=dict(workload='d-5: one %d^2 textured pair shifted by (1.5, -0.7) px, alpha 1e5, beta 1e4, sigma 2.5, rtol 1e-6; '
+                                         '%d slabs of %d rows, halo rows by %s, multigrid levels >= %d replicated'
+                                         % (N, world, sl.rows_per_rank, 'peer stores (CUDA IPC mailboxes)' if comm.peer_halo else
+                                            'ncclSend/ncclRecv', sl.gather_level),
+                                parallelism='1-D slab decomposition over %d GPUs' % world, iterations=int(stats['it'][0]),
+                                l2='working set per rank %.1f GB exceeds the 126 MB L2' % (12 * 3 * Nx_loc * N * itemsize / 1e9)),
+                    e2e=dict(value=1.0 / (float(t[1]) * 1e-3), unit='frame-pairs/s', h2d_bytes_per_step=int(tot[0]),
+                             d2h_bytes_per_step=int(tot[1])),
+                    gpu_launches=int(launches),
+                    roofline=dict(bound='hbm', kernel='k_stream<float,true,OpSmooth> level 0 on one slab', achieved=achieved, peak=peak,
+                                  unit='GB/s', frac=achieved / peak, traffic=None, peak_source=peak_src, ms_per_launch=sweep_ms,
+                                  algorithmic_bytes_per_launch=alg_bytes),
+                    clocks=sampler.summary())
+        print(json.dumps(line))
+    dist.barrier()
+    comm.close()
+    dist.destroy_process_group()
+
+
 if __name__ == '__main__':
     a = parse()
     if a.impl == 'reference':
         run_reference(a)
+    elif a.workload == 'd-5':
+        run_slab(a)
     else:
         run_gpu(a)

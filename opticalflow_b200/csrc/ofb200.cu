@@ -210,9 +210,12 @@ int slab_partition(int NxG, int Ny, int world, int hint, int* rows_per_rank, int
     if (max_lg < 1) return fail(-21, "frame %dx%d is too small for a slab-decomposed multigrid solve", NxG, Ny);
     const int per = (NxG - 2 + world - 1) / world;     // interior rows per rank, before rounding
     int Lg = hint;
-    if (Lg <= 0) {                                     // distribute a level while a rank keeps >= 32 rows of it
+    if (Lg <= 0) {
+        // distribute a level while a rank keeps >= 128 rows of it: below that the sweeps are launch-latency bound
+        // and solving the level redundantly on every rank is cheaper than its four halo exchanges per V-cycle
+        // (8192^2 over 8 GPUs: gather level 4 / 5 / 6 = 14.8 / 15.2 / 15.9 ms)
         Lg = 1;
-        while (Lg < max_lg && (per >> Lg) >= 32) ++Lg;
+        while (Lg < max_lg && (per >> Lg) >= 128) ++Lg;
     }
     Lg = std::min(Lg, max_lg);
     for (; Lg >= 1; --Lg) {

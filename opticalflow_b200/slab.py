@@ -69,21 +69,34 @@ def make_slab(comm, Nx, Ny, gather_level=0):
                      comm=comm.handle)
 
 
-def local_frames(movie, slab, sigma, tdtype, device):
-    """This rank's rows of every frame, blurred, as a device tensor [T, owned+4, Ny]: local row m is global row
-    a-2+m (rows outside the frame are zero and never read)."""
+def upload_rows(movie, slab, sigma, tdtype, device):
+    """Host -> device copy of the rows this rank needs: its rows +-2, plus the blur radius.  Returns (tensor, meta)."""
     T, Nx, Ny = movie.shape
     first, owned = owned_rows(Nx, slab.rows_per_rank, slab.rank)
     radius = engine.gaussian_weights(sigma)[1] if sigma is not None else 0
     lo, hi = first - 2, first + owned + 2                              # rows wanted
     src_lo, src_hi = max(lo - radius, 0), min(hi + radius, Nx)         # rows read (blur support)
-    part = torch.from_numpy(np.ascontiguousarray(movie[:, src_lo:src_hi])).to(device=device, dtype=tdtype)
+    part = torch.from_numpy(np.ascontiguousarray(movie[:, src_lo:src_hi])).to(device=device, dtype=tdtype, non_blocking=True)
+    return part, (lo, hi, src_lo, Nx, owned)
+
+
+def blur_rows(part, meta, sigma, out=None):
+    """Blur the uploaded rows and cut out [T, owned+4, Ny]: local row m is global row a-2+m (rows outside the frame
+    are zero and never read).  Rows of `part` whose blur support was cut by the slab edge are dropped here."""
+    lo, hi, src_lo, Nx, owned = meta
     if sigma is not None:
-        part = engine.blur(part, sigma)                                # edges of `part` inside the frame are cut off below
-    out = torch.zeros((T, owned + 4, Ny), dtype=tdtype, device=device)
+        part = engine.blur(part, sigma)
+    T, _, Ny = part.shape
+    out = torch.zeros((T, owned + 4, Ny), dtype=part.dtype, device=part.device) if out is None else out
     g_lo, g_hi = max(lo, 0), min(hi, Nx)
     out[:, g_lo - lo:g_hi - lo] = part[:, g_lo - src_lo:g_hi - src_lo]
     return out
+
+
+def local_frames(movie, slab, sigma, tdtype, device):
+    """This rank's rows of every frame, blurred, as a device tensor [T, owned+4, Ny]."""
+    part, meta = upload_rows(np.asarray(movie), slab, sigma, tdtype, device)
+    return blur_rows(part, meta, sigma)
 
 
 def solve_slab(P_ext, C_ext, slab, speed_alpha, remodelling_alpha, rtol=1e-6, max_it=1000, options=None, x0=None):
@@ -129,7 +142,8 @@ def variational_optical_flow_slab(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1
 
     Call on every rank with the same arguments (torch.distributed initialised, one GPU per rank).  Rank 0 returns
     the reference's result dictionary (plus 'solver_info'); the other ranks return None.  With
-    gather_result=False nothing is gathered and every rank returns its own rows (keys 'rows' = (lo, hi))."""
+    gather_result=False nothing is gathered and every rank returns its own rows as device tensors ('rows' = (lo, hi));
+    gather_result='local' returns them as host float64 arrays."""
     import torch.distributed as dist
     movie = np.asarray(movie)
     T, Nx, Ny = movie.shape
@@ -156,6 +170,10 @@ def variational_optical_flow_slab(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1
                 'converged': torch.cat(cvs).cpu().numpy().astype(bool), 'rows_per_rank': slab.rows_per_rank,
                 'gather_level': slab.gather_level, 'world': comm.world, 'peer_halo': comm.peer_halo}
         dist.all_reduce(fun, group=group)                              # functionals: sum of the ranks' partial sums
+        if gather_result == 'local':        # every rank keeps its own rows, as host float64 arrays like the reference's
+            host = fields.cpu().numpy().astype(np.float64)
+            return {'rows': (lo, hi), 'v_x': host[0], 'v_y': host[1], 'speed': host[2], 'remodelling': host[3],
+                    'functionals': fun.cpu().numpy(), 'solver_info': info}
         if not gather_result:
             return {'rows': (lo, hi), 'fields': fields, 'functionals': fun.cpu().numpy(), 'solver_info': info}
         blurred = frames[:, lo - (first - 2):hi - (first - 2)]
