@@ -305,7 +305,9 @@ def run_slab(args):
     movie = synthetic.translating_movie(N, N, 2, seed=3).astype(np.float32)
     comm = slab.SlabComm()
     sl = slab.make_slab(comm, N, N, 0)
-    sigma, a, be = KW['smoothing_sigma'], KW['speed_alpha'], KW['remodelling_alpha']
+    sigma = KW['smoothing_sigma']
+    a = torch.full((1,), KW['speed_alpha'], dtype=torch.float64, device=dev)
+    be = torch.full((1,), KW['remodelling_alpha'], dtype=torch.float64, device=dev)
     part, meta = slab.upload_rows(movie, sl, sigma, tdtype, dev)
     stats = {}
 
@@ -337,7 +339,7 @@ def run_slab(args):
     assert int(stats['cv'][0]) == 1, 'the pair did not converge'
 
     def e2e_step():
-        return slab.variational_optical_flow_slab(movie, speed_alpha=a, remodelling_alpha=be, smoothing_sigma=sigma, dtype=args.dtype,
+        return slab.variational_optical_flow_slab(movie, speed_alpha=KW['speed_alpha'], remodelling_alpha=KW['remodelling_alpha'], smoothing_sigma=sigma, dtype=args.dtype,
                                                   rtol=RTOL, comm=comm, gather_result='local')
     res = e2e_step()
     barrier()

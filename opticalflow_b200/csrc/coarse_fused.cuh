@@ -82,6 +82,7 @@ __global__ void __launch_bounds__(1024, 1) k_coarse_vcycle(FusedArgs<T> A) {
     extern __shared__ __align__(16) unsigned char fused_smem[];
     T* sm = reinterpret_cast<T*>(fused_smem);
     const int pair = blockIdx.x;
+    pdl_enter();
     if (A.active != nullptr && A.active[pair] == 0) return;
     const int tid = threadIdx.x, nth = blockDim.x;
     const double alpha = A.alpha[pair], beta = A.beta[pair];

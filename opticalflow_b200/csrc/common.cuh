@@ -154,6 +154,16 @@ __device__ __forceinline__ void load_row(Row<T>& r, const T* __restrict__ plane,
     load_row_ptr<T, MODE, false>(r, plane + (long long)row * g.pitch, is_ghost_row(i, g), j0, g, lane, edge_warp);
 }
 
+// ---------------------------------------------------------------- programmatic dependent launch
+// Kernels of the solver loop are launched with the programmatic-stream-serialisation attribute: a kernel lets its
+// successor be scheduled right away (its CTAs take SM slots as this kernel's CTAs retire and run their prologue),
+// and waits here for its predecessor's results before it touches global memory.  Without the attribute both are
+// no-ops.  This hides the launch latency and the prologue of ~400 dependent launches per 16-pair step.
+__device__ __forceinline__ void pdl_enter() {
+    asm volatile("griddepcontrol.launch_dependents;");
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---------------------------------------------------------------- reductions
 __device__ __forceinline__ double warp_sum(double v) {
 #pragma unroll

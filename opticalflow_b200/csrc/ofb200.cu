@@ -46,6 +46,25 @@ std::atomic<long long> g_launches{0};     // kernels launched by this process (d
         if (r__ != ncclSuccess) return fail(-2000 - (int)r__, "%s: %s", #expr, nccl_api().GetErrorString(r__)); \
     } while (0)
 
+// Launch with the programmatic-stream-serialisation attribute (see pdl_enter in common.cuh) when `pdl` is set.
+template <typename... KArgs, typename... Args>
+cudaError_t launch_kernel(bool pdl, void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+#define OFB_LAUNCH(pdl, kern, grid, block, smem, stream, ...)                                      \
+    do {                                                                                            \
+        g_launches.fetch_add(1);                                                                    \
+        OFB_CHECK_CUDA(launch_kernel(pdl, kern, grid, block, smem, stream, __VA_ARGS__));           \
+    } while (0)
+
 constexpr int MAX_LEVELS = 16;
 constexpr int MIN_COARSE = 6;          // keep coarsening while both coarse sizes stay >= this
 constexpr int MAX_DENSE_N = 768;       // largest coarsest system solved with the dense inverse
@@ -71,7 +90,8 @@ inline int device_sms() {
 
 // Streamed (TMA bulk copy + mbarrier ring) sweep: persistent grid of (CTAs per SM) x SMs.
 template <typename T, bool FROM_IMAGE, typename Op>
-int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_strip, bool skip_last_ghost, cudaStream_t stream) {
+int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_strip, bool skip_last_ghost, cudaStream_t stream,
+                  bool pdl = false) {
     using C = StreamCfg<T>;
     using Lay = StreamLayout<T, FROM_IMAGE, Op>;
     auto kern = k_stream<T, FROM_IMAGE, Op>;
@@ -90,6 +110,9 @@ int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_
     // On coarse levels the last column is a ghost column that no kernel ever reads from memory (every reader
     // mirrors it from column Ny-3), so tiles need not cover it: 513 columns are one 512-wide tile, not two.
     L.tiles_x = ((skip_last_ghost ? L.g.Ny - 1 : L.g.Ny) + C::TW - 1) / C::TW;
+    // wide frames: let concurrently running CTAs read neighbouring column tiles of the same rows (whole DRAM pages);
+    // 8192 columns: 0.85 -> 0.90 of the HBM peak, neutral at 1024 columns
+    if (L.tiles_x >= 4) L.tile_fastest = 1;
     int R = rows_per_strip;
     if (R <= 0) {
         // Persistent CTAs take work items round-robin, so a launch lasts ceil(items / slots) rounds of one item
@@ -112,8 +135,7 @@ int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_
     const long long n_items = (long long)L.tiles_x * L.strips * B;
     if (n_items > 0x7fffffffLL) return fail(-10, "too many work items");
     const int grid = (int)std::min<long long>(n_items, slots);
-    kern<<<grid, C::THREADS, Lay::SMEM_BYTES, stream>>>(L, x, op, (int)n_items);
-    OFB_CHECK_LAUNCH();
+    OFB_LAUNCH(pdl, kern, dim3(grid), dim3(C::THREADS), Lay::SMEM_BYTES, stream, L, x, op, (int)n_items);
     return 0;
 }
 
@@ -332,6 +354,7 @@ template <typename T> struct Solver {
     Geom g_stage;                    // local geometry of the staging planes at the gather level
 
     // ---- slab communication (no-ops for ordinary solves) ------------------------------------------------
+    bool pdl() const { return (opt.flags & OFB_FLAG_NO_PDL) == 0; }
     bool distributed(int l) const { return slab.on && l < slab.Lg; }
     // refresh the halo rows of `nplanes` planes per pair on level l from the neighbouring slabs
     int exchange(int l, T* base, int nplanes, long long pair_stride) {
@@ -425,6 +448,7 @@ template <typename T> struct Solver {
         }
         L.rows_per_strip = R;
         L.strips = (g[l].Nx + R - 1) / R;
+        L.tile_fastest = (opt.flags & OFB_FLAG_TILE_FASTEST) ? 1 : 0;
         return L;
     }
 
@@ -435,15 +459,14 @@ template <typename T> struct Solver {
     template <typename Op> int sweep(int l, const T* x, Op op) {
         const LevelArgs<T> L = level_args(l);
         if (use_stream(l)) {
-            if (l == 0) return launch_stream<T, true, Op>(L, x, op, B, opt.rows_per_strip, false, stream);
-            return launch_stream<T, false, Op>(L, x, op, B, opt.rows_per_strip, true, stream);
+            if (l == 0) return launch_stream<T, true, Op>(L, x, op, B, opt.rows_per_strip, false, stream, pdl());
+            return launch_stream<T, false, Op>(L, x, op, B, opt.rows_per_strip, true, stream, pdl());
         }
         const int warps_per_block = 4;
         const int items = L.tiles_x * L.strips;
         dim3 grid((items + warps_per_block - 1) / warps_per_block, B);
-        if (l == 0) k_sweep<T, true, Op><<<grid, warps_per_block * 32, 0, stream>>>(L, x, op);
-        else        k_sweep<T, false, Op><<<grid, warps_per_block * 32, 0, stream>>>(L, x, op);
-        OFB_CHECK_LAUNCH();
+        if (l == 0) OFB_LAUNCH(pdl(), (k_sweep<T, true, Op>), grid, dim3(warps_per_block * 32), 0, stream, L, x, op);
+        else        OFB_LAUNCH(pdl(), (k_sweep<T, false, Op>), grid, dim3(warps_per_block * 32), 0, stream, L, x, op);
         return 0;
     }
 
@@ -534,8 +557,7 @@ template <typename T> struct Solver {
             configured[dev] = true;
         }
         const size_t smem = (size_t)off * sizeof(T);
-        kern<<<B, 1024, smem, stream>>>(A);
-        OFB_CHECK_LAUNCH();
+        OFB_LAUNCH(pdl(), kern, dim3(B), dim3(1024), smem, stream, A);
         return 0;
     }
 
@@ -561,8 +583,7 @@ template <typename T> struct Solver {
             const Geom gc = gather ? g_stage : g[lc];
             T* lb = gather ? w.stage : w.lb[lc];
             dim3 block(128), grid((gc.Ny + 127) / 128, gc.Nx, B);
-            k_restrict<T, false><<<grid, block, 0, stream>>>(g[l], res, g[l].pair, gc, lb, gc.pair, 3, active);
-            OFB_CHECK_LAUNCH();
+            OFB_LAUNCH(pdl(), (k_restrict<T, false>), grid, block, 0, stream, g[l], (const T*)res, g[l].pair, gc, lb, gc.pair, 3, active);
             if (gather && (rc = gather_planes(w.stage, gc.pair, w.lb[lc], g[lc].pair, 3))) return rc;
         }
         T* ec = nullptr;
@@ -593,15 +614,13 @@ template <typename T> struct Solver {
             if constexpr (sizeof(T) == 4) {
                 if (g[l].aligned && g[l].Ny % 4 == 0) {
                     dim3 block(128), grid((g[l].Ny / 4 + 127) / 128, g[l].Nx, B);
-                    k_prolong_add4<<<grid, block, 0, stream>>>(gcv, ecv, g[l], cur, active);
-                    OFB_CHECK_LAUNCH();
+                    OFB_LAUNCH(pdl(), k_prolong_add4, grid, block, 0, stream, gcv, ecv, g[l], cur, active);
                     done = true;
                 }
             }
             if (!done) {
                 dim3 block(128), grid((g[l].Ny + 127) / 128, g[l].Nx, B);
-                k_prolong_add<T><<<grid, block, 0, stream>>>(gcv, ecv, g[l], cur, active);
-                OFB_CHECK_LAUNCH();
+                OFB_LAUNCH(pdl(), k_prolong_add<T>, grid, block, 0, stream, gcv, ecv, g[l], cur, active);
             }
         }
         for (int s = 0; s < opt.nu_post; ++s) {
@@ -680,6 +699,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
                const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
                int* converged_out, int B, int Nx, int Ny, void* stream_, const ofb_slab* sl = nullptr) {
     Solver<T> S;
+    memset(&S.slab, 0, sizeof(S.slab));
     int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, b3, x3, sl);
     if (rc) return rc;
     cudaStream_t stream = S.stream;
@@ -731,8 +751,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
             if ((rc = S.sweep(0, ph, op))) return rc;
         }
         if ((rc = S.allreduce_acc())) return rc;
-        k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 1, rtol, max_it, nullptr);
-        OFB_CHECK_LAUNCH();
+        OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 1, rtol, max_it, (int*)nullptr);
         {   // s = r - alpha v ; z = w D^-1 s
             OpDirJacobi<T, 1> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.d = w.s; op.z = sh_first; op.w = wj; op.st = w.st;
             if ((rc = S.sweep(0, nullptr, op))) return rc;
@@ -743,15 +762,13 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
             if ((rc = S.sweep(0, sh, op))) return rc;
         }
         if ((rc = S.allreduce_acc())) return rc;
-        k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 2, rtol, max_it, nullptr);
-        OFB_CHECK_LAUNCH();
-        k_update_x_r<T><<<blas_grid, tb, 0, stream>>>(nvec, nvec, x, ph, sh, w.r, w.s, w.t, w.rhat, w.st);
-        OFB_CHECK_LAUNCH();
+        OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 2, rtol, max_it, (int*)nullptr);
+        OFB_LAUNCH(S.pdl(), k_update_x_r<T>, blas_grid, dim3(tb), 0, stream, nvec, nvec, x, (const T*)ph, (const T*)sh, w.r, (const T*)w.s,
+                   (const T*)w.t, (const T*)w.rhat, w.st);
         const bool poll = ((it + 1) % S.opt.check_every == 0) || (it + 1 == max_it);
         if (poll) OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active, 0, sizeof(int), stream));
         if ((rc = S.allreduce_acc())) return rc;
-        k_scalars<<<sb, 128, 0, stream>>>(w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : nullptr);
-        OFB_CHECK_LAUNCH();
+        OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : (int*)nullptr);
         if (poll) {
             OFB_CHECK_CUDA(cudaMemcpyAsync(&host_active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
             OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
@@ -780,6 +797,7 @@ template <typename T>
 int precondition_impl(const void* P, const void* r3, void* z3, const double* alpha, const double* beta, const ofb_solve_options* opt,
                       void* workspace, size_t workspace_bytes, int B, int Nx, int Ny, void* stream_) {
     Solver<T> S;
+    memset(&S.slab, 0, sizeof(S.slab));
     int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, r3, z3);
     if (rc) return rc;
     const bool mg = (S.opt.precond == OFB_PRECOND_MG && S.plan.nlevels > 1);
@@ -860,6 +878,7 @@ template <typename T>
 int apply_elim_impl(const void* P, const void* x3, void* y3, const double* alpha, const double* beta, int B, int Nx, int Ny,
                     void* stream) {
     Solver<T> S;
+    memset(&S.slab, 0, sizeof(S.slab));
     ofb_default_options(&S.opt);
     S.opt.precond = OFB_PRECOND_BJACOBI;
     S.B = B;
@@ -875,6 +894,7 @@ template <typename T>
 int smooth_impl(const void* P, const void* b3, const void* x_in, void* x_out, const double* alpha, const double* beta,
                 const ofb_solve_options* opt, int B, int Nx, int Ny, void* stream) {
     Solver<T> S;
+    memset(&S.slab, 0, sizeof(S.slab));
     if (opt) S.opt = *opt; else ofb_default_options(&S.opt);
     S.opt.precond = OFB_PRECOND_BJACOBI;
     S.B = B;

@@ -193,6 +193,7 @@ template <typename T, int KIND> struct OpDirJacobi {
 
 template <typename T, bool FROM_IMAGE, typename Op>
 __global__ void __launch_bounds__(128) k_sweep(LevelArgs<T> L, const T* __restrict__ x, Op op) {
+    pdl_enter();
     sweep_body<T, FROM_IMAGE, Op>(L, x, op);
 }
 
@@ -204,6 +205,7 @@ __global__ void __launch_bounds__(256) k_update_x_r(long long n_per_pair, long l
                                                     T* __restrict__ x, const T* __restrict__ ph, const T* __restrict__ sh,
                                                     T* __restrict__ r, const T* __restrict__ s, const T* __restrict__ t,
                                                     const T* __restrict__ rhat, PairState* __restrict__ st) {
+    pdl_enter();
     const int pair = blockIdx.y;
     double acc[2] = {0.0, 0.0};
     if (st[pair].active) {
@@ -229,6 +231,7 @@ __global__ void __launch_bounds__(256) k_update_x_r(long long n_per_pair, long l
 // stage 3: after the x/r update         (acc[2] = r.r, acc[3] = rhat.r) -> convergence test, beta_k
 __global__ void k_scalars(PairState* __restrict__ st, int* __restrict__ active_arr, int B, int stage, double rtol, int max_it,
                           int* __restrict__ n_active) {
+    pdl_enter();
     const int pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= B) return;
     PairState s = st[pair];

@@ -60,6 +60,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
     }
     fence_proxy_async();
     __syncthreads();
+    pdl_enter();                                        // everything above overlaps the tail of the previous kernel
 
     const int items_per_pair = L.tiles_x * L.strips;
     uint32_t n = 0;                                     // running stage counter (continues across items)
@@ -74,7 +75,8 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
             const int pair = item / items_per_pair;
             if (L.active != nullptr && L.active[pair] == 0) continue;
             const int rem = item - pair * items_per_pair;
-            const int tile = rem / L.strips, strip = rem - tile * L.strips;
+            const int tile = L.tile_fastest ? rem % L.tiles_x : rem / L.strips;
+            const int strip = L.tile_fastest ? rem / L.tiles_x : rem - tile * L.strips;
             const int c0 = tile * C::TW;
             const int lo = max(c0 - C::HALO, 0), hi = min(c0 + C::TW + C::HALO, g.pitch);
             const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(T);
@@ -119,7 +121,8 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
             const int pair = item / items_per_pair;
             if (L.active != nullptr && L.active[pair] == 0) continue;
             const int rem = item - pair * items_per_pair;
-            const int tile = rem / L.strips, strip = rem - tile * L.strips;
+            const int tile = L.tile_fastest ? rem % L.tiles_x : rem / L.strips;
+            const int strip = L.tile_fastest ? rem / L.tiles_x : rem - tile * L.strips;
             const int c0 = tile * C::TW;
             const int cw0 = c0 + warp * (WARP * V);
             const int j0 = cw0 + lane * V;

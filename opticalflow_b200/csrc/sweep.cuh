@@ -21,6 +21,7 @@ template <typename T> struct LevelArgs {
     int rows_per_strip;
     int tiles_x;            // warp tiles per row
     int strips;             // row strips per pair
+    int tile_fastest;       // streamed sweep: consecutive work items are neighbouring column tiles of one strip
 };
 
 template <typename T, bool FROM_IMAGE> struct CoefRows {

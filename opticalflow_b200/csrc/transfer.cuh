@@ -58,6 +58,7 @@ __global__ void k_coef_from_image(Geom gf, const T* __restrict__ P, Geom gc, T* 
 template <typename T, bool COEF>
 __global__ void k_restrict(Geom gf, const T* __restrict__ fine, long long fine_pair, Geom gc, T* __restrict__ coarse,
                            long long coarse_pair, int nplanes, const int* __restrict__ active) {
+    pdl_enter();
     const int L = blockIdx.x * blockDim.x + threadIdx.x;
     const int K = blockIdx.y;
     const int pair = blockIdx.z;
@@ -93,6 +94,7 @@ __global__ void k_restrict(Geom gf, const T* __restrict__ fine, long long fine_p
 template <typename T>
 __global__ void k_prolong_add(Geom gc, const T* __restrict__ coarse, Geom gf, T* __restrict__ fine,
                               const int* __restrict__ active) {
+    pdl_enter();
     const int j = blockIdx.x * blockDim.x + threadIdx.x;
     const int i = blockIdx.y;
     const int pair = blockIdx.z;
@@ -115,6 +117,7 @@ __global__ void k_prolong_add(Geom gc, const T* __restrict__ coarse, Geom gf, T*
 // Requires fp32, Ny % 4 == 0 and 16-byte aligned fine rows.
 __global__ void __launch_bounds__(128) k_prolong_add4(Geom gc, const float* __restrict__ coarse, Geom gf, float* __restrict__ fine,
                                                       const int* __restrict__ active) {
+    pdl_enter();
     const int j4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
     const int i = blockIdx.y;
     const int pair = blockIdx.z;

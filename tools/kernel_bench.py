@@ -32,6 +32,7 @@ def timeit(fn, reps=20, warm=3):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--n', type=int, default=1024)
+    ap.add_argument('--nx', type=int, default=0, help='rows (default --n)')
     ap.add_argument('--batch', type=int, default=16)
     ap.add_argument('--dtype', default='float32')
     ap.add_argument('--rows', default='0,8,16,24,32,48,64,128')
@@ -40,18 +41,19 @@ def main():
     tdtype, _ = engine.resolve_dtype(a.dtype)
     w = 4 if a.dtype == 'float32' else 8
     B, N = a.batch, a.n
+    NX = a.nx or N
     peak = 6650.0
     pf = os.path.join(ROOT, 'MEASURED_PEAKS.json')
     if os.path.isfile(pf):
         peak = float(json.load(open(pf))['hbm_gbs'])
     g = torch.Generator(device=dev).manual_seed(0)
-    P = (torch.rand((B, N, N), device=dev, generator=g, dtype=tdtype) * 100 + 50).contiguous()
-    b = torch.randn((B, 3, N, N), device=dev, generator=g, dtype=tdtype)
-    x = torch.randn((B, 3, N, N), device=dev, generator=g, dtype=tdtype)
+    P = (torch.rand((B, NX, N), device=dev, generator=g, dtype=tdtype) * 100 + 50).contiguous()
+    b = torch.randn((B, 3, NX, N), device=dev, generator=g, dtype=tdtype)
+    x = torch.randn((B, 3, NX, N), device=dev, generator=g, dtype=tdtype)
     y = torch.empty_like(x)
     alpha = torch.full((B,), 1e5, dtype=torch.float64, device=dev)
     beta = torch.full((B,), 1e4, dtype=torch.float64, device=dev)
-    px = B * N * N
+    px = B * NX * N
 
     def report(name, ms, words):
         gbs = words * w * px / (ms * 1e-3) / 1e9
@@ -59,7 +61,7 @@ def main():
 
     ms = timeit(lambda: y.copy_(x))
     report('torch copy (3 planes r+w)', ms, 6)
-    for flags, tag in ((0, 'stream'), (_lib.FLAG_NO_STREAM, 'register')):
+    for flags, tag in ((0, 'stream'), (_lib.FLAG_TILE_FASTEST, 'stream tile-fastest'), (_lib.FLAG_NO_STREAM, 'register')):
         for rows in [int(r) for r in a.rows.split(',')]:
             ms = timeit(lambda: engine.smooth(P, b, x, alpha, beta, rows_per_strip=rows, out=y, flags=flags))
             report('smooth %s rows=%d' % (tag, rows), ms, 10)
