@@ -38,6 +38,7 @@ extern "C" {
 #define OFB_FLAG_LEGACY_COARSE_BOUNDARY 4 /* node-mirror far boundary on every coarse level (A/B measurements) */
 
 #define OFB_FLAG_TILE_FASTEST 16 /* streamed sweeps: neighbouring column tiles of a strip run concurrently (A/B measurements) */
+#define OFB_FLAG_STRIP_ITEMS 64 /* streamed sweeps: fixed-size row strips dealt round-robin instead of the balanced walk (A/B) */
 #define OFB_FLAG_NO_PDL 32 /* plain stream-ordered launches instead of programmatic dependent launch (A/B measurements) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 

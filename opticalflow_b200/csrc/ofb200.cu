@@ -110,16 +110,27 @@ int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_
     // On coarse levels the last column is a ghost column that no kernel ever reads from memory (every reader
     // mirrors it from column Ny-3), so tiles need not cover it: 513 columns are one 512-wide tile, not two.
     L.tiles_x = ((skip_last_ghost ? L.g.Ny - 1 : L.g.Ny) + C::TW - 1) / C::TW;
+    L.n_pairs = B;
     // wide frames: let concurrently running CTAs read neighbouring column tiles of the same rows (whole DRAM pages);
     // 8192 columns: 0.85 -> 0.90 of the HBM peak, neutral at 1024 columns
     if (L.tiles_x >= 4) L.tile_fastest = 1;
     int R = rows_per_strip;
+    if (R <= 0 && L.tiles_x < 4 && !(L.tile_fastest) && !L.balanced) {
+        // balanced walk: every persistent CTA gets the same number of rows of the end-to-end (pair, tile) columns
+        const long long columns = (long long)L.tiles_x * B;
+        const long long total_rows = columns * L.g.Nx;
+        if (columns > 0x7fffffffLL) return fail(-10, "too many work items");
+        L.balanced = 1;
+        L.rows_per_strip = L.g.Nx; L.strips = 1;
+        const int grid = (int)std::max<long long>(1, std::min<long long>(slots, total_rows / 8));
+        OFB_LAUNCH(pdl, kern, dim3(grid), dim3(C::THREADS), Lay::SMEM_BYTES, stream, L, x, op, (int)columns);
+        return 0;
+    }
+    L.balanced = 0;
     if (R <= 0) {
         // Persistent CTAs take work items round-robin, so a launch lasts ceil(items / slots) rounds of one item
         // each; an item costs its R rows plus the two extra window rows (only the windowed streams re-read them).
-        // Pick the strip length that minimises rounds x item cost: it balances the tail of the last round
-        // against halo re-reads (e.g. 513 rows x 16 pairs: 16-row strips leave 528 items on 444 slots - two
-        // rounds for 1.2 rounds of work - while 5-row strips fill 5 rounds evenly).
+        // Pick the strip length that minimises rounds x item cost.
         const double halo = 2.0 * (double)Lay::NWIN / (double)Lay::NROWS;
         double best = 1e300;
         for (int r = 4; r <= 64; ++r) {
@@ -449,6 +460,8 @@ template <typename T> struct Solver {
         L.rows_per_strip = R;
         L.strips = (g[l].Nx + R - 1) / R;
         L.tile_fastest = (opt.flags & OFB_FLAG_TILE_FASTEST) ? 1 : 0;
+        L.balanced = (opt.flags & OFB_FLAG_STRIP_ITEMS) ? 1 : 0;      // launch_stream: 1 here = balanced walk disabled
+        L.n_pairs = B;
         return L;
     }
 

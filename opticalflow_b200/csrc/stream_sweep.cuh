@@ -41,6 +41,65 @@ template <typename T, bool FROM_IMAGE, typename Op> struct StreamLayout {
 
 template <int N> using IC = std::integral_constant<int, N>;
 
+// Work distribution over the persistent CTAs (identical walk in the producer and the consumer warps).
+//   strips   : work items = (pair, column tile, strip of rows_per_strip rows); CTA c takes items c, c+G, c+2G, ...
+//   balanced : the (pair, tile) columns are laid end to end, rows fastest, and cut into G equal row ranges; a CTA
+//              walks its range and restarts its window where the range runs into the next column.  Every CTA gets
+//              the same number of rows (+- 1), so there is no partly filled last round: 16 pairs of 1024^2 on 444
+//              CTAs cost 74 + ~3 rows per CTA instead of two rounds of 38 + 2.5.
+template <typename T> struct WorkWalk {
+    const LevelArgs<T>& L;
+    long long cur, end;
+    int item, n_items;
+    int scan_pair, scan_seen;        // balanced: pairs examined so far / active pairs among them
+    __device__ __forceinline__ WorkWalk(const LevelArgs<T>& L_, int n_items_, int n_pairs)
+        : L(L_), cur(0), end(0), item(blockIdx.x), n_items(n_items_), scan_pair(0), scan_seen(0) {
+        if (L.balanced) {
+            // only the pairs that are still iterating are laid end to end: late iterations with a few active pairs
+            // are spread over all CTAs like the early ones
+            int n_act = n_pairs;
+            if (L.active != nullptr) {
+                n_act = 0;
+                for (int p = 0; p < n_pairs; ++p) n_act += (L.active[p] != 0) ? 1 : 0;
+            }
+            const long long total = (long long)n_act * L.tiles_x * L.g.Nx;
+            cur = (long long)blockIdx.x * total / gridDim.x;
+            end = (long long)(blockIdx.x + 1) * total / gridDim.x;
+        }
+    }
+    __device__ __forceinline__ bool next(int& pair, int& tile, int& i_begin, int& i_end) {
+        if (L.balanced) {
+            if (cur >= end) return false;
+            const long long col = cur / L.g.Nx;
+            i_begin = (int)(cur - col * L.g.Nx);
+            const int logical = (int)(col / L.tiles_x);                    // index among the active pairs
+            tile = (int)(col - (long long)logical * L.tiles_x);
+            if (L.active != nullptr) {
+                while (true) {                                             // advance to the logical-th active pair
+                    if (L.active[scan_pair] != 0) { if (scan_seen == logical) break; ++scan_seen; }
+                    ++scan_pair;
+                }
+                pair = scan_pair;
+            } else {
+                pair = logical;
+            }
+            i_end = (int)min((long long)L.g.Nx, (long long)i_begin + (end - cur));
+            cur += i_end - i_begin;
+            return true;
+        }
+        if (item >= n_items) return false;
+        const int items_per_pair = L.tiles_x * L.strips;
+        pair = item / items_per_pair;
+        const int rem = item - pair * items_per_pair;
+        tile = L.tile_fastest ? rem % L.tiles_x : rem / L.strips;
+        const int strip = L.tile_fastest ? rem / L.tiles_x : rem - tile * L.strips;
+        i_begin = strip * L.rows_per_strip;
+        i_end = min(i_begin + L.rows_per_strip, L.g.Nx);
+        item += gridDim.x;
+        return true;
+    }
+};
+
 template <typename T, bool FROM_IMAGE, typename Op>
 __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T> L, const T* __restrict__ x, Op op, int n_items) {
     using C = StreamCfg<T>;
@@ -62,7 +121,6 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
     __syncthreads();
     pdl_enter();                                        // everything above overlaps the tail of the previous kernel
 
-    const int items_per_pair = L.tiles_x * L.strips;
     uint32_t n = 0;                                     // running stage counter (continues across items)
 
     if (warp == C::CW) {
@@ -71,17 +129,13 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
         // then the centre rows: NCEN vectors x 3 planes, then 7 coefficient planes (!FROM_IMAGE).
         const bool is_win = lane < NWIN;
         const bool is_sol = Op::NEED_X && lane < 3;
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int pair = item / items_per_pair;
+        WorkWalk<T> walk(L, n_items, L.n_pairs);
+        int pair, tile, i_begin, i_end;
+        while (walk.next(pair, tile, i_begin, i_end)) {
             if (L.active != nullptr && L.active[pair] == 0) continue;
-            const int rem = item - pair * items_per_pair;
-            const int tile = L.tile_fastest ? rem % L.tiles_x : rem / L.strips;
-            const int strip = L.tile_fastest ? rem / L.tiles_x : rem - tile * L.strips;
             const int c0 = tile * C::TW;
             const int lo = max(c0 - C::HALO, 0), hi = min(c0 + C::TW + C::HALO, g.pitch);
             const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(T);
-            const int i_begin = strip * L.rows_per_strip;
-            const int i_end = min(i_begin + L.rows_per_strip, g.Nx);
             const int nk = i_end - i_begin + 2;
             const T* base = nullptr;
             if (lane < NROWS) {
@@ -117,19 +171,15 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
     } else {
         // ------------------------------------------------------------------ consumer warps
         Row<T> ux[3], uy[3], gg[3], pw[3];
-        for (int item = blockIdx.x; item < n_items; item += gridDim.x) {
-            const int pair = item / items_per_pair;
+        WorkWalk<T> walk(L, n_items, L.n_pairs);
+        int pair, tile, i_begin, i_end;
+        while (walk.next(pair, tile, i_begin, i_end)) {
             if (L.active != nullptr && L.active[pair] == 0) continue;
-            const int rem = item - pair * items_per_pair;
-            const int tile = L.tile_fastest ? rem % L.tiles_x : rem / L.strips;
-            const int strip = L.tile_fastest ? rem / L.tiles_x : rem - tile * L.strips;
             const int c0 = tile * C::TW;
             const int cw0 = c0 + warp * (WARP * V);
             const int j0 = cw0 + lane * V;
             const bool warp_has_cols = cw0 < g.Ny;
             const bool edge_warp = (cw0 == 0) || (cw0 + WARP * V + 1 >= g.Ny - 1);
-            const int i_begin = strip * L.rows_per_strip;
-            const int i_end = min(i_begin + L.rows_per_strip, g.Nx);
             const int nk = i_end - i_begin + 2;
             const T a = T(L.alpha[pair] * L.h2), be = T(L.beta[pair] * L.h2);
 

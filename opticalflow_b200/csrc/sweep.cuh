@@ -22,6 +22,8 @@ template <typename T> struct LevelArgs {
     int tiles_x;            // warp tiles per row
     int strips;             // row strips per pair
     int tile_fastest;       // streamed sweep: consecutive work items are neighbouring column tiles of one strip
+    int n_pairs;            // streamed sweep: batch size
+    int balanced;           // streamed sweep: equal row ranges per CTA instead of strips (WorkWalk in stream_sweep.cuh)
 };
 
 template <typename T, bool FROM_IMAGE> struct CoefRows {
