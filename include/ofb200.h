@@ -39,7 +39,8 @@ extern "C" {
 
 #define OFB_FLAG_TILE_FASTEST 16 /* streamed sweeps: neighbouring column tiles of a strip run concurrently (A/B measurements) */
 #define OFB_FLAG_STRIP_ITEMS 64 /* streamed sweeps: fixed-size row strips dealt round-robin instead of the balanced walk (A/B) */
-#define OFB_FLAG_NO_PDL 32 /* plain stream-ordered launches instead of programmatic dependent launch (A/B measurements) */
+#define OFB_FLAG_NO_HALF_STEP_EXIT 128 /* BiCGStab: no convergence test after the first half step (A/B measurements) */
+#define OFB_FLAG_PDL 32 /* programmatic dependent launch for the solver-loop kernels (measured neutral to -0.3%: off by default) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 
 #define OFB_ABI_VERSION 3

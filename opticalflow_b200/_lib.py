@@ -15,8 +15,9 @@ FLAG_NO_FUSED_TAIL = 2
 FLAG_LEGACY_COARSE_BOUNDARY = 4
 FLAG_SLAB_NCCL_HALO = 8
 FLAG_TILE_FASTEST = 16
-FLAG_NO_PDL = 32
+FLAG_PDL = 32
 FLAG_STRIP_ITEMS = 64
+FLAG_NO_HALF_STEP_EXIT = 128
 ABI_VERSION = 3
 
 # every symbol include/ofb200.h declares

@@ -155,10 +155,11 @@ __device__ __forceinline__ void load_row(Row<T>& r, const T* __restrict__ plane,
 }
 
 // ---------------------------------------------------------------- programmatic dependent launch
-// Kernels of the solver loop are launched with the programmatic-stream-serialisation attribute: a kernel lets its
-// successor be scheduled right away (its CTAs take SM slots as this kernel's CTAs retire and run their prologue),
-// and waits here for its predecessor's results before it touches global memory.  Without the attribute both are
-// no-ops.  This hides the launch latency and the prologue of ~400 dependent launches per 16-pair step.
+// With OFB_FLAG_PDL the kernels of the solver loop are launched with the programmatic-stream-serialisation
+// attribute: a kernel lets its successor be scheduled right away (its CTAs take SM slots as this kernel's CTAs
+// retire and run their prologue) and waits here for its predecessor's results before it touches global memory.
+// Without the attribute both instructions are no-ops.  Measured on the 16-pair step: neutral to -0.3 % (the
+// ~400 dependent launches are already queued back to back and the prologues are short), so it is off by default.
 __device__ __forceinline__ void pdl_enter() {
     asm volatile("griddepcontrol.launch_dependents;");
     asm volatile("griddepcontrol.wait;" ::: "memory");

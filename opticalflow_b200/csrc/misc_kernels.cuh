@@ -137,7 +137,7 @@ __global__ void k_state_init(PairState* __restrict__ st, int* __restrict__ activ
     PairState s;
     s.rho = s.rho_old = s.alpha = s.omega = 1.0; s.beta_k = 0.0;
     s.acc[0] = s.acc[1] = s.acc[2] = s.acc[3] = 0.0;
-    s.bnorm = 0.0; s.relres = 0.0; s.active = 1; s.iters = 0; s.status = ST_RUNNING; s.pad = 0;
+    s.bnorm = 0.0; s.relres = 0.0; s.active = 1; s.iters = 0; s.status = ST_RUNNING; s.half_pending = 0;
     st[pair] = s;
     active_arr[pair] = 1;
 }

@@ -365,7 +365,7 @@ template <typename T> struct Solver {
     Geom g_stage;                    // local geometry of the staging planes at the gather level
 
     // ---- slab communication (no-ops for ordinary solves) ------------------------------------------------
-    bool pdl() const { return (opt.flags & OFB_FLAG_NO_PDL) == 0; }
+    bool pdl() const { return (opt.flags & OFB_FLAG_PDL) != 0; }
     bool distributed(int l) const { return slab.on && l < slab.Lg; }
     // refresh the halo rows of `nplanes` planes per pair on level l from the neighbouring slabs
     int exchange(int l, T* base, int nplanes, long long pair_stride) {
@@ -494,7 +494,7 @@ template <typename T> struct Solver {
         return sweep(l, x, op);
     }
     int jacobi_zero(int l, const T* b, T* z, double wj) {
-        OpDirJacobi<T, 2> op; op.g = g[l]; op.cen[0] = b; op.d = nullptr; op.z = z; op.w = T(wj); op.st = w.st;
+        OpDirJacobi<T, 2> op; op.g = g[l]; op.cen[0] = b; op.d = nullptr; op.z = z; op.w = T(wj); op.st = w.st; op.acc[0] = 0.0;
         return sweep(l, nullptr, op);
     }
 
@@ -755,7 +755,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     for (int it = 0; it < max_it; ++it) {
         T *ph = nullptr, *sh = nullptr;
         {   // p = r + beta_k (p - omega v) ; z = w D^-1 p
-            OpDirJacobi<T, 0> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.cen[2] = w.p; op.d = w.p; op.z = ph_first; op.w = wj; op.st = w.st;
+            OpDirJacobi<T, 0> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.cen[2] = w.p; op.d = w.p; op.z = ph_first; op.w = wj; op.st = w.st; op.acc[0] = 0.0;
             if ((rc = S.sweep(0, nullptr, op))) return rc;
         }
         if ((rc = S.finish_precondition(w.p, ph_first, S.partner_of(ph_first, w.ph), &ph))) return rc;
@@ -767,7 +767,13 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 1, rtol, max_it, (int*)nullptr);
         {   // s = r - alpha v ; z = w D^-1 s
             OpDirJacobi<T, 1> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.d = w.s; op.z = sh_first; op.w = wj; op.st = w.st;
+            op.acc[0] = 0.0;
             if ((rc = S.sweep(0, nullptr, op))) return rc;
+        }
+        if ((S.opt.flags & OFB_FLAG_NO_HALF_STEP_EXIT) == 0) {
+            // pairs whose half-step residual already meets rtol skip the second preconditioner application
+            if ((rc = S.allreduce_acc())) return rc;
+            OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 15, rtol, max_it, (int*)nullptr);
         }
         if ((rc = S.finish_precondition(w.s, sh_first, S.partner_of(sh_first, w.sh), &sh))) return rc;
         {   // t = S sh ; acc[0] = t.s, acc[1] = t.t

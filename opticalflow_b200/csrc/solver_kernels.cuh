@@ -13,7 +13,8 @@ struct PairState {
     double rho, rho_old, alpha, omega, beta_k;
     double acc[4];          // [0] rhat.v | t.s   [1] t.t   [2] r.r   [3] rhat.r
     double bnorm, relres;
-    int active, iters, status, pad;
+    int active, iters, status;
+    int half_pending;       // converged at the BiCGStab half step: x += alpha ph is still owed (k_update_x_r pays it)
 };
 enum Status { ST_RUNNING = 0, ST_CONVERGED = 1, ST_MAXIT = 2, ST_BREAKDOWN = 3 };
 
@@ -149,7 +150,7 @@ template <typename T, int KIND> struct OpDirJacobi {
     static constexpr bool NEED_X = false;
     static constexpr int NCEN = KIND == 0 ? 3 : (KIND == 1 ? 2 : 1);
     static constexpr int V = VecOf<T>::V;
-    Geom g; const T* cen[NCEN]; T* d; T* z; T w; const PairState* st;
+    Geom g; const T* cen[NCEN]; T* d; T* z; T w; PairState* st; double acc[1];     // acc: KIND 1 only, s.s -> st.acc[2]
     template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
                                         const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
@@ -171,7 +172,10 @@ template <typename T, int KIND> struct OpDirJacobi {
                     for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[k] + bk * (pp[k] - om * vv[k]) : T(0);
                 } else {
 #pragma unroll
-                    for (int k = 0; k < V; ++k) dd[q][k] = inside[k] ? rr[k] - al * vv[k] : T(0);
+                    for (int k = 0; k < V; ++k) {
+                        dd[q][k] = inside[k] ? rr[k] - al * vv[k] : T(0);
+                        acc[0] += (double)dd[q][k] * (double)dd[q][k];
+                    }
                 }
             }
             store3<T>(d, g, pair, i, j0, dd);
@@ -187,8 +191,8 @@ template <typename T, int KIND> struct OpDirJacobi {
         }
         store3<T>(z, g, pair, i, j0, zz);
     }
-    __device__ __forceinline__ void finish(int, bool) {}
-    __device__ __forceinline__ void flush(int) {}
+    __device__ __forceinline__ void finish(int pair, bool) { if (KIND == 1) block_accumulate<1>(acc, st[pair].acc + 2); }
+    __device__ __forceinline__ void flush(int pair) { if (KIND == 1) warp_flush<1>(acc, st[pair].acc + 2); }
 };
 
 template <typename T, bool FROM_IMAGE, typename Op>
@@ -208,7 +212,13 @@ __global__ void __launch_bounds__(256) k_update_x_r(long long n_per_pair, long l
     pdl_enter();
     const int pair = blockIdx.y;
     double acc[2] = {0.0, 0.0};
-    if (st[pair].active) {
+    if (st[pair].half_pending) {
+        // the pair converged after the first half step: x += alpha ph, nothing else changes
+        const T al = T(st[pair].alpha);
+        const long long base = (long long)pair * pair_stride;
+        for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n_per_pair; e += (long long)gridDim.x * blockDim.x)
+            x[base + e] = x[base + e] + al * ph[base + e];
+    } else if (st[pair].active) {
         const T al = T(st[pair].alpha), om = T(st[pair].omega);
         const long long base = (long long)pair * pair_stride;
         for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n_per_pair;
@@ -227,6 +237,7 @@ __global__ void __launch_bounds__(256) k_update_x_r(long long n_per_pair, long l
 // ------------------------------------------------------------------ scalar stages (one thread per pair)
 // stage 0: after the initial residual   (acc[2] = r.r, acc[3] = rhat.r = r.r)
 // stage 1: after v = S ph               (acc[0] = rhat.v)            -> alpha
+// stage 15: after s = r - alpha v      (acc[2] = s.s)               -> half-step convergence exit
 // stage 2: after t = S sh               (acc[0] = t.s, acc[1] = t.t) -> omega
 // stage 3: after the x/r update         (acc[2] = r.r, acc[3] = rhat.r) -> convergence test, beta_k
 __global__ void k_scalars(PairState* __restrict__ st, int* __restrict__ active_arr, int B, int stage, double rtol, int max_it,
@@ -235,6 +246,7 @@ __global__ void k_scalars(PairState* __restrict__ st, int* __restrict__ active_a
     const int pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= B) return;
     PairState s = st[pair];
+    if (stage == 3 && s.half_pending) { s.half_pending = 0; st[pair] = s; }      // k_update_x_r has applied the half step
     if (!s.active) return;
     const double tiny = 1e-300;
     if (stage == 0) {
@@ -244,6 +256,10 @@ __global__ void k_scalars(PairState* __restrict__ st, int* __restrict__ active_a
     } else if (stage == 1) {
         if (!(fabs(s.acc[0]) > tiny) || !isfinite(s.acc[0])) { s.active = 0; s.status = ST_BREAKDOWN; }
         else s.alpha = s.rho / s.acc[0];
+    } else if (stage == 15) {
+        // half-step exit: s = r - alpha v is the residual of x + alpha ph (acc[2] = s.s)
+        const double rel = sqrt(s.acc[2]) / s.bnorm;
+        if (rel <= rtol) { s.iters += 1; s.relres = rel; s.active = 0; s.status = ST_CONVERGED; s.half_pending = 1; }
     } else if (stage == 2) {
         if (!(s.acc[1] > tiny) || !isfinite(s.acc[0]) || !isfinite(s.acc[1])) { s.active = 0; s.status = ST_BREAKDOWN; }
         else s.omega = s.acc[0] / s.acc[1];

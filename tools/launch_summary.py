@@ -8,7 +8,7 @@ def main(path, out=None, note=''):
     with open(path) as f:
         lines = [l for l in f if l.startswith('"')]
     rows = [(r['Kernel Name'], r['Grid Size'], float(r['Metric Value'])) for r in csv.DictReader(lines)]
-    idx = [i for i, (k, g, t) in enumerate(rows) if 'k_blur_axis<float, 0>' in k or 'k_blur_rows' in k]
+    idx = [i for i, (k, g, t) in enumerate(rows) if 'k_blur_axis<float, 0>' in k or 'k_blur_rows' in k or 'k_blur_tile' in k]
     if not idx:
         s, e = 0, len(rows)
     else:
