@@ -204,10 +204,13 @@ __global__ void __launch_bounds__(1024) k_coarse_setup(Geom g, const T* __restri
         for (int q = 0; q < 3; ++q) M[(long long)col * n + (long long)q * npix + rp] = y[q];
     }
     __syncthreads();
-    // Gauss-Jordan inversion in place with row pivoting, column-major M.
+    // Gauss-Jordan inversion in place with row pivoting, column-major M (element (r, c) at M[c*n + r]).
+    // The n pivot steps are a dependent chain, so the cost is barriers and latency, not arithmetic: three block
+    // barriers per step (pivot search | row swap | elimination with the pivot-row scaling folded in; the
+    // pivot-column update overlaps the next search, which reads another column).
     int* piv = piv_all + (long long)pair * n;
     __shared__ int s_p;
-    __shared__ double s_pivinv;
+    const int cgrp = threadIdx.x >> 3, r0 = threadIdx.x & 7, ngrp = blockDim.x >> 3;     // 8 threads share a column
     for (int k = 0; k < n; ++k) {
         if (threadIdx.x < 32) {   // pivot search in column k, rows k..n-1 (warp 0)
             double best = -1.0; int bi = k;
@@ -228,26 +231,29 @@ __global__ void __launch_bounds__(1024) k_coarse_setup(Geom g, const T* __restri
             const double t = M[(long long)c * n + k]; M[(long long)c * n + k] = M[(long long)c * n + p]; M[(long long)c * n + p] = t;
         }
         __syncthreads();
-        if (threadIdx.x == 0) s_pivinv = 1.0 / M[(long long)k * n + k];
-        __syncthreads();
-        const double pinv = s_pivinv;
-        // scale pivot row: M[k][c] *= pinv (c != k), M[k][k] = pinv
-        for (int c = threadIdx.x; c < n; c += blockDim.x) {
-            const long long idx = (long long)c * n + k;
-            M[idx] = (c == k) ? pinv : M[idx] * pinv;
+        const double pinv = 1.0 / M[(long long)k * n + k];
+        // columns c != k: scaled pivot-row entry m = M[k][c] * pinv, then M[r][c] -= M[r][k] * m for r != k
+        for (int c = cgrp; c < n; c += ngrp) {
+            if (c == k) continue;
+            double* col = M + (long long)c * n;
+            const double m = col[k] * pinv;
+            const double* pc = M + (long long)k * n;
+            for (int r = r0; r < n; r += 8)
+                if (r != k) col[r] -= pc[r] * m;
         }
         __syncthreads();
-        // eliminate: for r != k: f = M[r][k]; M[r][c] -= f*M[k][c] (c != k); M[r][k] = -f*pinv
-        for (long long e = threadIdx.x; e < (long long)n * n; e += blockDim.x) {
-            const int r = (int)(e % n), c = (int)(e / n);
-            if (r == k || c == k) continue;
-            M[(long long)c * n + r] -= M[(long long)k * n + r] * M[(long long)c * n + k];
+        // pivot row: M[k][c] *= pinv (c != k); pivot column: M[r][k] = -M[r][k] * pinv (r != k), M[k][k] = pinv.
+        // Nothing here is read by the next pivot search (column k+1, rows > k).
+        for (int e = threadIdx.x; e < 2 * n; e += blockDim.x) {
+            if (e < n) {
+                const long long idx = (long long)k * n + e;                 // column k, row e
+                M[idx] = (e == k) ? pinv : -M[idx] * pinv;
+            } else if (e - n != k) {
+                M[(long long)(e - n) * n + k] *= pinv;                      // row k, column e - n
+            }
         }
-        __syncthreads();
-        for (int r = threadIdx.x; r < n; r += blockDim.x)
-            if (r != k) M[(long long)k * n + r] = -M[(long long)k * n + r] * pinv;
-        __syncthreads();
     }
+    __syncthreads();
     // undo the row swaps as column swaps in reverse order
     for (int k = n - 1; k >= 0; --k) {
         const int p = piv[k];
