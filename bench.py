@@ -251,6 +251,11 @@ def run_gpu(args):
     else:
         peak, peak_src = 6650.0, 'fallback (B200_PROFILING.md)'
 
+    traffic = None                                                  # DRAM bytes per launch from the committed ncu --set full capture
+    tf = os.path.join(ROOT, 'profiles', 'r01_smoother_traffic.json')
+    if os.path.isfile(tf) and B == 16 and args.dtype == 'float32':
+        traffic = int(json.load(open(tf))['traffic_bytes_per_launch'])
+
     # ---- reduce over ranks
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
     if world > 1:
@@ -272,7 +277,7 @@ def run_gpu(args):
                     e2e=dict(value=e2e_value, unit='frame-pairs/s', h2d_bytes_per_step=int(h2d), d2h_bytes_per_step=int(d2h)),
                     gpu_launches=int(launches),
                     roofline=dict(bound='hbm', kernel='k_stream<float,true,OpSmooth> level 0 (block-Jacobi smoother, streamed sweep)', achieved=achieved,
-                                  peak=peak, unit='GB/s', frac=achieved / peak, traffic=None, peak_source=peak_src,
+                                  peak=peak, unit='GB/s', frac=achieved / peak, traffic=traffic, peak_source=peak_src,
                                   ms_per_launch=sweep_ms, algorithmic_bytes_per_launch=alg_bytes),
                     clocks=sampler.summary())
         if not args.no_cpu_baseline and world == 1:
