@@ -123,34 +123,52 @@ def _default_batch(Nx, Ny, itemsize, n_pairs):
     return B
 
 
+PROBE_IT = 100
+
+
 def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace, solver_options):
-    """Solve a batch.  Pairs the default multigrid cycle does not converge are redone with the robust V(2,2)
-    cycle and, failing that, with plain block-Jacobi BiCGStab (always convergent, slowly)."""
+    """Solve a batch.  Pairs the default multigrid cycle does not converge are redone with the robust V(2,2) cycle,
+    then (float32 only) in float64 - where alpha approaches max(I^2) the system is too ill-conditioned for float32
+    storage - and last with plain block-Jacobi BiCGStab, which wins on small frames.  A pair none of them converges
+    is reported like the reference reports it (:1137-1138): ``converged`` False, best iterate returned."""
     B = P.shape[0]
     b = engine.build_rhs(P, C)
     x = x0.clone()
     opts = engine.make_options(preconditioner, **solver_options)
-    iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace)
     fallback = torch.zeros(B, dtype=torch.bool, device=P.device)
     if opts.precond != _lib.PRECOND_MG:
+        iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace)
         return x, iters, relres, conv, fallback
+    # The cycle needs 6-10 iterations where it works; a pair still running after PROBE_IT iterations is in a regime
+    # it does not handle, and the remaining budget is better spent on the fallbacks (which restart from x0 anyway).
+    probe = min(int(max_it), PROBE_IT)
+    iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, probe, opts, workspace)
     passthrough = {k: v for k, v in solver_options.items() if k in ('check_every', 'rows_per_strip', 'flags')}
-    chain = []
-    if not any(k in solver_options for k in ('nu_pre', 'nu_post', 'omega', 'omega_pre', 'omega_post')):
-        chain.append(engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8, omega_pre=(0.8, 0.8), omega_post=(0.8, 0.8),
-                                         **passthrough))
-    chain.append(engine.make_options('bjacobi', **passthrough))
-    for fb_opts in chain:
+    robust = engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8, omega_pre=(0.8, 0.8), omega_post=(0.8, 0.8), **passthrough)
+    chain = []                                      # (options, solve in float64, iteration budget)
+    custom = any(k in solver_options for k in ('nu_pre', 'nu_post', 'omega', 'omega_pre', 'omega_post'))
+    if P.dtype == torch.float32:
+        if not custom:
+            chain.append((robust, False, probe))
+        chain.append((robust, True, max_it))
+    else:
+        chain.append((opts if custom else robust, False, max_it))
+    chain.append((engine.make_options('bjacobi', **passthrough), P.dtype == torch.float32, max_it))
+    for fb_opts, widen, budget in chain:
         bad = (conv == 0).nonzero().flatten()
         if bad.numel() == 0:
             break
-        xb = x0[bad].clone()
         a_b = engine._weights(alpha, B, P.device)[bad]
         be_b = engine._weights(beta, B, P.device)[bad]
-        it2, rr2, cv2 = engine.solve(P[bad].contiguous(), b[bad].contiguous(), xb, a_b, be_b, rtol, max_it, fb_opts, workspace)
+        if widen:
+            Pb, Cb = P[bad].double().contiguous(), C[bad].double().contiguous()
+            bb, xb, ws = engine.build_rhs(Pb, Cb), x0[bad].double().contiguous(), engine.Workspace()
+        else:
+            Pb, bb, xb, ws = P[bad].contiguous(), b[bad].contiguous(), x0[bad].clone(), workspace
+        it2, rr2, cv2 = engine.solve(Pb, bb, xb, a_b, be_b, rtol, budget, fb_opts, ws)
         better = (cv2 == 1) | (rr2 < relres[bad])
         sel = bad[better]
-        x[sel] = xb[better]
+        x[sel] = xb[better].to(x.dtype)
         iters[sel] = it2[better] + iters[sel]
         relres[sel] = rr2[better]
         conv[sel] = cv2[better]

@@ -183,6 +183,19 @@ def test_vary_regularisation_matches_loop(cuda_device):
             assert got['converged'][i, j]
 
 
+def test_float32_pairs_that_stall_are_redone_in_float64(cuda_device):
+    """alpha close to max(I^2): the float32 solve stalls above rtol, the drop-in redoes the pair in float64
+    (solver_info['fallback']) and the result still meets the float32 tolerance against the oracle."""
+    movie = synthetic.rotating_shearing_movie(128, 128, 2, seed=2)
+    kw = dict(speed_alpha=2.15e4, remodelling_alpha=1e4, smoothing_sigma=2.5)
+    want = fo.variational_optical_flow(movie, **kw)
+    got = optical_flow.variational_optical_flow(movie, dtype='float32', rtol=1e-6, max_it=400, **kw)
+    assert got['converged']
+    for key in ('v_x', 'v_y'):
+        assert rel(got[key], want[key]) < 1e-3
+        assert np.abs(got[key] - want[key]).max() < 1e-2
+
+
 def test_low_alpha_regime_falls_back_and_still_matches(cuda_device):
     """Regularisation weights where the multigrid cycle is not contractive: the block-Jacobi path must take over."""
     movie = fo.blur_movie(synthetic.translating_movie(32, 32, 2, seed=13), 2.5)
