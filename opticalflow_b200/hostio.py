@@ -12,6 +12,8 @@ so they are taken off the critical path:
 
 PyTorch is plumbing here (pinned memory, streams, events); no arithmetic of the hot path happens in it.
 """
+import ctypes
+import os
 import queue
 import threading
 import time
@@ -45,9 +47,58 @@ def copy_pool():
     return _copy_pool
 
 
+class _HostCopyDesc(ctypes.Structure):
+    _fields_ = [('src', ctypes.c_void_p), ('dst', ctypes.c_void_p), ('count', ctypes.c_size_t), ('kind', ctypes.c_int),
+                ('reserved', ctypes.c_int)]
+
+
+_KINDS = {('float32', 'float64'): 1, ('uint8', 'float64'): 2, ('uint16', 'float64'): 3, ('uint8', 'float32'): 4,
+          ('uint16', 'float32'): 5, ('float64', 'float32'): 6}
+_host_lib = None
+_host_lib_tried = False
+
+
+def host_library():
+    """libofb200_host.so (csrc/hostcopy.cpp): a native pool of copy threads, one ctypes call per batch of copies.
+    Returns None if it has not been built; the numpy thread pool below is then used (host copies only - the
+    compute path has no such alternative)."""
+    global _host_lib, _host_lib_tried
+    with _copy_pool_lock:
+        if not _host_lib_tried:
+            _host_lib_tried = True
+            path = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'libofb200_host.so')
+            if os.path.isfile(path) and os.environ.get('OFB_HOST_NATIVE', '1') != '0':
+                lib = ctypes.CDLL(path)
+                lib.ofb_host_pool_start.restype = ctypes.c_int
+                lib.ofb_host_pool_start.argtypes = [ctypes.c_int, ctypes.c_int]
+                lib.ofb_host_copy_many.restype = ctypes.c_int
+                lib.ofb_host_copy_many.argtypes = [ctypes.POINTER(_HostCopyDesc), ctypes.c_int, ctypes.c_size_t]
+                ranks_here = max(1, int(os.environ.get('LOCAL_WORLD_SIZE', '1') or 1))
+                workers = int(os.environ.get('OFB_COPY_THREADS', '0') or 0) or max(2, ((os.cpu_count() or 8) - 2) // ranks_here)
+                lib.ofb_host_pool_start(workers, int(os.environ.get('OFB_HOST_NT', '1') != '0'))
+                _host_lib = lib
+    return _host_lib
+
+
 def parallel_copy(pairs, piece_bytes=4 << 20):
-    """copyto(dst, src, casting='unsafe') for every (dst, src) pair of equally shaped C-contiguous arrays, cut into
-    ~piece_bytes pieces that the copy pool works through concurrently.  Returns when all pieces are done."""
+    """dst[...] = src (cast) for every (dst, src) pair of equally shaped C-contiguous arrays.  Returns when all bytes
+    are written.  Native path: one call into the host copy pool; otherwise ~piece_bytes numpy.copyto pieces on a
+    Python thread pool."""
+    lib = host_library()
+    if lib is not None:
+        native, rest = [], []
+        for dst, src in pairs:
+            kind = 0 if dst.dtype == src.dtype else _KINDS.get((src.dtype.name, dst.dtype.name))
+            ok = kind is not None and dst.flags.c_contiguous and src.flags.c_contiguous and dst.size == src.size
+            (native if ok else rest).append((dst, src, kind))
+        if native:
+            descs = (_HostCopyDesc * len(native))()
+            for k, (dst, src, kind) in enumerate(native):
+                descs[k] = _HostCopyDesc(src.ctypes.data, dst.ctypes.data, src.nbytes if kind == 0 else src.size, kind, 0)
+            lib.ofb_host_copy_many(descs, len(native), 1 << 20)
+        pairs = [(dst, src) for dst, src, _ in rest]
+        if not pairs:
+            return
     pool = copy_pool()
     futures = []
     for dst, src in pairs:
@@ -97,6 +148,60 @@ class PinnedPool:
 
 
 pinned_pool = PinnedPool()
+
+
+class ResultArena:
+    """Recycles the memory of result arrays the caller has dropped.
+
+    The drop-in returns ~50 MB of float64 per 1024^2 frame pair.  Fresh anonymous memory is zero-filled by the kernel
+    page by page on first touch, which at several hundred pairs per second costs as much host bandwidth as the
+    widening itself.  `alloc` hands out arrays carved from buffers whose previous arrays are all gone (a weakref
+    finalizer on the carrier view returns the buffer), so a caller that processes movie after movie - or calls in a
+    loop - writes into pages that are already mapped.  Contents are uninitialised, like numpy.empty.  At most
+    `max_idle_bytes` are kept while idle (OFB_RESULT_ARENA_BYTES, default min(32 GiB, RAM/8); 0 disables recycling)."""
+
+    def __init__(self, max_idle_bytes=None):
+        import os
+        if max_idle_bytes is None:
+            try:
+                ram = os.sysconf('SC_PAGE_SIZE') * os.sysconf('SC_PHYS_PAGES')
+            except (ValueError, OSError):
+                ram = 64 << 30
+            max_idle_bytes = int(os.environ.get('OFB_RESULT_ARENA_BYTES', min(32 << 30, ram // 8)))
+        self.max_idle_bytes = int(max_idle_bytes)
+        self.free = []                       # idle uint8 buffers
+        self.lock = threading.Lock()
+
+    def _give_back(self, buf):
+        with self.lock:
+            if sum(b.nbytes for b in self.free) + buf.nbytes <= self.max_idle_bytes:
+                self.free.append(buf)
+
+    def alloc(self, shape, dtype):
+        import weakref
+        dtype = np.dtype(dtype)
+        need = int(np.prod(shape)) * dtype.itemsize
+        if self.max_idle_bytes <= 0 or need < (1 << 20):
+            return np.empty(shape, dtype=dtype)
+        buf = None
+        with self.lock:
+            best = None
+            for k, b in enumerate(self.free):
+                if need <= b.nbytes <= need + (need >> 2) and (best is None or b.nbytes < self.free[best].nbytes):
+                    best = k
+            if best is not None:
+                buf = self.free.pop(best)
+        if buf is None:
+            buf = np.empty(need, dtype=np.uint8)
+        # numpy collapses .base chains of ndarray views onto the owning array, so the owner the caller's arrays keep
+        # alive must be a per-allocation object of our own: a ctypes window onto the buffer.  When the last view of
+        # it is gone the finalizer returns the buffer (which the finalizer's argument list keeps alive until then).
+        carrier = (ctypes.c_char * need).from_address(buf.ctypes.data)
+        weakref.finalize(carrier, self._give_back, buf)
+        return np.frombuffer(carrier, dtype=dtype).reshape(shape)
+
+
+result_arena = ResultArena()
 
 
 def as_native_tensor(array):

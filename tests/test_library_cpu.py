@@ -60,3 +60,29 @@ def test_product_does_not_import_oracle():
         if fn.endswith('.py'):
             text = open(os.path.join(pkg, fn)).read()
             assert 'oracle' not in text.replace('the oracle', ''), fn
+
+
+def test_result_arena_recycles_only_dropped_arrays():
+    """hostio.ResultArena: a buffer goes back to the pool when the LAST view of an array carved from it is gone."""
+    import gc
+    import numpy as np
+    from opticalflow_b200 import hostio
+    arena = hostio.ResultArena(max_idle_bytes=1 << 30)
+    a = arena.alloc((4, 512, 512), np.float64)
+    address = a.ctypes.data
+    assert a.flags.c_contiguous and a.flags.writeable and a.dtype == np.float64
+    view = a[1:3].reshape(-1)[7:]
+    del a
+    gc.collect()
+    assert not arena.free                                   # a view is still alive
+    b = arena.alloc((4, 512, 512), np.float64)
+    assert b.ctypes.data != address
+    del view
+    gc.collect()
+    assert len(arena.free) == 1
+    c = arena.alloc((4, 512, 512), np.float64)
+    assert c.ctypes.data == address                         # recycled
+    small = arena.alloc((10, 10), np.float64)               # small arrays are plain numpy.empty
+    assert small.base is None
+    off = hostio.ResultArena(max_idle_bytes=0)
+    assert off.alloc((4, 512, 512), np.float64).base is None

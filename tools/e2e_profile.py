@@ -5,7 +5,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.ins
 from opticalflow_b200 import optical_flow, synthetic
 B = 16
 movie = synthetic.rotating_shearing_movie(1024, 1024, B + 1, seed=2).astype(np.float32)
-zig = np.concatenate([np.arange(0, B + 1), np.arange(B - 1, -1, -1), np.arange(1, B + 1), np.arange(B - 1, -1, -1)])
+REP = int(sys.argv[1]) if len(sys.argv) > 1 else 1            # 1: 64 pairs, 3: 128 pairs (the bench's movie)
+zig = np.concatenate([np.arange(0, B + 1), np.arange(B - 1, -1, -1)] + [np.arange(1, B + 1), np.arange(B - 1, -1, -1)] * REP)
 m = np.ascontiguousarray(movie[zig])
 kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.5, dtype='float32', rtol=1e-6, batch_pairs=B)
 res = None
@@ -13,7 +14,7 @@ for rep in range(6):
     t = time.perf_counter(); res = optical_flow.variational_optical_flow(m, **kw); dt = time.perf_counter() - t
     tl = res['solver_info']['timeline']
     print('rep %d call %.1f ms -> %.1f pairs/s | chunks (wait,solve): %s | %s | egress %s' % (
-        rep, dt * 1e3, 64 / dt, [(round(r['wait_slot_and_frames'] * 1e3, 1), round(r['solve'] * 1e3, 1)) for r in tl[:-1]],
+        rep, dt * 1e3, (m.shape[0] - 1) / dt, [(round(r['wait_slot_and_frames'] * 1e3, 1), round(r['solve'] * 1e3, 1)) for r in tl[:-1]],
         {k: round(v * 1e3, 1) for k, v in tl[-1].items()},
         [(round(a * 1e3, 1), round(b * 1e3, 1)) for a, b in res['solver_info']['egress_log']]), flush=True)
     if rep == 3:
