@@ -74,7 +74,9 @@ def host_library():
                 lib.ofb_host_copy_many.restype = ctypes.c_int
                 lib.ofb_host_copy_many.argtypes = [ctypes.POINTER(_HostCopyDesc), ctypes.c_int, ctypes.c_size_t]
                 ranks_here = max(1, int(os.environ.get('LOCAL_WORLD_SIZE', '1') or 1))
-                workers = int(os.environ.get('OFB_COPY_THREADS', '0') or 0) or max(2, ((os.cpu_count() or 8) - 2) // ranks_here)
+                # the widening is bandwidth bound with non-temporal stores: 6-8 threads saturate a socket, more only take
+                # cores from the kernel-launching thread (16-core host: 6 threads 205 ms per 128 pairs, 14 threads 240 ms)
+                workers = int(os.environ.get('OFB_COPY_THREADS', '0') or 0) or min(8, max(2, ((os.cpu_count() or 8) - 2) // ranks_here))
                 lib.ofb_host_pool_start(workers, int(os.environ.get('OFB_HOST_NT', '1') != '0'))
                 _host_lib = lib
     return _host_lib
