@@ -43,7 +43,7 @@ extern "C" {
 #define OFB_FLAG_PDL 32 /* programmatic dependent launch for the solver-loop kernels (measured neutral to -0.3%: off by default) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 
-#define OFB_ABI_VERSION 3
+#define OFB_ABI_VERSION 4
 
 typedef struct ofb_solve_options {
     int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
@@ -164,6 +164,42 @@ int ofb_solve_slab(const void* P, const void* b3, void* x3, const double* alpha,
 int ofb_epilogue_slab(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma,
                       double* functionals, double* moments, const double* alpha, const double* beta, double scale,
                       int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Callers either side of the hot path (SURVEY.md section 8f NEXT-3 / NEXT-4).  Frames [F][Nx][Ny] row-major.
+ * ------------------------------------------------------------------------------------------------------- */
+
+/* Liu-Shen 2-field Jacobi iteration: replaces liu_shen_optical_flow_jit (optical_flow.py:426-673) for B frame
+ *     pairs at once.  P/C = previous/current frames [B][Nx][Ny]; vx, vy: in = initial guess in pixel units
+ *     (initial_v * delta_t/delta_x, :497-498), out = velocities times `scale` (= delta_x/delta_t, :669-670);
+ *     speed out (:671); tmp_vx/tmp_vy = scratch of the same size.  Exactly `iterations` sweeps (the reference's
+ *     `tolerance` argument is ignored there too).  Ghost values are the mirror image about the edge pixel
+ *     (apply_constant_boundary_condition on the padded arrays, :1304-1316). */
+int ofb_liu_shen(const void* P, const void* C, void* vx, void* vy, void* speed, void* tmp_vx, void* tmp_vy,
+                 double alpha, int iterations, double scale, int B, int Nx, int Ny, int dtype, void* stream);
+
+/* np.max over n elements (:328) -> *max_out (device double). */
+int ofb_movie_max(const void* in, long long n, int dtype, double* max_out, void* stream);
+
+/* apply_adaptive_threshold (optical_flow.py:308-338): uint8(movie/max*255) into tmp_u8 [F][Nx][Ny], then
+ *     cv2.adaptiveThreshold(.., 1.0, ADAPTIVE_THRESH_MEAN_C, THRESH_BINARY, window, threshold):
+ *     out = 1 where src > boxmean(window, replicated border) - idelta, idelta = ceil(threshold).
+ *     window odd, 3..255.  movie_max: device double (ofb_movie_max). */
+int ofb_adaptive_threshold(const void* in, const double* movie_max, unsigned char* tmp_u8, unsigned char* out,
+                           int window, int idelta, int F, int Nx, int Ny, int dtype, void* stream);
+
+/* apply_clahe (optical_flow.py:340-374): cv2.createCLAHE(clip_limit, (tiles_x, tiles_y)).apply on
+ *     movie.astype(uint16), 65536 bins per tile; out has the dtype of in (the reference returns float64).
+ *     tiles_x splits the columns, tiles_y the rows.  The workspace holds histograms and look-up tables of the
+ *     frames in flight (6 bytes x 65536 x tiles per frame); the call loops over as many frames as it holds. */
+size_t ofb_clahe_workspace_bytes(int frames_in_flight, int tiles_x, int tiles_y);
+int ofb_clahe(const void* in, void* out, double clip_limit, int tiles_x, int tiles_y, void* workspace,
+              size_t workspace_bytes, int F, int Nx, int Ny, int dtype, void* stream);
+
+/* Background subtraction of conduct_optical_flow (optical_flow.py:195-198):
+ *     out = movie - background where blurred > background, else 0 (blurred = ofb_blur(movie, sigma 10)). */
+int ofb_subtract_background(const void* movie, const void* blurred, void* out, double background, long long n,
+                            int dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -18,13 +18,15 @@ FLAG_TILE_FASTEST = 16
 FLAG_PDL = 32
 FLAG_STRIP_ITEMS = 64
 FLAG_NO_HALF_STEP_EXIT = 128
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 # every symbol include/ofb200.h declares
 EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_workspace_bytes', 'ofb_blur',
                     'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_smooth', 'ofb_solve', 'ofb_precondition',
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
-                    'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab')
+                    'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab',
+                    'ofb_liu_shen', 'ofb_movie_max', 'ofb_adaptive_threshold', 'ofb_clahe_workspace_bytes', 'ofb_clahe',
+                    'ofb_subtract_background')
 
 
 class SolveOptions(ctypes.Structure):
@@ -107,6 +109,19 @@ def load():
                                    i, i, i, i, slabp, vp]
     lib.ofb_epilogue_slab.restype = i
     lib.ofb_epilogue_slab.argtypes = [vp, vp, vp, vp, vp, vp, vp, dp, dp, dp, dp, d, i, i, i, i, slabp, vp]
+    ll = ctypes.c_longlong
+    lib.ofb_liu_shen.restype = i
+    lib.ofb_liu_shen.argtypes = [vp, vp, vp, vp, vp, vp, vp, d, i, d, i, i, i, i, vp]
+    lib.ofb_movie_max.restype = i
+    lib.ofb_movie_max.argtypes = [vp, ll, i, dp, vp]
+    lib.ofb_adaptive_threshold.restype = i
+    lib.ofb_adaptive_threshold.argtypes = [vp, dp, vp, vp, i, i, i, i, i, i, vp]
+    lib.ofb_clahe_workspace_bytes.restype = sz
+    lib.ofb_clahe_workspace_bytes.argtypes = [i, i, i]
+    lib.ofb_clahe.restype = i
+    lib.ofb_clahe.argtypes = [vp, vp, d, i, i, vp, sz, i, i, i, i, vp]
+    lib.ofb_subtract_background.restype = i
+    lib.ofb_subtract_background.argtypes = [vp, vp, vp, d, ll, i, vp]
     if lib.ofb_version() != ABI_VERSION:
         raise OfbError('libofb200.so ABI version %d != expected %d' % (lib.ofb_version(), ABI_VERSION))
     _lib = lib

@@ -1,0 +1,424 @@
+// ofb200 - kernels for the callers either side of the hot path (SURVEY.md section 8f NEXT-3 / NEXT-4):
+//   k_liu_shen_step     one Jacobi sweep of liu_shen_optical_flow_jit          (optical_flow.py:507-651)
+//   k_liu_shen_finish   its scaling / speed epilogue                           (:665-672)
+//   k_movie_max         np.max(movie)                                          (:328)
+//   k_to_u8_range / k_adaptive_threshold  uint8 conversion, cv2.adaptiveThreshold MEAN_C   (:328-333)
+//   k_clahe_hist / k_clahe_lut / k_clahe_interp   cv2 CLAHE on uint16 frames   (:362-370)
+//   k_subtract_background                                                      (:195-198)
+// All of it is HBM-bound element / byte work; nothing here is a contraction.
+#pragma once
+#include "common.cuh"
+
+namespace ofb {
+
+// -----------------------------------------------------------------------------------------------------
+// Liu-Shen Jacobi sweep.  A CTA stages a (TH+2) x (TW+2) tile of vx, vy, P and C in shared memory (16-byte global
+// loads for the body, the one-pixel halo mirrored about the edge pixel = apply_constant_boundary_condition on the
+// reference's padded arrays, :1304-1316), then every thread updates four adjacent pixels per row from 16-byte
+// shared loads and stores 16 bytes.  Algorithmic traffic: read vx, vy, P, C, write vx', vy' = 6 words per pixel.
+// -----------------------------------------------------------------------------------------------------
+template <typename T> struct LsCfg {
+    static constexpr int TW = 128;                 // tile width (columns)
+    static constexpr int TH = 128 / sizeof(T);     // tile height: 32 rows fp32, 16 rows fp64
+    static constexpr int OFF = 4;                  // column of the first body element in a shared row (16-byte aligned)
+    static constexpr int PITCH = TW + 8;
+    static constexpr int THREADS = 256;
+    static constexpr int MIN_CTAS = sizeof(T) == 4 ? 3 : 2;   // resident CTAs per SM the register budget is held to
+    static constexpr size_t SMEM = (size_t)4 * (TH + 2) * PITCH * sizeof(T);
+};
+
+// frame row/column seen at logical index i in [-1, N]: the ghost is the mirror image about the edge pixel
+__device__ __forceinline__ int ls_mirror(int i, int N) {
+    i = i < 0 ? -i : i;
+    i = i >= N ? 2 * N - 2 - i : i;
+    return min(max(i, 0), N - 1);                  // rows/columns of a ragged tile beyond the ghost: any valid address
+}
+
+template <typename T> struct Vec4 { T v[4]; };
+
+template <typename T>
+__device__ __forceinline__ Vec4<T> ld4_global(const T* p) {
+    Vec4<T> r;
+    if constexpr (sizeof(T) == 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p);
+        r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+    } else {
+        const double2 a = *reinterpret_cast<const double2*>(p), b = *reinterpret_cast<const double2*>(p + 2);
+        r.v[0] = a.x; r.v[1] = a.y; r.v[2] = b.x; r.v[3] = b.y;
+    }
+    return r;
+}
+template <typename T>
+__device__ __forceinline__ void st4(T* p, const T (&v)[4]) {
+    if constexpr (sizeof(T) == 4) {
+        *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+    } else {
+        *reinterpret_cast<double2*>(p) = make_double2(v[0], v[1]);
+        *reinterpret_cast<double2*>(p + 2) = make_double2(v[2], v[3]);
+    }
+}
+
+// six consecutive elements of a shared row starting one left of the thread's body columns
+template <typename T>
+__device__ __forceinline__ void ld6_shared(const T* row, int body, T (&a)[6]) {
+    a[0] = row[body - 1];
+    const Vec4<T> m = ld4_global<T>(row + body);
+    a[1] = m.v[0]; a[2] = m.v[1]; a[3] = m.v[2]; a[4] = m.v[3];
+    a[5] = row[body + 4];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(LsCfg<T>::THREADS, LsCfg<T>::MIN_CTAS)
+k_liu_shen_step(const T* __restrict__ P, const T* __restrict__ C, const T* __restrict__ vx_in, const T* __restrict__ vy_in,
+                T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny, long long plane, T alpha, int vec_ok) {
+    using Cfg = LsCfg<T>;
+    constexpr int TW = Cfg::TW, TH = Cfg::TH, OFF = Cfg::OFF, PITCH = Cfg::PITCH;
+    extern __shared__ __align__(16) unsigned char ls_smem[];
+    T* s_vx = reinterpret_cast<T*>(ls_smem);
+    T* s_vy = s_vx + (TH + 2) * PITCH;
+    T* s_p = s_vy + (TH + 2) * PITCH;
+    T* s_c = s_p + (TH + 2) * PITCH;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int c0 = blockIdx.x * TW, i0 = blockIdx.y * TH;
+    const long long base = (long long)blockIdx.z * plane;
+    const T* src[4] = {vx_in + base, vy_in + base, P + base, C + base};
+    T* dst[4] = {s_vx, s_vy, s_p, s_c};
+
+    // ---- stage the tile: warp per row, lane per four body columns, lanes 0/1 also fetch the halo columns
+    for (int rr = warp; rr < TH + 2; rr += Cfg::THREADS / 32) {
+        const int gi = ls_mirror(i0 - 1 + rr, Nx);
+        const int j = c0 + 4 * lane;
+        const bool fast = vec_ok && j + 3 < Ny;
+        const int jh = ls_mirror(lane == 0 ? c0 - 1 : c0 + TW, Ny);
+#pragma unroll
+        for (int a = 0; a < 4; ++a) {
+            const T* g = src[a] + (long long)gi * Ny;
+            T* s = dst[a] + rr * PITCH + OFF;
+            Vec4<T> v;
+            if (fast) {
+                v = ld4_global<T>(g + j);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) v.v[k] = g[ls_mirror(j + k, Ny)];
+            }
+            st4<T>(s + 4 * lane, v.v);
+            if (lane == 0) s[-1] = g[jh];
+            if (lane == 1) s[TW] = g[jh];
+        }
+    }
+    __syncthreads();
+
+    // ---- update: thread = four adjacent columns, rows rg, rg+8, ...
+    const int cg = threadIdx.x & 31, rg = threadIdx.x >> 5;
+    const int j = c0 + 4 * cg;
+    const int body = OFF + 4 * cg;
+    const T half = T(0.5), quarter = T(0.25), two = T(2);
+    for (int r = rg; r < TH; r += Cfg::THREADS / 32) {
+        const int i = i0 + r;
+        if (i >= Nx || j >= Ny) continue;
+        T ax[3][6], ay[3][6], ap[3][6], ac[6];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+            ld6_shared<T>(s_vx + (r + q) * PITCH, body, ax[q]);
+            ld6_shared<T>(s_vy + (r + q) * PITCH, body, ay[q]);
+            ld6_shared<T>(s_p + (r + q) * PITCH, body, ap[q]);
+        }
+        ld6_shared<T>(s_c + (r + 1) * PITCH, body, ac);
+        const Vec4<T> cu = ld4_global<T>(s_c + r * PITCH + body), cd = ld4_global<T>(s_c + (r + 2) * PITCH + body);
+        // the 8-neighbour sum takes zeros outside the frame (:522-538) where the derivative terms take the mirror
+        const T m_up = i > 0 ? T(1) : T(0), m_dn = i < Nx - 1 ? T(1) : T(0);
+        const bool edge_i = (i == 0) || (i == Nx - 1);
+        T ox[4], oy[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int c = k + 1, jj = j + k;
+            const T m_l = jj > 0 ? T(1) : T(0), m_r = jj < Ny - 1 ? T(1) : T(0);
+            const bool edge_j = (jj == 0) || (jj == Ny - 1);
+            // image terms (:564-595); index 0 = row i-1 ("x" is the row axis)
+            const T I = ap[1][c];
+            const T Ix = (ap[2][c] - ap[0][c]) * half;
+            const T Iy = (ap[1][c + 1] - ap[1][c - 1]) * half;
+            const T Ixt = (cd.v[k] - cu.v[k] - ap[2][c] + ap[0][c]) * half;
+            const T Iyt = (ac[c + 1] - ac[c - 1] - ap[1][c + 1] + ap[1][c - 1]) * half;
+            const T Ixx = ap[2][c] + ap[0][c] - two * I;
+            const T Iyy = ap[1][c + 1] + ap[1][c - 1] - two * I;
+            const T Ixy = (ap[2][c + 1] - ap[2][c - 1] - ap[0][c + 1] + ap[0][c - 1]) * quarter;
+            // velocity terms (:513-520, :598-605)
+            const T dxVx = (ax[2][c] - ax[0][c]) * half, dyVx = (ax[1][c + 1] - ax[1][c - 1]) * half;
+            const T dxyVx = (ax[2][c + 1] - ax[2][c - 1] - ax[0][c + 1] + ax[0][c - 1]) * quarter;
+            const T dxVy = (ay[2][c] - ay[0][c]) * half, dyVy = (ay[1][c + 1] - ay[1][c - 1]) * half;
+            const T dxyVy = (ay[2][c + 1] - ay[2][c - 1] - ay[0][c + 1] + ay[0][c - 1]) * quarter;
+            const T Vx_barx = ax[2][c] + ax[0][c];
+            const T Vy_bary = ay[1][c + 1] + ay[1][c - 1];
+            const T barx = m_up * (m_l * ax[0][c - 1] + ax[0][c] + m_r * ax[0][c + 1]) + m_l * ax[1][c - 1] + m_r * ax[1][c + 1]
+                         + m_dn * (m_l * ax[2][c - 1] + ax[2][c] + m_r * ax[2][c + 1]);
+            const T bary = m_up * (m_l * ay[0][c - 1] + ay[0][c] + m_r * ay[0][c + 1]) + m_l * ay[1][c - 1] + m_r * ay[1][c + 1]
+                         + m_dn * (m_l * ay[2][c - 1] + ay[2][c] + m_r * ay[2][c + 1]);
+            // right-hand side (:636-646) and 2x2 matrix (:631-639)
+            const T I2 = I * I;
+            const T F0 = -I * Ixt - I * (two * Ix * dxVx + Iy * dxVy + Ix * dyVy) - I2 * (Vx_barx + dxyVy) - alpha * barx;
+            const T F1 = -I * Iyt - I * (two * Iy * dyVy + Ix * dyVx + Iy * dxVx) - I2 * (Vy_bary + dxyVx) - alpha * bary;
+            const T pref = (edge_i && edge_j) ? T(3) : ((edge_i || edge_j) ? T(5) : T(8));
+            const T a00 = I * Ixx - two * I2 - pref * alpha;
+            const T a01 = I * Ixy;
+            const T a11 = I * Iyy - two * I2 - pref * alpha;
+            const T inv_det = T(1) / (a00 * a11 - a01 * a01);
+            ox[k] = (a11 * F0 - a01 * F1) * inv_det;
+            oy[k] = (a00 * F1 - a01 * F0) * inv_det;
+        }
+        T* px = vx_out + base + (long long)i * Ny + j;
+        T* py = vy_out + base + (long long)i * Ny + j;
+        if (vec_ok && j + 3 < Ny) {
+            st4<T>(px, ox);
+            st4<T>(py, oy);
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (j + k < Ny) { px[k] = ox[k]; py[k] = oy[k]; }
+        }
+    }
+}
+
+// :665-672  v *= delta_x/delta_t, speed = sqrt(vx^2 + vy^2)
+template <typename T>
+__global__ void k_liu_shen_finish(T* __restrict__ vx, T* __restrict__ vy, T* __restrict__ speed, long long n, T scale) {
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x) {
+        const T x = vx[k] * scale, y = vy[k] * scale;
+        vx[k] = x;
+        vy[k] = y;
+        speed[k] = sqrt(x * x + y * y);
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// np.max over a movie (:328): block reduction, one atomic per block on the bit pattern of a double.
+// -----------------------------------------------------------------------------------------------------
+__global__ void k_fill_double(double* p, double v) { *p = v; }
+
+__device__ __forceinline__ void atomic_max_double(double* addr, double v) {
+    unsigned long long* a = reinterpret_cast<unsigned long long*>(addr);
+    unsigned long long old = *a;
+    while (__longlong_as_double((long long)old) < v) {
+        const unsigned long long seen = atomicCAS(a, old, (unsigned long long)__double_as_longlong(v));
+        if (seen == old) break;
+        old = seen;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_movie_max(const T* __restrict__ in, long long n, double* __restrict__ out) {
+    __shared__ double part[8];
+    double m = -INFINITY;
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x)
+        m = fmax(m, (double)in[k]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(FULL, m, o));
+    if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) m = fmax(m, part[w]);
+        atomic_max_double(out, m);
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// Adaptive threshold (:328-333): uint8 conversion, k x k normalised box mean with replicated borders (integer
+// window sums, separable inside a shared-memory tile), dst = src > mean - ceil(threshold).  A CTA owns a 64 x 64
+// output tile and stages (64+2r)^2 converted bytes; the row sums never leave shared memory.
+// -----------------------------------------------------------------------------------------------------
+constexpr int AT_TILE = 64;
+constexpr int AT_THREADS = 256;
+inline size_t adaptive_threshold_smem(int window) {
+    const size_t e = AT_TILE + 2 * (window / 2);
+    return ((e * e + 15) / 16) * 16 + e * AT_TILE * sizeof(unsigned short);
+}
+
+template <typename T>
+__device__ __forceinline__ unsigned char to_u8_range(T v, T mx) {
+    // np.array(movie/np.max(movie)*255.0, dtype='uint8'): divide, multiply (in the movie's float type), truncate
+    if constexpr (sizeof(T) == 4) return (unsigned char)(int)__fmul_rn(__fdiv_rn(v, mx), 255.0f);
+    else return (unsigned char)(int)__dmul_rn(__ddiv_rn(v, mx), 255.0);
+}
+
+// np.array(movie/np.max(movie)*255.0, dtype='uint8') as its own pass, so that the k x k windows below re-read bytes
+template <typename T>
+__global__ void k_to_u8_range(const T* __restrict__ in, const double* __restrict__ movie_max, unsigned char* __restrict__ out, long long n) {
+    const T mx = (T)(*movie_max);
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x)
+        out[k] = to_u8_range<T>(in[k], mx);
+}
+
+__global__ void __launch_bounds__(AT_THREADS)
+k_adaptive_threshold(const unsigned char* __restrict__ in, unsigned char* __restrict__ out, int Nx, int Ny, long long plane, int window,
+                     int idelta) {
+    extern __shared__ __align__(16) unsigned char at_smem[];
+    const int r = window / 2, e = AT_TILE + 2 * r;
+    unsigned char* tile = at_smem;                                                   // [e][e]
+    unsigned short* hs = reinterpret_cast<unsigned short*>(at_smem + (((size_t)e * e + 15) / 16) * 16);   // [e][AT_TILE]
+    const unsigned char* f = in + (long long)blockIdx.z * plane;
+    const int c0 = blockIdx.x * AT_TILE, i0 = blockIdx.y * AT_TILE;
+    for (int k = threadIdx.x; k < e * e; k += AT_THREADS) {
+        const int rr = k / e, cc = k - rr * e;
+        const int gi = min(max(i0 - r + rr, 0), Nx - 1), gj = min(max(c0 - r + cc, 0), Ny - 1);
+        tile[k] = f[(long long)gi * Ny + gj];
+    }
+    __syncthreads();
+    // horizontal window sums: thread per staged row (255 * 255 < 65536: the sums fit 16 bits)
+    for (int rr = threadIdx.x; rr < e; rr += AT_THREADS) {
+        const unsigned char* t = tile + (size_t)rr * e;
+        int s = 0;
+        for (int k = 0; k < window; ++k) s += t[k];
+        unsigned short* h = hs + (size_t)rr * AT_TILE;
+        h[0] = (unsigned short)s;
+        for (int c = 1; c < AT_TILE; ++c) {
+            s += (int)t[c + window - 1] - (int)t[c - 1];
+            h[c] = (unsigned short)s;
+        }
+    }
+    __syncthreads();
+    // vertical window sums: thread = column x quarter of the rows
+    const int col = threadIdx.x % AT_TILE, q = threadIdx.x / AT_TILE;
+    constexpr int ROWS = AT_TILE / (AT_THREADS / AT_TILE);
+    const int r0 = q * ROWS;
+    int s = 0;
+    for (int k = 0; k < window; ++k) s += hs[(size_t)(r0 + k) * AT_TILE + col];
+    const int k2 = window * window;
+    for (int rr = r0; rr < r0 + ROWS; ++rr) {
+        if (rr > r0) s += (int)hs[(size_t)(rr + window - 1) * AT_TILE + col] - (int)hs[(size_t)(rr - 1) * AT_TILE + col];
+        const int i = i0 + rr, j = c0 + col;
+        if (i < Nx && j < Ny) {
+            const int mean = (2 * s + k2) / (2 * k2);          // round to nearest; k odd => no ties
+            const int v = tile[(size_t)(rr + r) * e + col + r];
+            out[(long long)blockIdx.z * plane + (long long)i * Ny + j] = (v - mean > -idelta) ? 1 : 0;
+        }
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// CLAHE on uint16 frames (:362-370; OpenCV clahe.cpp, 16-bit path: 65536 bins).
+// -----------------------------------------------------------------------------------------------------
+constexpr int CLAHE_BINS = 65536;
+
+struct ClaheGeom {
+    int Nx, Ny;              // frame
+    int ext_x, ext_y;        // frame extended (BORDER_REFLECT_101) to a multiple of the tile grid
+    int tiles_x, tiles_y;    // tiles along the columns / the rows
+    int tw, th;              // tile width (columns) / height (rows)
+    int clip;                // clip limit in counts (0 = none)
+    float lut_scale;         // 65535 / tile area
+};
+
+template <typename T>
+__device__ __forceinline__ unsigned short to_u16(T v) { return (unsigned short)(int)v; }     // movie.astype(np.uint16)
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_clahe_hist(const T* __restrict__ in, int* __restrict__ hist, ClaheGeom g, long long plane) {
+    const T* f = in + (long long)blockIdx.z * plane;
+    int* h = hist + (long long)blockIdx.z * g.tiles_x * g.tiles_y * CLAHE_BINS;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= g.ext_y) return;
+    const int si = i < g.Nx ? i : 2 * g.Nx - 2 - i, sj = j < g.Ny ? j : 2 * g.Ny - 2 - j;
+    const unsigned short v = to_u16<T>(f[(long long)si * g.Ny + sj]);
+    atomicAdd(h + (long long)((i / g.th) * g.tiles_x + j / g.tw) * CLAHE_BINS + v, 1);
+}
+
+// One CTA per (tile, frame): clip, redistribute, running sum, scale -> 16-bit look-up table.
+__global__ void __launch_bounds__(1024) k_clahe_lut(const int* __restrict__ hist, unsigned short* __restrict__ lut, ClaheGeom g) {
+    __shared__ int warp_sum[32];
+    __shared__ int carry_s, clipped_s;
+    const long long t = (long long)blockIdx.y * gridDim.x + blockIdx.x;
+    const int* h = hist + t * CLAHE_BINS;
+    unsigned short* l = lut + t * CLAHE_BINS;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int batch = 0, residual = 0, step = 1;
+    if (g.clip > 0) {
+        int c = 0;
+        for (int b = threadIdx.x; b < CLAHE_BINS; b += 1024) c += max(h[b] - g.clip, 0);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
+        if (lane == 0) warp_sum[warp] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            int tot = 0;
+            for (int w = 0; w < 32; ++w) tot += warp_sum[w];
+            clipped_s = tot;
+        }
+        __syncthreads();
+        const int clipped = clipped_s;
+        batch = clipped / CLAHE_BINS;
+        residual = clipped - batch * CLAHE_BINS;
+        step = residual != 0 ? max(CLAHE_BINS / residual, 1) : 1;
+    }
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int chunk = 0; chunk < CLAHE_BINS; chunk += 1024) {
+        const int b = chunk + threadIdx.x;
+        int v = h[b];
+        if (g.clip > 0) {
+            v = min(v, g.clip) + batch;
+            if (residual != 0 && b % step == 0 && b / step < residual) v += 1;
+        }
+        int s = v;                                           // inclusive scan over the 1024 bins of the chunk
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int u = __shfl_up_sync(FULL, s, o);
+            if (lane >= o) s += u;
+        }
+        if (lane == 31) warp_sum[warp] = s;
+        __syncthreads();
+        if (warp == 0) {
+            int w = warp_sum[lane];
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int u = __shfl_up_sync(FULL, w, o);
+                if (lane >= o) w += u;
+            }
+            warp_sum[lane] = w;
+        }
+        __syncthreads();
+        const int sum = carry_s + (warp > 0 ? warp_sum[warp - 1] : 0) + s;
+        // lut[i] = saturate_cast<ushort>(sum * lutScale): float product, round half to even
+        const int q = __float2int_rn(__fmul_rn(__int2float_rn(sum), g.lut_scale));
+        l[b] = (unsigned short)min(max(q, 0), 65535);
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = sum;
+        __syncthreads();
+    }
+}
+
+template <typename T, typename TO>
+__global__ void __launch_bounds__(256) k_clahe_interp(const T* __restrict__ in, const unsigned short* __restrict__ lut,
+                                                      TO* __restrict__ out, ClaheGeom g, long long plane) {
+    const T* f = in + (long long)blockIdx.z * plane;
+    const unsigned short* l = lut + (long long)blockIdx.z * g.tiles_x * g.tiles_y * CLAHE_BINS;
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= g.Ny) return;
+    const float inv_tw = __fdiv_rn(1.0f, (float)g.tw), inv_th = __fdiv_rn(1.0f, (float)g.th);
+    const float txf = __fsub_rn(__fmul_rn((float)j, inv_tw), 0.5f), tyf = __fsub_rn(__fmul_rn((float)i, inv_th), 0.5f);
+    int tx1 = (int)floorf(txf), ty1 = (int)floorf(tyf);
+    const float xa = __fsub_rn(txf, (float)tx1), ya = __fsub_rn(tyf, (float)ty1);
+    const float xa1 = __fsub_rn(1.0f, xa), ya1 = __fsub_rn(1.0f, ya);
+    const int tx2 = min(tx1 + 1, g.tiles_x - 1), ty2 = min(ty1 + 1, g.tiles_y - 1);
+    tx1 = max(tx1, 0);
+    ty1 = max(ty1, 0);
+    const int v = to_u16<T>(f[(long long)i * g.Ny + j]);
+    const float l11 = l[(long long)(ty1 * g.tiles_x + tx1) * CLAHE_BINS + v], l12 = l[(long long)(ty1 * g.tiles_x + tx2) * CLAHE_BINS + v];
+    const float l21 = l[(long long)(ty2 * g.tiles_x + tx1) * CLAHE_BINS + v], l22 = l[(long long)(ty2 * g.tiles_x + tx2) * CLAHE_BINS + v];
+    // (l11*xa1 + l12*xa)*ya1 + (l21*xa1 + l22*xa)*ya with every product and sum rounded (no contraction)
+    const float top = __fadd_rn(__fmul_rn(l11, xa1), __fmul_rn(l12, xa)), bot = __fadd_rn(__fmul_rn(l21, xa1), __fmul_rn(l22, xa));
+    const float res = __fadd_rn(__fmul_rn(top, ya1), __fmul_rn(bot, ya));
+    const int q = min(max(__float2int_rn(res), 0), 65535);
+    out[(long long)blockIdx.z * plane + (long long)i * g.Ny + j] = (TO)q;
+}
+
+// -----------------------------------------------------------------------------------------------------
+// background subtraction (:195-198): out = movie - background where blur(movie, 10) > background, else 0
+// -----------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void k_subtract_background(const T* __restrict__ movie, const T* __restrict__ blurred, T* __restrict__ out, long long n,
+                                      T background) {
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x)
+        out[k] = blurred[k] > background ? movie[k] - background : T(0);
+}
+
+}  // namespace ofb

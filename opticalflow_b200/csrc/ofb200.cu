@@ -12,6 +12,7 @@
 #include "comm.h"
 #include "halo_exchange.cuh"
 #include "coarse_fused.cuh"
+#include "legacy_kernels.cuh"
 
 using namespace ofb;
 
@@ -1169,6 +1170,185 @@ int ofb_epilogue_slab(const void* P, const void* C, const void* x3, void* vx, vo
                                                    Ny, (cudaStream_t)stream, lo, hi)
                             : epilogue_impl<double>(P, C, x3, vx, vy, speed, gamma, functionals, moments, alpha, beta, scale, B, Nx_local,
                                                     Ny, (cudaStream_t)stream, lo, hi);
+}
+
+}  // extern "C"
+
+// =====================================================================================================
+// Callers either side of the hot path (legacy_kernels.cuh)
+// =====================================================================================================
+namespace {
+
+inline int device_slot() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return std::min(std::max(dev, 0), MAX_DEVICES - 1);
+}
+inline int stream_grid(long long n, int threads) {
+    const long long blocks = (n + threads - 1) / threads;
+    return (int)std::max(1LL, std::min(blocks, (long long)device_sms() * 8));
+}
+
+template <typename T>
+int liu_shen_impl(const void* P, const void* C, void* vx, void* vy, void* speed, void* tmp_vx, void* tmp_vy, double alpha,
+                  int iterations, double scale, int B, int Nx, int Ny, cudaStream_t stream) {
+    using Cfg = LsCfg<T>;
+    auto kern = k_liu_shen_step<T>;
+    static bool configured[MAX_DEVICES] = {false};
+    const int dev = device_slot();
+    if (!configured[dev]) {
+        OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
+        configured[dev] = true;
+    }
+    const long long plane = (long long)Nx * Ny;
+    const int vec_ok = (Ny % 4 == 0 && ptr_aligned16(P) && ptr_aligned16(C) && ptr_aligned16(vx) && ptr_aligned16(vy) &&
+                        ptr_aligned16(tmp_vx) && ptr_aligned16(tmp_vy)) ? 1 : 0;
+    dim3 grid((Ny + Cfg::TW - 1) / Cfg::TW, (Nx + Cfg::TH - 1) / Cfg::TH, B);
+    T *ax = (T*)vx, *ay = (T*)vy, *bx = (T*)tmp_vx, *by = (T*)tmp_vy;
+    for (int it = 0; it < iterations; ++it) {
+        kern<<<grid, Cfg::THREADS, Cfg::SMEM, stream>>>((const T*)P, (const T*)C, ax, ay, bx, by, Nx, Ny, plane, (T)alpha, vec_ok);
+        OFB_CHECK_LAUNCH();
+        std::swap(ax, bx);
+        std::swap(ay, by);
+    }
+    if (ax != (T*)vx) {     // odd number of sweeps: the result sits in the scratch planes
+        OFB_CHECK_CUDA(cudaMemcpyAsync(vx, ax, sizeof(T) * plane * B, cudaMemcpyDeviceToDevice, stream));
+        OFB_CHECK_CUDA(cudaMemcpyAsync(vy, ay, sizeof(T) * plane * B, cudaMemcpyDeviceToDevice, stream));
+    }
+    const long long n = plane * B;
+    k_liu_shen_finish<T><<<stream_grid(n, 256), 256, 0, stream>>>((T*)vx, (T*)vy, (T*)speed, n, (T)scale);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T>
+int movie_max_impl(const void* in, long long n, double* out, cudaStream_t stream) {
+    k_fill_double<<<1, 1, 0, stream>>>(out, -INFINITY);
+    OFB_CHECK_LAUNCH();
+    k_movie_max<T><<<stream_grid(n, 256 * 8), 256, 0, stream>>>((const T*)in, n, out);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+template <typename T>
+int adaptive_threshold_impl(const void* in, const double* movie_max, unsigned char* tmp, unsigned char* out, int window, int idelta,
+                            int F, int Nx, int Ny, cudaStream_t stream) {
+    const long long plane = (long long)Nx * Ny, n = plane * F;
+    k_to_u8_range<T><<<stream_grid(n, 256 * 4), 256, 0, stream>>>((const T*)in, movie_max, tmp, n);
+    OFB_CHECK_LAUNCH();
+    auto kern = k_adaptive_threshold;
+    static bool configured[MAX_DEVICES] = {false};
+    const int dev = device_slot();
+    if (!configured[dev]) {
+        OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)adaptive_threshold_smem(255)));
+        configured[dev] = true;
+    }
+    dim3 grid((Ny + AT_TILE - 1) / AT_TILE, (Nx + AT_TILE - 1) / AT_TILE, F);
+    kern<<<grid, AT_THREADS, adaptive_threshold_smem(window), stream>>>(tmp, out, Nx, Ny, plane, window, idelta);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+inline size_t clahe_frame_bytes(int tiles_x, int tiles_y) {
+    return (size_t)tiles_x * tiles_y * CLAHE_BINS * (sizeof(int) + sizeof(unsigned short));
+}
+
+template <typename T>
+int clahe_impl(const void* in, void* out, const ClaheGeom& g, void* workspace, int frames_in_flight, int F, cudaStream_t stream) {
+    const long long plane = (long long)g.Nx * g.Ny;
+    const size_t tiles = (size_t)g.tiles_x * g.tiles_y;
+    int* hist = (int*)workspace;
+    unsigned short* lut = (unsigned short*)((char*)workspace + (size_t)frames_in_flight * tiles * CLAHE_BINS * sizeof(int));
+    for (int f0 = 0; f0 < F; f0 += frames_in_flight) {
+        const int nf = std::min(frames_in_flight, F - f0);
+        const T* src = (const T*)in + plane * f0;
+        OFB_CHECK_CUDA(cudaMemsetAsync(hist, 0, (size_t)nf * tiles * CLAHE_BINS * sizeof(int), stream));
+        k_clahe_hist<T><<<dim3((g.ext_y + 255) / 256, g.ext_x, nf), 256, 0, stream>>>(src, hist, g, plane);
+        OFB_CHECK_LAUNCH();
+        k_clahe_lut<<<dim3((unsigned)tiles, nf), 1024, 0, stream>>>(hist, lut, g);
+        OFB_CHECK_LAUNCH();
+        k_clahe_interp<T, T><<<dim3((g.Ny + 255) / 256, g.Nx, nf), 256, 0, stream>>>(src, lut, (T*)out + plane * f0, g, plane);
+        OFB_CHECK_LAUNCH();
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ofb_liu_shen(const void* P, const void* C, void* vx, void* vy, void* speed, void* tmp_vx, void* tmp_vy, double alpha,
+                 int iterations, double scale, int B, int Nx, int Ny, int dtype, void* stream) {
+    if (B < 1 || Nx < 2 || Ny < 2) return fail(-1, "ofb_liu_shen: bad shape %d x %d x %d (frames must be at least 2x2)", B, Nx, Ny);
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    if (iterations < 0) return fail(-6, "ofb_liu_shen: iterations must be >= 0 (got %d)", iterations);
+    if (!P || !C || !vx || !vy || !speed || !tmp_vx || !tmp_vy) return fail(-6, "ofb_liu_shen: null pointer");
+    if (vx == tmp_vx || vy == tmp_vy || vx == vy || tmp_vx == tmp_vy) return fail(-7, "ofb_liu_shen: velocity planes must not alias");
+    return dtype == OFB_F32 ? liu_shen_impl<float>(P, C, vx, vy, speed, tmp_vx, tmp_vy, alpha, iterations, scale, B, Nx, Ny, (cudaStream_t)stream)
+                            : liu_shen_impl<double>(P, C, vx, vy, speed, tmp_vx, tmp_vy, alpha, iterations, scale, B, Nx, Ny, (cudaStream_t)stream);
+}
+
+int ofb_movie_max(const void* in, long long n, int dtype, double* max_out, void* stream) {
+    if (n < 1 || !in || !max_out) return fail(-1, "ofb_movie_max: empty input");
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    return dtype == OFB_F32 ? movie_max_impl<float>(in, n, max_out, (cudaStream_t)stream)
+                            : movie_max_impl<double>(in, n, max_out, (cudaStream_t)stream);
+}
+
+int ofb_adaptive_threshold(const void* in, const double* movie_max, unsigned char* tmp_u8, unsigned char* out, int window, int idelta,
+                           int F, int Nx, int Ny, int dtype, void* stream) {
+    if (F < 1 || Nx < 1 || Ny < 1) return fail(-1, "ofb_adaptive_threshold: bad shape %d x %d x %d", F, Nx, Ny);
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    // cv2.adaptiveThreshold asserts blockSize % 2 == 1 && blockSize > 1; 255 keeps the row sums in 16 bits
+    if (window < 3 || window > 255 || window % 2 == 0) return fail(-6, "ofb_adaptive_threshold: window must be odd and in 3..255 (got %d)", window);
+    if (!in || !movie_max || !tmp_u8 || !out || tmp_u8 == out) return fail(-7, "ofb_adaptive_threshold: null or aliasing buffers");
+    return dtype == OFB_F32 ? adaptive_threshold_impl<float>(in, movie_max, tmp_u8, out, window, idelta, F, Nx, Ny, (cudaStream_t)stream)
+                            : adaptive_threshold_impl<double>(in, movie_max, tmp_u8, out, window, idelta, F, Nx, Ny, (cudaStream_t)stream);
+}
+
+size_t ofb_clahe_workspace_bytes(int frames_in_flight, int tiles_x, int tiles_y) {
+    if (frames_in_flight < 1 || tiles_x < 1 || tiles_y < 1) return 0;
+    return (size_t)frames_in_flight * clahe_frame_bytes(tiles_x, tiles_y);
+}
+
+int ofb_clahe(const void* in, void* out, double clip_limit, int tiles_x, int tiles_y, void* workspace, size_t workspace_bytes, int F,
+              int Nx, int Ny, int dtype, void* stream) {
+    if (F < 1 || Nx < 1 || Ny < 1) return fail(-1, "ofb_clahe: bad shape %d x %d x %d", F, Nx, Ny);
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    if (tiles_x < 1 || tiles_y < 1) return fail(-6, "ofb_clahe: tile grid must be at least 1 x 1 (got %d x %d)", tiles_x, tiles_y);
+    if (!in || !out || in == out || !workspace) return fail(-7, "ofb_clahe: null or aliasing buffers");
+    ClaheGeom g;
+    g.Nx = Nx; g.Ny = Ny; g.tiles_x = tiles_x; g.tiles_y = tiles_y;
+    if (Ny % tiles_x == 0 && Nx % tiles_y == 0) {
+        g.ext_x = Nx; g.ext_y = Ny;
+    } else {        // clahe.cpp: copyMakeBorder(0, tilesY - rows % tilesY, 0, tilesX - cols % tilesX, BORDER_REFLECT_101)
+        g.ext_x = Nx + (tiles_y - Nx % tiles_y);
+        g.ext_y = Ny + (tiles_x - Ny % tiles_x);
+        if (g.ext_x - Nx > Nx - 1 || g.ext_y - Ny > Ny - 1)
+            return fail(-6, "ofb_clahe: a %d x %d tile grid needs more reflected border than a %d x %d frame has", tiles_x, tiles_y, Nx, Ny);
+    }
+    g.tw = g.ext_y / tiles_x;
+    g.th = g.ext_x / tiles_y;
+    const int area = g.tw * g.th;
+    g.lut_scale = (float)(CLAHE_BINS - 1) / area;
+    g.clip = 0;
+    if (clip_limit > 0.0) g.clip = std::max((int)(clip_limit * area / CLAHE_BINS), 1);
+    const size_t per_frame = clahe_frame_bytes(tiles_x, tiles_y);
+    const int in_flight = (int)std::min<size_t>(workspace_bytes / per_frame, (size_t)F);
+    if (in_flight < 1) return fail(-5, "ofb_clahe: workspace too small: %zu bytes given, %zu per frame needed", workspace_bytes, per_frame);
+    return dtype == OFB_F32 ? clahe_impl<float>(in, out, g, workspace, in_flight, F, (cudaStream_t)stream)
+                            : clahe_impl<double>(in, out, g, workspace, in_flight, F, (cudaStream_t)stream);
+}
+
+int ofb_subtract_background(const void* movie, const void* blurred, void* out, double background, long long n, int dtype, void* stream) {
+    if (n < 1 || !movie || !blurred || !out) return fail(-1, "ofb_subtract_background: empty input");
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    if (dtype == OFB_F32)
+        k_subtract_background<float><<<stream_grid(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>((const float*)movie, (const float*)blurred, (float*)out, n, (float)background);
+    else
+        k_subtract_background<double><<<stream_grid(n, 256 * 4), 256, 0, (cudaStream_t)stream>>>((const double*)movie, (const double*)blurred, (double*)out, n, background);
+    OFB_CHECK_LAUNCH();
+    return 0;
 }
 
 }  // extern "C"

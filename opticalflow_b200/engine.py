@@ -191,3 +191,70 @@ def epilogue(P, C, x, speed_alpha, remodelling_alpha, scale, out=None):
                                         _ptr(out[3]), _ptr(fun), _ptr(mom), _ptr(a), _ptr(be), float(scale), B, Nx, Ny, _code(P),
                                         _stream_ptr(P.device)))
     return out[0], out[1], out[2], out[3], fun, mom
+
+
+# ------------------------------------------------------------------------------------------------
+# callers either side of the hot path (SURVEY.md 8f NEXT-3 / NEXT-4)
+# ------------------------------------------------------------------------------------------------
+def liu_shen(P, C, vx, vy, alpha, iterations, scale=1.0):
+    """``iterations`` Liu-Shen Jacobi sweeps on ``B`` pairs (optical_flow.py:507-651); ``vx, vy [B,Nx,Ny]`` hold the initial
+    guess in pixel units and are overwritten with the scaled velocities.  Returns ``(vx, vy, speed)``."""
+    _require_cuda(P, C, vx, vy)
+    B, Nx, Ny = P.shape
+    for t in (C, vx, vy):
+        assert t.is_contiguous() and t.shape == P.shape and t.dtype == P.dtype
+    assert P.is_contiguous()
+    speed, tx, ty = torch.empty_like(vx), torch.empty_like(vx), torch.empty_like(vy)
+    _lib.check(_lib.load().ofb_liu_shen(_ptr(P), _ptr(C), _ptr(vx), _ptr(vy), _ptr(speed), _ptr(tx), _ptr(ty), float(alpha),
+                                        int(iterations), float(scale), B, Nx, Ny, _code(P), _stream_ptr(P.device)))
+    return vx, vy, speed
+
+
+def movie_max(frames):
+    """np.max of a device movie as a one-element float64 device tensor."""
+    _require_cuda(frames)
+    frames = frames.contiguous()
+    out = torch.empty(1, dtype=torch.float64, device=frames.device)
+    _lib.check(_lib.load().ofb_movie_max(_ptr(frames), frames.numel(), _code(frames), _ptr(out), _stream_ptr(frames.device)))
+    return out
+
+
+def adaptive_threshold(frames, window_size, threshold):
+    """optical_flow.py:328-335 on device frames ``[F,Nx,Ny]`` -> bool tensor."""
+    _require_cuda(frames)
+    frames = frames.contiguous()
+    F, Nx, Ny = frames.shape
+    mx = movie_max(frames)
+    tmp = torch.empty((F, Nx, Ny), dtype=torch.uint8, device=frames.device)
+    out = torch.empty_like(tmp)
+    _lib.check(_lib.load().ofb_adaptive_threshold(_ptr(frames), _ptr(mx), _ptr(tmp), _ptr(out), int(window_size),
+                                                  int(np.ceil(threshold)), F, Nx, Ny, _code(frames), _stream_ptr(frames.device)))
+    return out.view(torch.bool)
+
+
+def clahe(frames, clip_limit, tiles_x, tiles_y, frames_in_flight=8):
+    """optical_flow.py:362-370 on device frames ``[F,Nx,Ny]`` (values are truncated to uint16 like ``astype``)."""
+    _require_cuda(frames)
+    frames = frames.contiguous()
+    F, Nx, Ny = frames.shape
+    lib = _lib.load()
+    in_flight = max(1, min(int(frames_in_flight), F))
+    nbytes = lib.ofb_clahe_workspace_bytes(in_flight, int(tiles_x), int(tiles_y))
+    if nbytes == 0:
+        raise _lib.OfbError('CLAHE tile grid must be at least 1 x 1 (got %r x %r)' % (tiles_x, tiles_y))
+    workspace = torch.empty(nbytes, dtype=torch.uint8, device=frames.device)
+    out = torch.empty_like(frames)
+    _lib.check(lib.ofb_clahe(_ptr(frames), _ptr(out), float(clip_limit), int(tiles_x), int(tiles_y), _ptr(workspace), nbytes,
+                             F, Nx, Ny, _code(frames), _stream_ptr(frames.device)))
+    return out
+
+
+def subtract_background(frames, blurred, background):
+    """optical_flow.py:195-198: ``frames - background`` where ``blurred > background``, else 0."""
+    _require_cuda(frames, blurred)
+    frames, blurred = frames.contiguous(), blurred.contiguous()
+    assert frames.shape == blurred.shape and frames.dtype == blurred.dtype
+    out = torch.empty_like(frames)
+    _lib.check(_lib.load().ofb_subtract_background(_ptr(frames), _ptr(blurred), _ptr(out), float(background), frames.numel(),
+                                                   _code(frames), _stream_ptr(frames.device)))
+    return out

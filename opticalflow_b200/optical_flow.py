@@ -1,8 +1,10 @@
 """Drop-in for the hot path of kursawe/OpticalFlow ``source/optical_flow.py``.
 
 Same entry points, argument conventions and result dictionaries as the reference
-(``variational_optical_flow`` :715-1210, ``vary_regularisation`` :1918-1998, ``blur_movie`` :282-306 and the
-small helpers :676-713, :1212-1316); the work is done by hand-written sm_100a kernels behind the C ABI of
+(``variational_optical_flow`` :715-1210, ``vary_regularisation`` :1918-1998, ``blur_movie`` :282-306, the
+small helpers :676-713, :1212-1316, and the callers either side of the path: ``apply_adaptive_threshold``
+:308-338, ``apply_clahe`` :340-374, the background subtraction :195-198, ``liu_shen_optical_flow_jit`` :426-673
+with its driver ``conduct_variational_optical_flow_deprecated`` :1318-1529); the work is done by hand-written sm_100a kernels behind the C ABI of
 ``include/ofb200.h``.  There is no CPU fallback: without a CUDA device or without ``libofb200.so`` the
 calls raise.
 
@@ -25,7 +27,8 @@ import torch
 from . import _lib, engine, hostio, sharding
 
 __all__ = ['variational_optical_flow', 'vary_regularisation', 'blur_movie', 'apply_numerical_derivative',
-           'apply_constant_boundary_condition', 'get_index_set', 'format_elapsed_time']
+           'apply_constant_boundary_condition', 'get_index_set', 'format_elapsed_time', 'apply_adaptive_threshold',
+           'apply_clahe', 'subtract_background', 'liu_shen_optical_flow_jit', 'conduct_variational_optical_flow_deprecated']
 
 _QUANTITY_OFFSET = {'ux': 0, 'uy': 1, 'remodelling': 2}
 
@@ -412,3 +415,162 @@ def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
     if filename is not None:
         np.save(filename, result_dict)
     return result_dict
+
+
+# ------------------------------------------------------------------------------------------------
+# pre-processing upstream of the flow call (SURVEY.md 8f NEXT-3)
+# ------------------------------------------------------------------------------------------------
+def _to_device_float(movie, dev, dtype=None):
+    """Movie -> contiguous device tensor.  Integer movies become float64 (numpy's true division promotes them the
+    same way); float32 / float64 movies keep their type unless ``dtype`` is given."""
+    movie = np.ascontiguousarray(np.asarray(movie))
+    if dtype is None:
+        dtype = movie.dtype if movie.dtype in (np.float32, np.float64) else np.float64
+    tdtype, _ = engine.resolve_dtype(dtype)
+    return hostio.as_native_tensor(movie).to(dev).to(tdtype)
+
+
+def apply_adaptive_threshold(movie, window_size=51, threshold=0.0, *, device=None):
+    """OpenCV mean adaptive threshold of every frame (optical_flow.py:308-338), on the GPU.
+
+    The movie is mapped to uint8 by ``movie/np.max(movie)*255`` (:328); a pixel is True where it exceeds the
+    ``window_size`` x ``window_size`` box mean (replicated border) minus ``ceil(threshold)``.  Returns a bool
+    array of the movie's shape.  ``window_size`` must be odd, 3..255 (cv2 asserts odd and > 1)."""
+    dev = _device(device)
+    frames = _to_device_float(movie, dev)
+    return engine.adaptive_threshold(frames, window_size, threshold).cpu().numpy()
+
+
+def apply_clahe(movie, clipLimit=50000, tile_number=10, *, device=None, verbose=False):
+    """OpenCV CLAHE of every frame on ``movie.astype(uint16)`` (optical_flow.py:340-374), on the GPU.
+
+    ``tile_number`` tiles split the columns and ``round(tile_number * Ny/Nx)`` tiles the rows - that is what the
+    reference's ``tileGridSize=(tile_number, round(tile_number*aspect_ratio))`` means to OpenCV (:364-366).
+    Returns float64 like the reference (which also prints the maximum, :372: here only with ``verbose``)."""
+    dev = _device(device)
+    movie = np.asarray(movie)
+    frames = _to_device_float(movie, dev)
+    aspect_ratio = movie.shape[2] / movie.shape[1]
+    out = engine.clahe(frames, clipLimit, int(tile_number), int(round(tile_number * aspect_ratio)))
+    out = out.to(torch.float64).cpu().numpy()
+    if verbose:
+        print(np.max(out))
+    return out
+
+
+def subtract_background(movie, background, *, thresholding_sigma=10, dtype='float64', device=None):
+    """Background subtraction of ``conduct_optical_flow`` (optical_flow.py:195-198; inline there, a function here):
+    ``movie - background`` where the ``sigma=10`` blur of the movie exceeds ``background``, 0 elsewhere."""
+    dev = _device(device)
+    frames = _to_device_float(movie, dev, dtype)
+    blurred = engine.blur(frames, thresholding_sigma)
+    return engine.subtract_background(frames, blurred, background).to(torch.float64).cpu().numpy()
+
+
+# ------------------------------------------------------------------------------------------------
+# Liu-Shen Jacobi solver behind the deprecated driver (SURVEY.md 8f NEXT-4)
+# ------------------------------------------------------------------------------------------------
+def _guess(value, n_pairs, Nx, Ny):
+    """Initial guess as a [n_pairs or 1, Nx, Ny] float64 stack: one frame-shaped plane for every pair (the reference,
+    :497-499) or one plane per pair (what its driver feeds back when it records iterates, :1458-1460)."""
+    plane = np.zeros((Nx, Ny)) if value is None else np.asarray(value, dtype=np.float64)
+    if plane.shape == (Nx, Ny):
+        return plane[None]
+    if plane.shape != (n_pairs, Nx, Ny):
+        raise ValueError('initial guess must have the frame shape %r or %r, got %r' % ((Nx, Ny), (n_pairs, Nx, Ny), plane.shape))
+    return plane
+
+
+def liu_shen_optical_flow_jit(movie, delta_x=1.0, delta_t=1.0, alpha=100, remodelling_alpha=1.0, initial_v_x=None,
+                              initial_v_y=None, initial_remodelling=None, max_iterations=10, tolerance=1e-9,
+                              include_remodelling=True, *, dtype='float64', device=None, batch_pairs=None):
+    """Liu-Shen variational flow by ``max_iterations`` Jacobi sweeps per frame pair (optical_flow.py:426-673), on the GPU.
+
+    Same positional arguments and the same 5-tuple ``(v_x, v_y, speed, remodelling, last_iteration_index)`` as the
+    reference.  Like there, ``tolerance``, ``remodelling_alpha`` and ``include_remodelling`` have no effect, every
+    pair restarts from the initial guess (:497-499) and ``remodelling`` is the initial guess handed back (:499).
+    The reference's default guesses are 10x10 zero arrays, which only fit 10x10 frames: ``None`` here means zeros
+    of the frame shape.  A guess may also be a ``[T-1, Nx, Ny]`` stack (one plane per pair)."""
+    dev = _device(device)
+    tdtype, _ = engine.resolve_dtype(dtype)
+    movie = np.asarray(movie)
+    T, Nx, Ny = movie.shape
+    if max_iterations < 1:
+        raise ValueError('max_iterations must be at least 1 (the reference returns an unbound iteration index otherwise)')
+    n_pairs = T - 1
+    guess_x = _guess(initial_v_x, n_pairs, Nx, Ny) * delta_t / delta_x
+    guess_y = _guess(initial_v_y, n_pairs, Nx, Ny) * delta_t / delta_x
+    all_remodelling = np.broadcast_to(_guess(initial_remodelling, n_pairs, Nx, Ny), (n_pairs, Nx, Ny)).copy()
+    out = [np.zeros((n_pairs, Nx, Ny)) for _ in range(3)]
+    if n_pairs < 1:
+        return out[0], out[1], out[2], all_remodelling, max_iterations - 1
+    frames = _to_device_float(movie, dev, 'float32' if tdtype == torch.float32 else 'float64')
+    gx = torch.from_numpy(guess_x).to(dev).to(tdtype)
+    gy = torch.from_numpy(guess_y).to(dev).to(tdtype)
+    itemsize = 4 if tdtype == torch.float32 else 8
+    B = int(batch_pairs) if batch_pairs else int(max(1, min(n_pairs, (2 << 30) // (6 * Nx * Ny * itemsize))))
+    for k0 in range(0, n_pairs, B):
+        k1 = min(k0 + B, n_pairs)
+        vx = (gx[k0:k1] if gx.shape[0] > 1 else gx.expand(k1 - k0, Nx, Ny)).contiguous().clone()
+        vy = (gy[k0:k1] if gy.shape[0] > 1 else gy.expand(k1 - k0, Nx, Ny)).contiguous().clone()
+        fields = engine.liu_shen(frames[k0:k1], frames[k0 + 1:k1 + 1], vx, vy, alpha, max_iterations, delta_x / delta_t)
+        for dst, src in zip(out, fields):
+            dst[k0:k1] = src.to(torch.float64).cpu().numpy()
+    return out[0], out[1], out[2], all_remodelling, max_iterations - 1
+
+
+def conduct_variational_optical_flow_deprecated(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, remodelling_alpha=1000.0,
+                                                v_x_guess=0.1, v_y_guess=0.1, remodelling_guess=0.5, max_iterations=10,
+                                                smoothing_sigma=None, return_iterations=False, iteration_stepsize=1,
+                                                tolerance=1e-10, include_remodelling=True, use_liu_shen=False, *,
+                                                dtype='float64', device=None):
+    """Driver of the Liu-Shen solver (optical_flow.py:1318-1529): optional blur, constant initial guesses, optionally
+    the iterates every ``iteration_stepsize`` sweeps.
+
+    The reference driver cannot run as committed - it unpacks four values from a function that returns five
+    (:1422, :1492 vs :673); this one takes the five and otherwise keeps the reference's result keys, including
+    ``total_iterations = max_iterations``."""
+    if smoothing_sigma is not None:
+        movie_to_analyse = blur_movie(movie, smoothing_sigma, device=device)
+    else:
+        movie_to_analyse = movie
+    if not use_liu_shen:
+        raise ValueError("I can currently only really do this for the liu shen jitted method")
+    movie_np = np.asarray(movie)
+    shape = (movie_np.shape[1], movie_np.shape[2])
+    initial_v_x = np.full(shape, float(v_x_guess))
+    initial_v_y = np.full(shape, float(v_y_guess))
+    initial_remodelling = np.full(shape, float(remodelling_guess))
+    solver = dict(tolerance=tolerance, include_remodelling=include_remodelling, dtype=dtype, device=device)
+    result = dict()
+    if return_iterations:
+        recorded = max_iterations // iteration_stepsize
+        fields = liu_shen_optical_flow_jit(movie_to_analyse, delta_x, delta_t, speed_alpha, remodelling_alpha, initial_v_x,
+                                           initial_v_y, initial_remodelling, max_iterations=iteration_stepsize, **solver)[:4]
+        steps = [np.zeros((fields[0].shape[0], recorded + 1) + shape) for _ in range(4)]
+        firsts = (initial_v_x, initial_v_y, np.sqrt(initial_v_x ** 2 + initial_v_y ** 2), initial_remodelling)
+        for store, first, field in zip(steps, firsts, fields):
+            store[:, 0] = first
+            store[:, 1] = field
+        for index in range(2, recorded + 1):
+            # the reference feeds the velocity stacks back as the next initial guess (:1458-1460): one plane per pair
+            fields = liu_shen_optical_flow_jit(movie_to_analyse, delta_x, delta_t, speed_alpha, remodelling_alpha, fields[0],
+                                               fields[1], fields[3], max_iterations=iteration_stepsize, **solver)[:4]
+            for store, field in zip(steps, fields):
+                store[:, index] = field
+        for key, store in zip(('v_x', 'v_y', 'speed', 'remodelling'), steps):
+            result[key] = store[:, -1]
+            result[key + '_steps'] = store
+        result['iteration_stepsize'] = iteration_stepsize
+    else:
+        fields = liu_shen_optical_flow_jit(movie_to_analyse, delta_x, delta_t, speed_alpha, remodelling_alpha, initial_v_x,
+                                           initial_v_y, initial_remodelling, max_iterations, **solver)
+        for key, field in zip(('v_x', 'v_y', 'speed', 'remodelling'), fields):
+            result[key] = field
+    result['original_data'] = movie
+    result['delta_x'] = delta_x
+    result['delta_t'] = delta_t
+    result['blurred_data'] = movie_to_analyse
+    result['max_iterations'] = max_iterations
+    result['total_iterations'] = max_iterations
+    return result

@@ -63,5 +63,58 @@ def main():
         print(name, movie.shape, 'max residual %.2e' % max(residuals))
 
 
+def _texture(T, Nx, Ny, seed, lo=20.0, hi=220.0):
+    """Smooth random texture drifting by one pixel per frame plus a slow brightening (stored in the fixture)."""
+    import scipy.ndimage
+    rng = np.random.default_rng(seed)
+    base = scipy.ndimage.gaussian_filter(rng.standard_normal((Nx + 2 * T, Ny + 2 * T)), 2.0)
+    base = (base - base.min()) / (base.max() - base.min()) * (hi - lo) + lo
+    return np.stack([base[T + t:T + t + Nx, T:T + Ny] + 0.3 * t for t in range(T)])
+
+
+def make_legacy():
+    """Fixtures for the callers either side of the hot path (SURVEY 8f NEXT-3/NEXT-4): the reference's own numba
+    (liu_shen_optical_flow_jit) and OpenCV (apply_adaptive_threshold, apply_clahe) code, run unmodified here."""
+    import contextlib
+    import io
+    ref = ref_import.import_reference()
+    rng = np.random.default_rng(42)
+    payload = {}
+    # --- Liu-Shen: ragged three-frame movie with random guesses and unit scaling, and the driver's constant guesses
+    movie = _texture(3, 22, 19, 1)
+    gx, gy, gr = (rng.standard_normal((22, 19)) * 0.1 for _ in range(3))
+    out = ref.liu_shen_optical_flow_jit(movie, 0.5, 2.0, 100.0, 1.0, gx, gy, gr, 7, 1e-9, True)
+    payload.update(ls_a_movie=movie, ls_a_gx=gx, ls_a_gy=gy, ls_a_gr=gr, ls_a_args=np.array([0.5, 2.0, 100.0, 7]),
+                   ls_a_vx=out[0], ls_a_vy=out[1], ls_a_speed=out[2], ls_a_rem=out[3], ls_a_last=np.array(out[4]))
+    movie = _texture(2, 16, 136, 2)          # wider than one 128-column tile
+    g = np.full((16, 136), 0.1)
+    out = ref.liu_shen_optical_flow_jit(movie, 1.0, 1.0, 1e4, 1.0, g, g, np.full((16, 136), 0.5), 12, 1e-9, True)
+    payload.update(ls_b_movie=movie, ls_b_args=np.array([1.0, 1.0, 1e4, 12]), ls_b_vx=out[0], ls_b_vy=out[1], ls_b_speed=out[2])
+    # --- adaptive threshold (defaults; and the analysis scripts' window 151 / threshold -5)
+    movie = np.abs(_texture(2, 70, 90, 3)) ** 1.5
+    payload.update(th_a_movie=movie, th_a_args=np.array([51, 0.0]), th_a_out=np.packbits(ref.apply_adaptive_threshold(movie, 51, 0.0)))
+    movie = _texture(2, 160, 150, 4)
+    payload.update(th_b_movie=movie, th_b_args=np.array([151, -5.0]), th_b_out=np.packbits(ref.apply_adaptive_threshold(movie, 151, -5)))
+    movie = _texture(1, 33, 47, 5).astype(np.float32)
+    payload.update(th_c_movie=movie, th_c_args=np.array([5, 2.5]), th_c_out=np.packbits(ref.apply_adaptive_threshold(movie, 5, 2.5)))
+    # --- CLAHE (tile grid dividing the frame; and the reflected-border path with a clip limit that bites)
+    with contextlib.redirect_stdout(io.StringIO()):
+        movie = _texture(2, 100, 100, 6) * 150.0
+        payload.update(cl_a_movie=movie, cl_a_args=np.array([50000, 10]), cl_a_out=ref.apply_clahe(movie, 50000, 10).astype(np.uint16))
+        movie = _texture(2, 90, 70, 7) * 40.0
+        payload.update(cl_b_movie=movie, cl_b_args=np.array([1000, 10]), cl_b_out=ref.apply_clahe(movie, 1000, 10).astype(np.uint16))
+        movie = np.round(_texture(1, 64, 96, 8))         # few distinct values: clipping and residual redistribution
+        payload.update(cl_c_movie=movie, cl_c_args=np.array([2.0, 4]), cl_c_out=ref.apply_clahe(movie, 2.0, 4).astype(np.uint16))
+    # --- background subtraction: conduct_optical_flow hands movie_to_analyse back as 'blurred_data' (:195-198, :214)
+    movie = _texture(2, 64, 72, 9)
+    with contextlib.redirect_stdout(io.StringIO()):
+        res = ref.conduct_optical_flow(movie, boxsize=5, background=120.0)
+    payload.update(bg_movie=movie, bg_level=np.array(120.0), bg_out=res['blurred_data'])
+    np.savez_compressed(os.path.join(GOLDEN, 'legacy_callers.npz'), **payload)
+    print('legacy_callers', {k: v.shape for k, v in payload.items() if k.endswith('_out') or k.endswith('_vx')})
+
+
 if __name__ == '__main__':
-    main()
+    if '--legacy-only' not in sys.argv:
+        main()
+    make_legacy()

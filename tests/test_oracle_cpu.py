@@ -23,7 +23,8 @@ def load_golden(name):
     return z, kwargs
 
 
-GOLDEN_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, '*.npz')))
+GOLDEN_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, '*.npz'))
+                      if not os.path.basename(p).startswith('legacy_'))      # legacy_*.npz: tests/test_legacy_*.py
 
 
 def test_golden_fixtures_exist():
