@@ -18,12 +18,13 @@ namespace ofb {
 // shared loads and stores 16 bytes.  Algorithmic traffic: read vx, vy, P, C, write vx', vy' = 6 words per pixel.
 // -----------------------------------------------------------------------------------------------------
 template <typename T> struct LsCfg {
-    static constexpr int TW = 128;                 // tile width (columns)
-    static constexpr int TH = 128 / sizeof(T);     // tile height: 32 rows fp32, 16 rows fp64
+    static constexpr int TW = 128;                 // tile width (columns): one warp spans it with four columns per lane
+    static constexpr int RPT = 4;                  // consecutive rows per thread (rolling three-row window)
+    static constexpr int THREADS = 128;
+    static constexpr int TH = RPT * THREADS / 32;  // tile height: 16 rows
     static constexpr int OFF = 4;                  // column of the first body element in a shared row (16-byte aligned)
     static constexpr int PITCH = TW + 8;
-    static constexpr int THREADS = 256;
-    static constexpr int MIN_CTAS = sizeof(T) == 4 ? 3 : 2;   // resident CTAs per SM the register budget is held to
+    static constexpr int MIN_CTAS = sizeof(T) == 4 ? 5 : 2;   // resident CTAs per SM the register budget is held to
     static constexpr size_t SMEM = (size_t)4 * (TH + 2) * PITCH * sizeof(T);
 };
 
@@ -58,14 +59,47 @@ __device__ __forceinline__ void st4(T* p, const T (&v)[4]) {
     }
 }
 
-// six consecutive elements of a shared row starting one left of the thread's body columns
-template <typename T>
-__device__ __forceinline__ void ld6_shared(const T* row, int body, T (&a)[6]) {
-    a[0] = row[body - 1];
-    const Vec4<T> m = ld4_global<T>(row + body);
-    a[1] = m.v[0]; a[2] = m.v[1]; a[3] = m.v[2]; a[4] = m.v[3];
-    a[5] = row[body + 4];
+// 16-byte asynchronous global -> shared copy (LDGSTS): the whole tile is in flight before anybody waits
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
 }
+__device__ __forceinline__ void cp_async_wait_all() {
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;\n" ::: "memory");
+}
+
+// Six consecutive elements of a shared row starting one left of the lane's four body columns.  The neighbours come from
+// the adjacent lanes by shuffle (a scalar shared load at a 16-byte lane stride would be a 4-way bank conflict); the halo
+// columns are read by every lane as a broadcast (lane 0 / lane 31 read the halo word, the others one common word) and
+// selected, so the row load is branch-free.
+template <typename T>
+__device__ __forceinline__ void ld6_shared(const T* row, int lane, T (&a)[6]) {
+    constexpr int OFF = LsCfg<T>::OFF, TW = LsCfg<T>::TW;
+    const Vec4<T> m = ld4_global<T>(row + OFF + 4 * lane);
+    a[1] = m.v[0]; a[2] = m.v[1]; a[3] = m.v[2]; a[4] = m.v[3];
+    const T left = __shfl_up_sync(FULL, m.v[3], 1), right = __shfl_down_sync(FULL, m.v[0], 1);
+    const T hl = row[lane == 0 ? OFF - 1 : OFF], hr = row[lane == 31 ? OFF + TW : OFF];
+    a[0] = lane == 0 ? hl : left;
+    a[5] = lane == 31 ? hr : right;
+}
+
+// 1/d without the slow-path branch of the IEEE division: SFU seed + Newton steps (float: 1 step, ~1 ulp; double: the
+// 20-bit seed squared twice, ~1 ulp).  The 2x2 determinants here are far from the denormal range.
+__device__ __forceinline__ float ls_rcp(float d) {
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(d));
+    return fmaf(r, fmaf(-d, r, 1.0f), r);
+}
+__device__ __forceinline__ double ls_rcp(double d) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+    r = fma(r, fma(-d, r, 1.0), r);
+    r = fma(r, fma(-d, r, 1.0), r);
+    return fma(r, fma(-d, r, 1.0), r);
+}
+
+template <typename T, bool EDGE>
+__device__ __forceinline__ void liu_shen_tile(T* s_vx, T* s_vy, T* s_p, T* s_c, T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny,
+                                              long long base, T alpha, int vec_ok, int i0, int c0);
 
 template <typename T>
 __global__ void __launch_bounds__(LsCfg<T>::THREADS, LsCfg<T>::MIN_CTAS)
@@ -73,6 +107,7 @@ k_liu_shen_step(const T* __restrict__ P, const T* __restrict__ C, const T* __res
                 T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny, long long plane, T alpha, int vec_ok) {
     using Cfg = LsCfg<T>;
     constexpr int TW = Cfg::TW, TH = Cfg::TH, OFF = Cfg::OFF, PITCH = Cfg::PITCH;
+    constexpr int WARPS = Cfg::THREADS / 32;
     extern __shared__ __align__(16) unsigned char ls_smem[];
     T* s_vx = reinterpret_cast<T*>(ls_smem);
     T* s_vy = s_vx + (TH + 2) * PITCH;
@@ -84,76 +119,101 @@ k_liu_shen_step(const T* __restrict__ P, const T* __restrict__ C, const T* __res
     const T* src[4] = {vx_in + base, vy_in + base, P + base, C + base};
     T* dst[4] = {s_vx, s_vy, s_p, s_c};
 
-    // ---- stage the tile: warp per row, lane per four body columns, lanes 0/1 also fetch the halo columns
-    for (int rr = warp; rr < TH + 2; rr += Cfg::THREADS / 32) {
-        const int gi = ls_mirror(i0 - 1 + rr, Nx);
+    // ---- stage the tile: warp per row, lane per four body columns (asynchronous 16-byte copies), then the halo columns
+    {
         const int j = c0 + 4 * lane;
         const bool fast = vec_ok && j + 3 < Ny;
-        const int jh = ls_mirror(lane == 0 ? c0 - 1 : c0 + TW, Ny);
+        for (int rr = warp; rr < TH + 2; rr += WARPS) {
+            const long long grow = (long long)ls_mirror(i0 - 1 + rr, Nx) * Ny;
 #pragma unroll
-        for (int a = 0; a < 4; ++a) {
-            const T* g = src[a] + (long long)gi * Ny;
-            T* s = dst[a] + rr * PITCH + OFF;
-            Vec4<T> v;
-            if (fast) {
-                v = ld4_global<T>(g + j);
-            } else {
+            for (int a = 0; a < 4; ++a) {
+                const T* g = src[a] + grow;
+                T* s = dst[a] + rr * PITCH + OFF + 4 * lane;
+                if (fast) {
+                    cp_async16(s, g + j);
+                    if constexpr (sizeof(T) == 8) cp_async16(s + 2, g + j + 2);
+                } else {
+                    Vec4<T> v;
 #pragma unroll
-                for (int k = 0; k < 4; ++k) v.v[k] = g[ls_mirror(j + k, Ny)];
+                    for (int k = 0; k < 4; ++k) v.v[k] = g[ls_mirror(j + k, Ny)];
+                    st4<T>(s, v.v);
+                }
             }
-            st4<T>(s + 4 * lane, v.v);
-            if (lane == 0) s[-1] = g[jh];
-            if (lane == 1) s[TW] = g[jh];
         }
+        const int jl = ls_mirror(c0 - 1, Ny), jr = ls_mirror(c0 + TW, Ny);
+        for (int e = threadIdx.x; e < 2 * (TH + 2); e += Cfg::THREADS) {
+            const int rr = e >> 1, side = e & 1;
+            const long long g = (long long)ls_mirror(i0 - 1 + rr, Nx) * Ny + (side ? jr : jl);
+            const int so = rr * PITCH + (side ? OFF + TW : OFF - 1);
+#pragma unroll
+            for (int a = 0; a < 4; ++a) dst[a][so] = src[a][g];
+        }
+        cp_async_wait_all();
     }
     __syncthreads();
+    // tiles that touch the frame edge take the general path (zero-masked neighbour sums, 3/5/8 prefactor, ragged stores)
+    const bool edge = i0 == 0 || i0 + TH >= Nx || c0 == 0 || c0 + TW >= Ny || !vec_ok;
+    if (edge) liu_shen_tile<T, true>(s_vx, s_vy, s_p, s_c, vx_out, vy_out, Nx, Ny, base, alpha, vec_ok, i0, c0);
+    else liu_shen_tile<T, false>(s_vx, s_vy, s_p, s_c, vx_out, vy_out, Nx, Ny, base, alpha, vec_ok, i0, c0);
+}
 
-    // ---- update: thread = four adjacent columns, rows rg, rg+8, ...
-    const int cg = threadIdx.x & 31, rg = threadIdx.x >> 5;
-    const int j = c0 + 4 * cg;
-    const int body = OFF + 4 * cg;
+template <typename T, bool EDGE>
+__device__ __forceinline__ void liu_shen_tile(T* s_vx, T* s_vy, T* s_p, T* s_c, T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny,
+                                              long long base, T alpha, int vec_ok, int i0, int c0) {
+    using Cfg = LsCfg<T>;
+    constexpr int PITCH = Cfg::PITCH, RPT = Cfg::RPT;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // ---- update: lane = four adjacent columns, warp = RPT consecutive rows with a rolling three-row window
+    const int j = c0 + 4 * lane;
+    const int r0 = warp * RPT;
+    if (i0 + r0 >= Nx) return;                      // warp-uniform: the shuffles below need whole warps
     const T half = T(0.5), quarter = T(0.25), two = T(2);
-    for (int r = rg; r < TH; r += Cfg::THREADS / 32) {
-        const int i = i0 + r;
-        if (i >= Nx || j >= Ny) continue;
-        T ax[3][6], ay[3][6], ap[3][6], ac[6];
+    T wx[3][6], wy[3][6], wp[3][6], wc[3][6];
 #pragma unroll
-        for (int q = 0; q < 3; ++q) {
-            ld6_shared<T>(s_vx + (r + q) * PITCH, body, ax[q]);
-            ld6_shared<T>(s_vy + (r + q) * PITCH, body, ay[q]);
-            ld6_shared<T>(s_p + (r + q) * PITCH, body, ap[q]);
-        }
-        ld6_shared<T>(s_c + (r + 1) * PITCH, body, ac);
-        const Vec4<T> cu = ld4_global<T>(s_c + r * PITCH + body), cd = ld4_global<T>(s_c + (r + 2) * PITCH + body);
+    for (int q = 0; q < 2; ++q) {
+        ld6_shared<T>(s_vx + (r0 + q) * PITCH, lane, wx[q]);
+        ld6_shared<T>(s_vy + (r0 + q) * PITCH, lane, wy[q]);
+        ld6_shared<T>(s_p + (r0 + q) * PITCH, lane, wp[q]);
+        ld6_shared<T>(s_c + (r0 + q) * PITCH, lane, wc[q]);
+    }
+#pragma unroll
+    for (int t = 0; t < RPT; ++t) {
+        const int u = t % 3, m = (t + 1) % 3, d = (t + 2) % 3;          // window slots of rows i-1, i, i+1
+        ld6_shared<T>(s_vx + (r0 + t + 2) * PITCH, lane, wx[d]);
+        ld6_shared<T>(s_vy + (r0 + t + 2) * PITCH, lane, wy[d]);
+        ld6_shared<T>(s_p + (r0 + t + 2) * PITCH, lane, wp[d]);
+        ld6_shared<T>(s_c + (r0 + t + 2) * PITCH, lane, wc[d]);
+        const int i = i0 + r0 + t;
+        if (EDGE && (i >= Nx || j >= Ny)) continue;
         // the 8-neighbour sum takes zeros outside the frame (:522-538) where the derivative terms take the mirror
-        const T m_up = i > 0 ? T(1) : T(0), m_dn = i < Nx - 1 ? T(1) : T(0);
-        const bool edge_i = (i == 0) || (i == Nx - 1);
+        const T m_up = (EDGE && i == 0) ? T(0) : T(1), m_dn = (EDGE && i == Nx - 1) ? T(0) : T(1);
+        const bool edge_i = EDGE && ((i == 0) || (i == Nx - 1));
         T ox[4], oy[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
             const int c = k + 1, jj = j + k;
-            const T m_l = jj > 0 ? T(1) : T(0), m_r = jj < Ny - 1 ? T(1) : T(0);
-            const bool edge_j = (jj == 0) || (jj == Ny - 1);
-            // image terms (:564-595); index 0 = row i-1 ("x" is the row axis)
-            const T I = ap[1][c];
-            const T Ix = (ap[2][c] - ap[0][c]) * half;
-            const T Iy = (ap[1][c + 1] - ap[1][c - 1]) * half;
-            const T Ixt = (cd.v[k] - cu.v[k] - ap[2][c] + ap[0][c]) * half;
-            const T Iyt = (ac[c + 1] - ac[c - 1] - ap[1][c + 1] + ap[1][c - 1]) * half;
-            const T Ixx = ap[2][c] + ap[0][c] - two * I;
-            const T Iyy = ap[1][c + 1] + ap[1][c - 1] - two * I;
-            const T Ixy = (ap[2][c + 1] - ap[2][c - 1] - ap[0][c + 1] + ap[0][c - 1]) * quarter;
+            const T m_l = (EDGE && jj == 0) ? T(0) : T(1), m_r = (EDGE && jj == Ny - 1) ? T(0) : T(1);
+            const bool edge_j = EDGE && ((jj == 0) || (jj == Ny - 1));
+            // image terms (:564-595); slot u = row i-1 ("x" is the row axis)
+            const T I = wp[m][c];
+            const T Ix = (wp[d][c] - wp[u][c]) * half;
+            const T Iy = (wp[m][c + 1] - wp[m][c - 1]) * half;
+            const T Ixt = (wc[d][c] - wc[u][c] - wp[d][c] + wp[u][c]) * half;
+            const T Iyt = (wc[m][c + 1] - wc[m][c - 1] - wp[m][c + 1] + wp[m][c - 1]) * half;
+            const T Ixx = wp[d][c] + wp[u][c] - two * I;
+            const T Iyy = wp[m][c + 1] + wp[m][c - 1] - two * I;
+            const T Ixy = (wp[d][c + 1] - wp[d][c - 1] - wp[u][c + 1] + wp[u][c - 1]) * quarter;
             // velocity terms (:513-520, :598-605)
-            const T dxVx = (ax[2][c] - ax[0][c]) * half, dyVx = (ax[1][c + 1] - ax[1][c - 1]) * half;
-            const T dxyVx = (ax[2][c + 1] - ax[2][c - 1] - ax[0][c + 1] + ax[0][c - 1]) * quarter;
-            const T dxVy = (ay[2][c] - ay[0][c]) * half, dyVy = (ay[1][c + 1] - ay[1][c - 1]) * half;
-            const T dxyVy = (ay[2][c + 1] - ay[2][c - 1] - ay[0][c + 1] + ay[0][c - 1]) * quarter;
-            const T Vx_barx = ax[2][c] + ax[0][c];
-            const T Vy_bary = ay[1][c + 1] + ay[1][c - 1];
-            const T barx = m_up * (m_l * ax[0][c - 1] + ax[0][c] + m_r * ax[0][c + 1]) + m_l * ax[1][c - 1] + m_r * ax[1][c + 1]
-                         + m_dn * (m_l * ax[2][c - 1] + ax[2][c] + m_r * ax[2][c + 1]);
-            const T bary = m_up * (m_l * ay[0][c - 1] + ay[0][c] + m_r * ay[0][c + 1]) + m_l * ay[1][c - 1] + m_r * ay[1][c + 1]
-                         + m_dn * (m_l * ay[2][c - 1] + ay[2][c] + m_r * ay[2][c + 1]);
+            const T dxVx = (wx[d][c] - wx[u][c]) * half, dyVx = (wx[m][c + 1] - wx[m][c - 1]) * half;
+            const T dxyVx = (wx[d][c + 1] - wx[d][c - 1] - wx[u][c + 1] + wx[u][c - 1]) * quarter;
+            const T dxVy = (wy[d][c] - wy[u][c]) * half, dyVy = (wy[m][c + 1] - wy[m][c - 1]) * half;
+            const T dxyVy = (wy[d][c + 1] - wy[d][c - 1] - wy[u][c + 1] + wy[u][c - 1]) * quarter;
+            const T Vx_barx = wx[d][c] + wx[u][c];
+            const T Vy_bary = wy[m][c + 1] + wy[m][c - 1];
+            const T barx = m_up * (m_l * wx[u][c - 1] + wx[u][c] + m_r * wx[u][c + 1]) + m_l * wx[m][c - 1] + m_r * wx[m][c + 1]
+                         + m_dn * (m_l * wx[d][c - 1] + wx[d][c] + m_r * wx[d][c + 1]);
+            const T bary = m_up * (m_l * wy[u][c - 1] + wy[u][c] + m_r * wy[u][c + 1]) + m_l * wy[m][c - 1] + m_r * wy[m][c + 1]
+                         + m_dn * (m_l * wy[d][c - 1] + wy[d][c] + m_r * wy[d][c + 1]);
             // right-hand side (:636-646) and 2x2 matrix (:631-639)
             const T I2 = I * I;
             const T F0 = -I * Ixt - I * (two * Ix * dxVx + Iy * dxVy + Ix * dyVy) - I2 * (Vx_barx + dxyVy) - alpha * barx;
@@ -162,13 +222,13 @@ k_liu_shen_step(const T* __restrict__ P, const T* __restrict__ C, const T* __res
             const T a00 = I * Ixx - two * I2 - pref * alpha;
             const T a01 = I * Ixy;
             const T a11 = I * Iyy - two * I2 - pref * alpha;
-            const T inv_det = T(1) / (a00 * a11 - a01 * a01);
+            const T inv_det = ls_rcp(a00 * a11 - a01 * a01);
             ox[k] = (a11 * F0 - a01 * F1) * inv_det;
             oy[k] = (a00 * F1 - a01 * F0) * inv_det;
         }
         T* px = vx_out + base + (long long)i * Ny + j;
         T* py = vy_out + base + (long long)i * Ny + j;
-        if (vec_ok && j + 3 < Ny) {
+        if (!EDGE || (vec_ok && j + 3 < Ny)) {
             st4<T>(px, ox);
             st4<T>(py, oy);
         } else {
