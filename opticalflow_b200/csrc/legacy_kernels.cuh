@@ -7,7 +7,9 @@
 //   k_subtract_background                                                      (:195-198)
 // All of it is HBM-bound element / byte work; nothing here is a contraction.
 #pragma once
+#include <type_traits>
 #include "common.cuh"
+#include "pipeline.cuh"
 
 namespace ofb {
 
@@ -97,9 +99,53 @@ __device__ __forceinline__ double ls_rcp(double d) {
     return fma(r, fma(-d, r, 1.0), r);
 }
 
-template <typename T, bool EDGE>
-__device__ __forceinline__ void liu_shen_tile(T* s_vx, T* s_vy, T* s_p, T* s_c, T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny,
-                                              long long base, T alpha, int vec_ok, int i0, int c0);
+// One row of the Jacobi update for the lane's four pixels.  xu/xm/xd = rows i-1, i, i+1 of v_x (six columns: one halo
+// each side), likewise v_y, P and C.  The derivative terms see the mirrored ghost values held in the windows; the
+// 8-neighbour sums see zeros outside the frame (:522-538) through the masks m_up/m_dn (row) and ml/mr (per column);
+// pa[k] = alpha * boundary_prefactor (8 inside, 5 on an edge, 3 in a corner, :619-629).
+template <typename T>
+__device__ __forceinline__ void ls_row_update(const T (&xu)[6], const T (&xm)[6], const T (&xd)[6], const T (&yu)[6], const T (&ym)[6],
+                                              const T (&yd)[6], const T (&pu)[6], const T (&pm)[6], const T (&pd)[6], const T (&cu)[6],
+                                              const T (&cm)[6], const T (&cd)[6], T m_up, T m_dn, const T (&ml)[4], const T (&mr)[4],
+                                              const T (&pa)[4], T alpha, T (&ox)[4], T (&oy)[4]) {
+    // Differences are kept unscaled (d = 2 * central difference, cross = 4 * mixed difference) and the factors folded
+    // into the products; signs are folded into the final 2x2 solve (G = -F).
+    const T quarter = T(0.25), two = T(2);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int c = k + 1;
+        // image terms (:564-595); "x" is the row axis
+        const T I = pm[c];
+        const T dPx = pd[c] - pu[c], dPy = pm[c + 1] - pm[c - 1];                       // 2 Ix, 2 Iy
+        const T Ixt2 = (cd[c] - cu[c]) - dPx, Iyt2 = (cm[c + 1] - cm[c - 1]) - dPy;     // 2 dIdx_t, 2 dIdy_t
+        const T Ixx = fma(-two, I, pd[c] + pu[c]), Iyy = fma(-two, I, pm[c + 1] + pm[c - 1]);
+        const T Ixy4 = (pd[c + 1] - pd[c - 1]) - (pu[c + 1] - pu[c - 1]);
+        // velocity terms (:513-520, :598-605)
+        const T dVxx = xd[c] - xu[c], dVxy = xm[c + 1] - xm[c - 1];                     // 2 dVx/dx, 2 dVx/dy
+        const T dVyx = yd[c] - yu[c], dVyy = ym[c + 1] - ym[c - 1];
+        const T cVx = (xd[c + 1] - xd[c - 1]) - (xu[c + 1] - xu[c - 1]);                // 4 d2Vx/dxdy
+        const T cVy = (yd[c + 1] - yd[c - 1]) - (yu[c + 1] - yu[c - 1]);
+        const T Vx_barx = xd[c] + xu[c];
+        const T Vy_bary = ym[c + 1] + ym[c - 1];
+        const T barx = m_up * (ml[k] * xu[c - 1] + xu[c] + mr[k] * xu[c + 1]) + ml[k] * xm[c - 1] + mr[k] * xm[c + 1]
+                     + m_dn * (ml[k] * xd[c - 1] + xd[c] + mr[k] * xd[c + 1]);
+        const T bary = m_up * (ml[k] * yu[c - 1] + yu[c] + mr[k] * yu[c + 1]) + ml[k] * ym[c - 1] + mr[k] * ym[c + 1]
+                     + m_dn * (ml[k] * yd[c - 1] + yd[c] + mr[k] * yd[c + 1]);
+        // G = -F (:636-646):  I/4 (2 Ixt2 + 2 dPx dVxx + dPy dVyx + dPx dVyy) + I^2 (Vx_barx + cVy/4) + alpha barx
+        const T I2 = I * I, hI = I * quarter, I2q = I2 * quarter;
+        const T ex = fma(dPx, dVxx, Ixt2), ey = fma(dPy, dVyy, Iyt2);
+        const T sx = fma(dPy, dVyx, fma(dPx, dVyy, ex + ex));
+        const T sy = fma(dPx, dVxy, fma(dPy, dVxx, ey + ey));
+        const T G0 = fma(alpha, barx, fma(I2q, cVy, fma(I2, Vx_barx, hI * sx)));
+        const T G1 = fma(alpha, bary, fma(I2q, cVx, fma(I2, Vy_bary, hI * sy)));
+        // 2x2 matrix (:631-639) and its inverse applied to F = -G
+        const T diag = fma(two, I2, pa[k]);
+        const T a00 = fma(I, Ixx, -diag), a11 = fma(I, Iyy, -diag), a01 = hI * Ixy4;
+        const T inv_det = ls_rcp(fma(a00, a11, -(a01 * a01)));
+        ox[k] = fma(a01, G1, -(a11 * G0)) * inv_det;
+        oy[k] = fma(a01, G0, -(a00 * G1)) * inv_det;
+    }
+}
 
 template <typename T>
 __global__ void __launch_bounds__(LsCfg<T>::THREADS, LsCfg<T>::MIN_CTAS)
@@ -151,23 +197,11 @@ k_liu_shen_step(const T* __restrict__ P, const T* __restrict__ C, const T* __res
         cp_async_wait_all();
     }
     __syncthreads();
-    // tiles that touch the frame edge take the general path (zero-masked neighbour sums, 3/5/8 prefactor, ragged stores)
-    const bool edge = i0 == 0 || i0 + TH >= Nx || c0 == 0 || c0 + TW >= Ny || !vec_ok;
-    if (edge) liu_shen_tile<T, true>(s_vx, s_vy, s_p, s_c, vx_out, vy_out, Nx, Ny, base, alpha, vec_ok, i0, c0);
-    else liu_shen_tile<T, false>(s_vx, s_vy, s_p, s_c, vx_out, vy_out, Nx, Ny, base, alpha, vec_ok, i0, c0);
-}
-
-template <typename T, bool EDGE>
-__device__ __forceinline__ void liu_shen_tile(T* s_vx, T* s_vy, T* s_p, T* s_c, T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny,
-                                              long long base, T alpha, int vec_ok, int i0, int c0) {
-    using Cfg = LsCfg<T>;
-    constexpr int PITCH = Cfg::PITCH, RPT = Cfg::RPT;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     // ---- update: lane = four adjacent columns, warp = RPT consecutive rows with a rolling three-row window
+    constexpr int RPT = Cfg::RPT;
     const int j = c0 + 4 * lane;
     const int r0 = warp * RPT;
     if (i0 + r0 >= Nx) return;                      // warp-uniform: the shuffles below need whole warps
-    const T half = T(0.5), quarter = T(0.25), two = T(2);
     T wx[3][6], wy[3][6], wp[3][6], wc[3][6];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
@@ -175,6 +209,14 @@ __device__ __forceinline__ void liu_shen_tile(T* s_vx, T* s_vy, T* s_p, T* s_c, 
         ld6_shared<T>(s_vy + (r0 + q) * PITCH, lane, wy[q]);
         ld6_shared<T>(s_p + (r0 + q) * PITCH, lane, wp[q]);
         ld6_shared<T>(s_c + (r0 + q) * PITCH, lane, wc[q]);
+    }
+    T ml[4], mr[4];
+    bool edge_j[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        ml[k] = (j + k == 0) ? T(0) : T(1);
+        mr[k] = (j + k == Ny - 1) ? T(0) : T(1);
+        edge_j[k] = (j + k == 0) || (j + k == Ny - 1);
     }
 #pragma unroll
     for (int t = 0; t < RPT; ++t) {
@@ -184,57 +226,152 @@ __device__ __forceinline__ void liu_shen_tile(T* s_vx, T* s_vy, T* s_p, T* s_c, 
         ld6_shared<T>(s_p + (r0 + t + 2) * PITCH, lane, wp[d]);
         ld6_shared<T>(s_c + (r0 + t + 2) * PITCH, lane, wc[d]);
         const int i = i0 + r0 + t;
-        if (EDGE && (i >= Nx || j >= Ny)) continue;
-        // the 8-neighbour sum takes zeros outside the frame (:522-538) where the derivative terms take the mirror
-        const T m_up = (EDGE && i == 0) ? T(0) : T(1), m_dn = (EDGE && i == Nx - 1) ? T(0) : T(1);
-        const bool edge_i = EDGE && ((i == 0) || (i == Nx - 1));
-        T ox[4], oy[4];
+        if (i >= Nx || j >= Ny) continue;
+        const bool edge_i = (i == 0) || (i == Nx - 1);
+        T pa[4], ox[4], oy[4];
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int c = k + 1, jj = j + k;
-            const T m_l = (EDGE && jj == 0) ? T(0) : T(1), m_r = (EDGE && jj == Ny - 1) ? T(0) : T(1);
-            const bool edge_j = EDGE && ((jj == 0) || (jj == Ny - 1));
-            // image terms (:564-595); slot u = row i-1 ("x" is the row axis)
-            const T I = wp[m][c];
-            const T Ix = (wp[d][c] - wp[u][c]) * half;
-            const T Iy = (wp[m][c + 1] - wp[m][c - 1]) * half;
-            const T Ixt = (wc[d][c] - wc[u][c] - wp[d][c] + wp[u][c]) * half;
-            const T Iyt = (wc[m][c + 1] - wc[m][c - 1] - wp[m][c + 1] + wp[m][c - 1]) * half;
-            const T Ixx = wp[d][c] + wp[u][c] - two * I;
-            const T Iyy = wp[m][c + 1] + wp[m][c - 1] - two * I;
-            const T Ixy = (wp[d][c + 1] - wp[d][c - 1] - wp[u][c + 1] + wp[u][c - 1]) * quarter;
-            // velocity terms (:513-520, :598-605)
-            const T dxVx = (wx[d][c] - wx[u][c]) * half, dyVx = (wx[m][c + 1] - wx[m][c - 1]) * half;
-            const T dxyVx = (wx[d][c + 1] - wx[d][c - 1] - wx[u][c + 1] + wx[u][c - 1]) * quarter;
-            const T dxVy = (wy[d][c] - wy[u][c]) * half, dyVy = (wy[m][c + 1] - wy[m][c - 1]) * half;
-            const T dxyVy = (wy[d][c + 1] - wy[d][c - 1] - wy[u][c + 1] + wy[u][c - 1]) * quarter;
-            const T Vx_barx = wx[d][c] + wx[u][c];
-            const T Vy_bary = wy[m][c + 1] + wy[m][c - 1];
-            const T barx = m_up * (m_l * wx[u][c - 1] + wx[u][c] + m_r * wx[u][c + 1]) + m_l * wx[m][c - 1] + m_r * wx[m][c + 1]
-                         + m_dn * (m_l * wx[d][c - 1] + wx[d][c] + m_r * wx[d][c + 1]);
-            const T bary = m_up * (m_l * wy[u][c - 1] + wy[u][c] + m_r * wy[u][c + 1]) + m_l * wy[m][c - 1] + m_r * wy[m][c + 1]
-                         + m_dn * (m_l * wy[d][c - 1] + wy[d][c] + m_r * wy[d][c + 1]);
-            // right-hand side (:636-646) and 2x2 matrix (:631-639)
-            const T I2 = I * I;
-            const T F0 = -I * Ixt - I * (two * Ix * dxVx + Iy * dxVy + Ix * dyVy) - I2 * (Vx_barx + dxyVy) - alpha * barx;
-            const T F1 = -I * Iyt - I * (two * Iy * dyVy + Ix * dyVx + Iy * dxVx) - I2 * (Vy_bary + dxyVx) - alpha * bary;
-            const T pref = (edge_i && edge_j) ? T(3) : ((edge_i || edge_j) ? T(5) : T(8));
-            const T a00 = I * Ixx - two * I2 - pref * alpha;
-            const T a01 = I * Ixy;
-            const T a11 = I * Iyy - two * I2 - pref * alpha;
-            const T inv_det = ls_rcp(a00 * a11 - a01 * a01);
-            ox[k] = (a11 * F0 - a01 * F1) * inv_det;
-            oy[k] = (a00 * F1 - a01 * F0) * inv_det;
-        }
+        for (int k = 0; k < 4; ++k) pa[k] = alpha * ((edge_i && edge_j[k]) ? T(3) : ((edge_i || edge_j[k]) ? T(5) : T(8)));
+        ls_row_update<T>(wx[u], wx[m], wx[d], wy[u], wy[m], wy[d], wp[u], wp[m], wp[d], wc[u], wc[m], wc[d], i == 0 ? T(0) : T(1),
+                         i == Nx - 1 ? T(0) : T(1), ml, mr, pa, alpha, ox, oy);
         T* px = vx_out + base + (long long)i * Ny + j;
         T* py = vy_out + base + (long long)i * Ny + j;
-        if (!EDGE || (vec_ok && j + 3 < Ny)) {
+        if (vec_ok && j + 3 < Ny) {
             st4<T>(px, ox);
             st4<T>(py, oy);
         } else {
 #pragma unroll
             for (int k = 0; k < 4; ++k)
                 if (j + k < Ny) { px[k] = ox[k]; py[k] = oy[k]; }
+        }
+    }
+}
+
+// -----------------------------------------------------------------------------------------------------
+// Streamed Liu-Shen sweep (frames whose rows are 16-byte multiples): the tile kernel above alternates a load phase
+// and a long straight-line compute phase (instruction-fetch bound, 0.6 of the HBM peak).  Here a producer warp streams
+// one row of vx, vy, P and C per stage global -> shared with bulk copies (TMA unit) into a ring, four consumer warps
+// march down the rows with the same rolling register window in a three-row loop body, CTAs are persistent and every
+// CTA gets the same number of rows of the (pair, column tile) columns laid end to end.  Ghost rows are the producer
+// reading the mirrored source row, ghost columns a register patch in the lanes that own column 0 / Ny-1.
+// -----------------------------------------------------------------------------------------------------
+template <typename T> struct LsStream {
+    static constexpr int CW = 4;                         // consumer warps
+    static constexpr int TW = CW * WARP * 4;             // columns per tile: 512
+    static constexpr int HALO = 16 / (int)sizeof(T);     // 16-byte column halo each side
+    static constexpr int ROW = TW + 2 * HALO;
+    static constexpr int STAGES = 4;
+    static constexpr int THREADS = (CW + 1) * WARP;
+    static constexpr int STAGE_ELEMS = 4 * ROW;
+    static constexpr size_t RING_BYTES = (size_t)STAGES * STAGE_ELEMS * sizeof(T);
+    static constexpr size_t SMEM = RING_BYTES + 2 * STAGES * sizeof(uint64_t);
+    static constexpr int MIN_CTAS = sizeof(T) == 4 ? 3 : 2;
+};
+
+// six columns of a staged row (rowp[j] = column j) around the lane's four: neighbours by shuffle, the two columns
+// beyond the warp's span as broadcast shared loads, mirror patch where the lane owns column 0 / Ny-1
+template <typename T>
+__device__ __forceinline__ void ls_load_window(const T* rowp, int cw0, int j0, int Ny, int lane, T (&a)[6]) {
+    const Vec4<T> m = ld4_global<T>(rowp + j0);
+    a[1] = m.v[0]; a[2] = m.v[1]; a[3] = m.v[2]; a[4] = m.v[3];
+    const T left = __shfl_up_sync(FULL, m.v[3], 1), right = __shfl_down_sync(FULL, m.v[0], 1);
+    const T hl = rowp[lane == 0 ? cw0 - 1 : cw0], hr = rowp[lane == 31 ? cw0 + 4 * WARP : cw0];
+    a[0] = lane == 0 ? hl : left;
+    a[5] = lane == 31 ? hr : right;
+    if (j0 == 0) a[0] = a[2];                    // column -1 -> column 1
+    if (j0 + 3 == Ny - 1) a[5] = a[3];           // column Ny -> column Ny-2
+}
+
+template <typename T>
+__global__ void __launch_bounds__(LsStream<T>::THREADS, LsStream<T>::MIN_CTAS)
+k_liu_shen_stream(const T* __restrict__ P, const T* __restrict__ C, const T* __restrict__ vx_in, const T* __restrict__ vy_in,
+                  T* __restrict__ vx_out, T* __restrict__ vy_out, int Nx, int Ny, long long plane, T alpha, int n_pairs, int tiles_x) {
+    using S = LsStream<T>;
+    constexpr int STAGES = S::STAGES;
+    extern __shared__ __align__(128) unsigned char lss_smem[];
+    T* ring = reinterpret_cast<T*>(lss_smem);
+    uint64_t* full = reinterpret_cast<uint64_t*>(lss_smem + S::RING_BYTES);
+    uint64_t* empty = full + STAGES;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int e = threadIdx.x; e < STAGES * S::STAGE_ELEMS; e += blockDim.x) ring[e] = T(0);
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full + s, 1); mbar_init(empty + s, S::CW); }
+        mbar_fence_init();
+    }
+    fence_proxy_async();
+    __syncthreads();
+
+    // this CTA's share of the rows of all (pair, tile) columns laid end to end
+    const long long total = (long long)n_pairs * tiles_x * Nx;
+    long long cur = (long long)blockIdx.x * total / gridDim.x;
+    const long long end = (long long)(blockIdx.x + 1) * total / gridDim.x;
+    uint32_t n = 0;                                      // running stage counter, continues across items
+
+    while (cur < end) {
+        const long long col = cur / Nx;
+        const int i_begin = (int)(cur - col * Nx);
+        const int pair = (int)(col / tiles_x), tile = (int)(col - (long long)pair * tiles_x);
+        const int i_end = (int)min((long long)Nx, (long long)i_begin + (end - cur));
+        cur += i_end - i_begin;
+        const int c0 = tile * S::TW;
+        const int nk = i_end - i_begin + 2;
+        const long long base = (long long)pair * plane;
+        if (warp == S::CW) {
+            // ---------------------------------------------------------------- producer: lane q streams plane q
+            const int lo = max(c0 - S::HALO, 0), hi = min(c0 + S::TW + S::HALO, Ny);
+            const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(T);
+            const T* src = lane == 0 ? vx_in : (lane == 1 ? vy_in : (lane == 2 ? P : C));
+            src += base + lo;
+            const int dst_off = lane * S::ROW + (lo - (c0 - S::HALO));
+            for (int k = 0; k < nk; ++k, ++n) {
+                const int s = n % STAGES;
+                mbar_wait_sleep(empty + s, ((n / STAGES) & 1u) ^ 1u, 128);
+                if (lane == 0) mbar_arrive_expect_tx(full + s, 4u * bytes);
+                __syncwarp();
+                if (lane < 4) bulk_g2s(ring + s * S::STAGE_ELEMS + dst_off, src + (long long)ls_mirror(i_begin - 1 + k, Nx) * Ny, bytes, full + s);
+            }
+        } else {
+            // ---------------------------------------------------------------- consumers
+            const int cw0 = c0 + warp * (4 * WARP);
+            const int j0 = cw0 + 4 * lane;
+            const bool has_cols = cw0 < Ny;
+            T wx[3][6], wy[3][6], wp[3][6], wc[3][6];
+            const T ml[4] = {j0 == 0 ? T(0) : T(1), T(1), T(1), T(1)};
+            const T mr[4] = {T(1), T(1), T(1), j0 + 3 == Ny - 1 ? T(0) : T(1)};
+            const bool edge_j0 = j0 == 0, edge_j3 = j0 + 3 == Ny - 1;
+
+            auto do_stage = [&](auto SLOT, int k) {
+                constexpr int sp = decltype(SLOT)::value, su = (sp + 1) % 3, sm = (sp + 2) % 3;     // rows i+1, i-1, i
+                const int s = n % STAGES;
+                const uint32_t ph = (n / STAGES) & 1u;
+                ++n;
+                mbar_wait_sleep(full + s, ph, 32);
+                if (has_cols) {
+                    const T* stg = ring + s * S::STAGE_ELEMS - (c0 - S::HALO);       // stg[q*ROW + j] = column j of plane q
+                    ls_load_window<T>(stg, cw0, j0, Ny, lane, wx[sp]);
+                    ls_load_window<T>(stg + S::ROW, cw0, j0, Ny, lane, wy[sp]);
+                    ls_load_window<T>(stg + 2 * S::ROW, cw0, j0, Ny, lane, wp[sp]);
+                    ls_load_window<T>(stg + 3 * S::ROW, cw0, j0, Ny, lane, wc[sp]);
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(empty + s);                               // the row now lives in registers
+                if (has_cols && k >= 2 && j0 < Ny) {
+                    const int i = i_begin + k - 2;
+                    const bool edge_i = (i == 0) || (i == Nx - 1);
+                    const T pa_in = alpha * (edge_i ? T(5) : T(8)), pa_edge = alpha * (edge_i ? T(3) : T(5));
+                    const T pa[4] = {edge_j0 ? pa_edge : pa_in, pa_in, pa_in, edge_j3 ? pa_edge : pa_in};
+                    T ox[4], oy[4];
+                    ls_row_update<T>(wx[su], wx[sm], wx[sp], wy[su], wy[sm], wy[sp], wp[su], wp[sm], wp[sp], wc[su], wc[sm], wc[sp],
+                                     i == 0 ? T(0) : T(1), i == Nx - 1 ? T(0) : T(1), ml, mr, pa, alpha, ox, oy);
+                    st4<T>(vx_out + base + (long long)i * Ny + j0, ox);
+                    st4<T>(vy_out + base + (long long)i * Ny + j0, oy);
+                }
+            };
+            int k = 0;
+            while (k < nk) {
+                do_stage(std::integral_constant<int, 0>{}, k); if (++k >= nk) break;
+                do_stage(std::integral_constant<int, 1>{}, k); if (++k >= nk) break;
+                do_stage(std::integral_constant<int, 2>{}, k); ++k;
+            }
         }
     }
 }

@@ -1,6 +1,7 @@
 // ofb200 - host side of the C ABI (include/ofb200.h): workspace planning, multigrid hierarchy set-up,
 // the BiCGStab driver loop and the launch wrappers.  Compiled for sm_100a only.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cstdarg>
 #include <vector>
@@ -1204,9 +1205,30 @@ int liu_shen_impl(const void* P, const void* C, void* vx, void* vy, void* speed,
     const int vec_ok = (Ny % 4 == 0 && ptr_aligned16(P) && ptr_aligned16(C) && ptr_aligned16(vx) && ptr_aligned16(vy) &&
                         ptr_aligned16(tmp_vx) && ptr_aligned16(tmp_vy)) ? 1 : 0;
     dim3 grid((Ny + Cfg::TW - 1) / Cfg::TW, (Nx + Cfg::TH - 1) / Cfg::TH, B);
+    // rows that are 16-byte multiples go through the streamed sweep (bulk copies into a ring, persistent CTAs)
+    using S = LsStream<T>;
+    auto skern = k_liu_shen_stream<T>;
+    const bool streamed = vec_ok && Ny >= 64 && !getenv("OFB_LIU_SHEN_TILED");
+    static int stream_ctas[MAX_DEVICES] = {0};
+    int sgrid = 0, tiles_x = 0;
+    if (streamed) {
+        if (stream_ctas[dev] == 0) {
+            OFB_CHECK_CUDA(cudaFuncSetAttribute(skern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)S::SMEM));
+            int nb = 0;
+            OFB_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, skern, S::THREADS, S::SMEM));
+            if (nb < 1) return fail(-9, "streamed Liu-Shen sweep does not fit on an SM");
+            stream_ctas[dev] = nb;
+        }
+        tiles_x = (Ny + S::TW - 1) / S::TW;
+        const long long rows = (long long)B * tiles_x * Nx;
+        sgrid = (int)std::min<long long>((long long)device_sms() * stream_ctas[dev], std::max<long long>(1, rows / 8));
+    }
     T *ax = (T*)vx, *ay = (T*)vy, *bx = (T*)tmp_vx, *by = (T*)tmp_vy;
     for (int it = 0; it < iterations; ++it) {
-        kern<<<grid, Cfg::THREADS, Cfg::SMEM, stream>>>((const T*)P, (const T*)C, ax, ay, bx, by, Nx, Ny, plane, (T)alpha, vec_ok);
+        if (streamed)
+            skern<<<sgrid, S::THREADS, S::SMEM, stream>>>((const T*)P, (const T*)C, ax, ay, bx, by, Nx, Ny, plane, (T)alpha, B, tiles_x);
+        else
+            kern<<<grid, Cfg::THREADS, Cfg::SMEM, stream>>>((const T*)P, (const T*)C, ax, ay, bx, by, Nx, Ny, plane, (T)alpha, vec_ok);
         OFB_CHECK_LAUNCH();
         std::swap(ax, bx);
         std::swap(ay, by);

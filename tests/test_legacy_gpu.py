@@ -69,6 +69,21 @@ def test_liu_shen_matches_oracle_on_ragged_shapes(cuda_device, shape, iterations
         assert relmax(g, w) < 1e-10
 
 
+@pytest.mark.parametrize('shape', [(64, 64), (70, 512), (33, 516), (200, 1028)])
+@pytest.mark.parametrize('dtype,tol', [('float64', 1e-10), ('float32', 2e-4)])
+def test_liu_shen_streamed_and_tiled_sweeps_agree_with_oracle(cuda_device, monkeypatch, shape, dtype, tol):
+    """Rows that are 16-byte multiples take the streamed sweep; OFB_LIU_SHEN_TILED forces the tile kernel on them."""
+    rng = np.random.default_rng(shape[1])
+    movie = texture(4, shape[0], shape[1], shape[0])
+    gx, gy = rng.standard_normal(shape) * 0.2, rng.standard_normal(shape) * 0.2
+    want = lo.liu_shen_optical_flow(movie, 1.0, 1.0, 800.0, 1.0, gx, gy, None, 5)
+    streamed = optical_flow.liu_shen_optical_flow_jit(movie, 1.0, 1.0, 800.0, 1.0, gx, gy, None, 5, dtype=dtype)
+    monkeypatch.setenv('OFB_LIU_SHEN_TILED', '1')
+    tiled = optical_flow.liu_shen_optical_flow_jit(movie, 1.0, 1.0, 800.0, 1.0, gx, gy, None, 5, dtype=dtype)
+    for q in range(3):
+        assert relmax(streamed[q], want[q]) < tol and relmax(tiled[q], want[q]) < tol
+
+
 def test_liu_shen_sweep_is_affine_at_full_size(cuda_device):
     """1024^2 (oracle-free): one sweep is v -> M v + c, so sweep(a) + sweep(b) - sweep(0) == sweep(a + b); float32 agrees."""
     rng = np.random.default_rng(3)
