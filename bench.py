@@ -118,14 +118,23 @@ class ClockSampler(threading.Thread):
         self.index, self.samples, self.stop_flag = index, [], threading.Event()
 
     def run(self):
-        while not self.stop_flag.is_set():
-            try:
-                out = subprocess.run(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q,
-                                      '--format=csv,noheader,nounits'], capture_output=True, text=True, timeout=5).stdout
-                self.samples.append([f.strip() for f in out.strip().split(',')])
-            except Exception:
-                pass
-            self.stop_flag.wait(0.1)
+        # ONE nvidia-smi process in loop mode (the profiling recipe's clocks line): spawning one per sample cost the
+        # host ~50 ms of CPU each and slowed the end-to-end leg it was sampling
+        try:
+            proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), '--query-gpu=' + self.Q, '--format=csv,noheader,nounits',
+                                     '-lms', '200'], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            return
+        self.stop_flag.wait()
+        time.sleep(0.25)                      # let the sample of the last interval arrive
+        proc.terminate()
+        try:
+            out, _ = proc.communicate(timeout=5)
+        except Exception:
+            proc.kill()
+            out = ''
+        for line in out.splitlines():
+            self.samples.append([f.strip() for f in line.strip().split(',')])
 
     def summary(self):
         sm = [float(s[0]) for s in self.samples if len(s) >= 7 and s[0].replace('.', '').isdigit()]

@@ -19,6 +19,7 @@ Differences from the reference that a caller can observe (all documented in DESI
 Keyword-only extras (defaults preserve reference behaviour): ``dtype``, ``rtol``, ``max_it``,
 ``preconditioner``, ``device``, ``batch_pairs``, ``verbose``.
 """
+import os
 import time
 
 import numpy as np
@@ -124,6 +125,26 @@ def _default_batch(Nx, Ny, itemsize, n_pairs):
     if B >= n_pairs and n_pairs * Nx * Ny >= (8 << 20):
         B = max((n_pairs + 1) // 2, -(-(4 << 20) // (Nx * Ny)))
     return B
+
+
+def _chunk_schedule(n_pairs, B, pixels, taper=True):
+    """Pair ranges [(k0, k1), ...] of the chunk pipeline: full chunks of B and, for movies of more than one chunk, a
+    tapered end - the last B..2B pairs go as halves of what is left (not below ~4 Mpixel per launch, which still fills the
+    machine).  Nothing overlaps the device->host copy and the widening of the final chunk, so that tail then costs a
+    quarter of a full chunk's."""
+    if not taper or n_pairs <= B:
+        return [(k, min(k + B, n_pairs)) for k in range(0, n_pairs, B)]
+    floor = max(1, -(-(4 << 20) // max(1, pixels)))
+    bounds, k = [], 0
+    while n_pairs - k > 2 * B:
+        bounds.append((k, k + B))
+        k += B
+    while n_pairs - k > 0:
+        rest = n_pairs - k
+        piece = min(B, rest if rest < 2 * floor else (rest + 1) // 2)
+        bounds.append((k, k + piece))
+        k += piece
+    return bounds
 
 
 PROBE_IT = 100
@@ -244,10 +265,10 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     timeline = []
     t_setup = time.time()
     try:
-        uploader.prefetch(source[0:min(B, n_pairs) + 1])
+        schedule = _chunk_schedule(n_pairs, B, Nx * Ny, taper=os.environ.get('OFB_TAPER', '1') != '0')
+        uploader.prefetch(source[schedule[0][0]:schedule[0][1] + 1])
         stats = []
-        for c, k0 in enumerate(range(0, n_pairs, B)):
-            k1 = min(k0 + B, n_pairs)
+        for c, (k0, k1) in enumerate(schedule):
             nb = k1 - k0
             slot = slots[c % 2]
             t_chunk = time.perf_counter()
@@ -255,8 +276,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                 slot['busy'].wait()                                            # worker has drained this slot's pinned planes
             frames = uploader.take(tdtype)                                     # nb+1 frames, uploaded during the previous solve
             t_take = time.perf_counter()
-            if k1 < n_pairs:
-                uploader.prefetch(source[k1:min(k1 + B, n_pairs) + 1])
+            if c + 1 < len(schedule):
+                uploader.prefetch(source[schedule[c + 1][0]:schedule[c + 1][1] + 1])
             if blur:
                 frames = engine.blur(frames, smoothing_sigma, out=slot['dev'][4, :nb + 1])     # :770-771
             P, C = frames[:-1], frames[1:]
@@ -332,7 +353,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info['batch_pairs'] = B
     info['timeline'] = timeline
     info['egress_log'] = list(worker.log)
-    info['h2d_bytes'] = int(sum(min(k0 + B, n_pairs) - k0 + 1 for k0 in range(0, n_pairs, B)) * source[0].nbytes)
+    info['h2d_bytes'] = int(sum(k1 - k0 + 1 for k0, k1 in schedule) * source[0].nbytes)
     info['d2h_bytes'] = int((4 * n_pairs + (T if blur else 0)) * Nx * Ny * itemsize)
     result['solver_info'] = info
     return result

@@ -86,3 +86,16 @@ def test_result_arena_recycles_only_dropped_arrays():
     assert small.base is None
     off = hostio.ResultArena(max_idle_bytes=0)
     assert off.alloc((4, 512, 512), np.float64).base is None
+
+
+def test_chunk_schedule_covers_every_pair_once_and_tapers_the_end():
+    from opticalflow_b200.optical_flow import _chunk_schedule
+    for n, B, px in [(128, 16, 1 << 20), (499, 16, 1 << 20), (99, 64, 512 * 512), (1, 16, 1 << 20), (16, 16, 1 << 20),
+                     (17, 16, 1 << 20), (40, 16, 64 * 64), (3, 2, 25), (5, 1, 25), (100, 7, 1 << 18)]:
+        for taper in (True, False):
+            sch = _chunk_schedule(n, B, px, taper=taper)
+            assert sch[0][0] == 0 and sch[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(sch, sch[1:])) and all(0 < k1 - k0 <= B for k0, k1 in sch)
+    assert [k1 - k0 for k0, k1 in _chunk_schedule(128, 16, 1 << 20)][-4:] == [16, 8, 4, 4]
+    assert _chunk_schedule(16, 16, 1 << 20) == [(0, 16)]                 # a single chunk is left alone
+    assert [k1 - k0 for k0, k1 in _chunk_schedule(40, 16, 64 * 64)] == [16, 16, 8]     # small frames: no launch below ~4 Mpixel
