@@ -18,6 +18,7 @@ FLAG_TILE_FASTEST = 16
 FLAG_PDL = 32
 FLAG_STRIP_ITEMS = 64
 FLAG_NO_HALF_STEP_EXIT = 128
+FLAG_SERIAL_SETUP = 256
 ABI_VERSION = 4
 
 # every symbol include/ofb200.h declares

@@ -7,6 +7,7 @@
 #include <vector>
 #include <algorithm>
 #include <atomic>
+#include <mutex>
 #include "../../include/ofb200.h"
 #include "misc_kernels.cuh"
 #include "stream_sweep.cuh"
@@ -353,8 +354,36 @@ int check_shape(int B, int Nx, int Ny, int dtype) {
 // =====================================================================================================
 namespace {
 
+// Side stream per device for work that is off a solve's critical path (the dense coarsest-level inverse, which is a
+// latency chain on 16 SMs: it runs beside the first fine-level sweeps instead of in front of them).  Shared by the
+// solves of a device; ordering between a solve and the side stream is by per-solve events.
+inline cudaStream_t side_stream() {
+    static cudaStream_t streams[MAX_DEVICES] = {nullptr};
+    static std::mutex mu;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+    std::lock_guard<std::mutex> lock(mu);
+    if (streams[dev] == nullptr && cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking) != cudaSuccess) streams[dev] = nullptr;
+    return streams[dev];
+}
+
 template <typename T> struct Solver {
     int B;
+    cudaEvent_t setup_done = nullptr;    // recorded on the side stream after the dense inverse; waited for before its first use
+    ~Solver() {
+        if (setup_done != nullptr) {
+            cudaStreamWaitEvent(stream, setup_done, 0);      // nothing of this solve may outlive the caller's workspace
+            cudaEventDestroy(setup_done);
+        }
+    }
+    int join_setup() {
+        if (setup_done == nullptr) return 0;
+        OFB_CHECK_CUDA(cudaStreamWaitEvent(stream, setup_done, 0));
+        cudaEventDestroy(setup_done);
+        setup_done = nullptr;
+        return 0;
+    }
     Plan plan;
     Workspace<T> w;
     Geom g[MAX_LEVELS];
@@ -532,15 +561,30 @@ template <typename T> struct Solver {
                     configured[dev] = true;
                 }
             }
-            kern<<<B, 1024, use_smem ? mbytes : 0, stream>>>(g[l], w.coef[l], alpha, beta, h2, w.dense_M, w.dense_Minv, w.dense_piv,
-                                                             use_smem);
+            cudaStream_t setup_stream = stream;
+            cudaStream_t side = (slab.on || (opt.flags & OFB_FLAG_SERIAL_SETUP)) ? nullptr : side_stream();
+            cudaEvent_t coef_ready = nullptr;
+            if (side != nullptr && cudaEventCreateWithFlags(&coef_ready, cudaEventDisableTiming) == cudaSuccess &&
+                cudaEventCreateWithFlags(&setup_done, cudaEventDisableTiming) == cudaSuccess) {
+                OFB_CHECK_CUDA(cudaEventRecord(coef_ready, stream));
+                OFB_CHECK_CUDA(cudaStreamWaitEvent(side, coef_ready, 0));
+                setup_stream = side;
+            } else {
+                setup_done = nullptr;
+                side = nullptr;
+            }
+            kern<<<B, 1024, use_smem ? mbytes : 0, setup_stream>>>(g[l], w.coef[l], alpha, beta, h2, w.dense_M, w.dense_Minv, w.dense_piv,
+                                                                   use_smem);
             OFB_CHECK_LAUNCH();
+            if (side != nullptr) OFB_CHECK_CUDA(cudaEventRecord(setup_done, side));
+            if (coef_ready != nullptr) cudaEventDestroy(coef_ready);
         }
         return 0;
     }
 
     // levels lc .. coarsest in one launch, one CTA per pair: w.lb[lc] -> w.xa[lc]
     int fused_tail(int lc) {
+        if (int rc = join_setup()) return rc;
         FusedArgs<T> A;
         memset(&A, 0, sizeof(A));
         A.nlev = plan.nlevels - lc;
@@ -607,6 +651,7 @@ template <typename T> struct Solver {
             ec = w.xa[lc];
         } else if (lc == plan.nlevels - 1) {
             if (plan.dense) {
+                if ((rc = join_setup())) return rc;
                 const int n = plan.dense_n;
                 k_coarse_solve<T><<<B, 128, n * sizeof(T), stream>>>(n, w.dense_Minv, w.lb[lc], w.xa[lc], g[lc].pair, active);
                 OFB_CHECK_LAUNCH();

@@ -9,7 +9,10 @@ fr=engine.blur(torch.from_numpy(movie).to(dev),2.5)
 P,C=fr[:-1].contiguous(),fr[1:].contiguous()
 b=engine.build_rhs(P,C)
 a=torch.full((B,),1e5,dtype=torch.float64,device=dev); be=torch.full((B,),1e4,dtype=torch.float64,device=dev)
-for name,flags in (('default',0),('no-half-step-exit',_lib.FLAG_NO_HALF_STEP_EXIT),('pdl',_lib.FLAG_PDL),('strips',_lib.FLAG_STRIP_ITEMS),('default',0),('pdl',_lib.FLAG_PDL),('strips',_lib.FLAG_STRIP_ITEMS),('strips+pdl',_lib.FLAG_STRIP_ITEMS|_lib.FLAG_PDL)):
+MODES = {'default': 0, 'no-half-step-exit': _lib.FLAG_NO_HALF_STEP_EXIT, 'pdl': _lib.FLAG_PDL, 'strips': _lib.FLAG_STRIP_ITEMS,
+         'serial-setup': _lib.FLAG_SERIAL_SETUP}
+names = sys.argv[1].split(',') if len(sys.argv) > 1 else ['default', 'serial-setup', 'default', 'serial-setup']
+for name,flags in [(n, MODES[n]) for n in names]:
     opt=engine.make_options('mg',flags=flags)
     ts=[]
     for r in range(6):
