@@ -182,10 +182,11 @@ int ofb_liu_shen(const void* P, const void* C, void* vx, void* vy, void* speed, 
 /* np.max over n elements (:328) -> *max_out (device double). */
 int ofb_movie_max(const void* in, long long n, int dtype, double* max_out, void* stream);
 
-/* apply_adaptive_threshold (optical_flow.py:308-338): uint8(movie/max*255) into tmp_u8 [F][Nx][Ny], then
+/* apply_adaptive_threshold (optical_flow.py:308-338): uint8(movie/max*255), then
  *     cv2.adaptiveThreshold(.., 1.0, ADAPTIVE_THRESH_MEAN_C, THRESH_BINARY, window, threshold):
  *     out = 1 where src > boxmean(window, replicated border) - idelta, idelta = ceil(threshold).
- *     window odd, 3..255.  movie_max: device double (ofb_movie_max). */
+ *     window odd, 3..255.  movie_max: device double (ofb_movie_max).  tmp_u8: scratch of 3*F*Nx*Ny bytes, 2-byte
+ *     aligned (16-bit row sums of the separable box filter, then the uint8 plane). */
 int ofb_adaptive_threshold(const void* in, const double* movie_max, unsigned char* tmp_u8, unsigned char* out,
                            int window, int idelta, int F, int Nx, int Ny, int dtype, void* stream);
 

@@ -2,7 +2,7 @@
 //   k_liu_shen_step     one Jacobi sweep of liu_shen_optical_flow_jit          (optical_flow.py:507-651)
 //   k_liu_shen_finish   its scaling / speed epilogue                           (:665-672)
 //   k_movie_max         np.max(movie)                                          (:328)
-//   k_to_u8_range / k_adaptive_threshold  uint8 conversion, cv2.adaptiveThreshold MEAN_C   (:328-333)
+//   k_threshold_rows / k_threshold_cols   uint8 conversion, cv2.adaptiveThreshold MEAN_C   (:328-333)
 //   k_clahe_hist / k_clahe_lut / k_clahe_interp   cv2 CLAHE on uint16 frames   (:362-370)
 //   k_subtract_background                                                      (:195-198)
 // All of it is HBM-bound element / byte work; nothing here is a contraction.
@@ -419,17 +419,11 @@ __global__ void __launch_bounds__(256) k_movie_max(const T* __restrict__ in, lon
 }
 
 // -----------------------------------------------------------------------------------------------------
-// Adaptive threshold (:328-333): uint8 conversion, k x k normalised box mean with replicated borders (integer
-// window sums, separable inside a shared-memory tile), dst = src > mean - ceil(threshold).  A CTA owns a 64 x 64
-// output tile and stages (64+2r)^2 converted bytes; the row sums never leave shared memory.
+// Adaptive threshold (:328-333): uint8 conversion, k x k normalised box mean with replicated borders, dst = src >
+// mean - ceil(threshold).  The box sum is separable and O(1) per pixel: a warp turns a row of bytes into its prefix
+// sums in shared memory and writes the k-wide window sums (16 bit: 255 * 255 < 65536); a thread per column then slides
+// the k-tall window down a strip of rows.  The byte and window-sum planes of a 16-frame batch stay in the L2.
 // -----------------------------------------------------------------------------------------------------
-constexpr int AT_TILE = 64;
-constexpr int AT_THREADS = 256;
-inline size_t adaptive_threshold_smem(int window) {
-    const size_t e = AT_TILE + 2 * (window / 2);
-    return ((e * e + 15) / 16) * 16 + e * AT_TILE * sizeof(unsigned short);
-}
-
 template <typename T>
 __device__ __forceinline__ unsigned char to_u8_range(T v, T mx) {
     // np.array(movie/np.max(movie)*255.0, dtype='uint8'): divide, multiply (in the movie's float type), truncate
@@ -437,57 +431,69 @@ __device__ __forceinline__ unsigned char to_u8_range(T v, T mx) {
     else return (unsigned char)(int)__dmul_rn(__ddiv_rn(v, mx), 255.0);
 }
 
-// np.array(movie/np.max(movie)*255.0, dtype='uint8') as its own pass, so that the k x k windows below re-read bytes
+// rows: u8 = uint8(movie / max * 255) (kept for the comparison), hs[i][j] = sum of u8[i][clamp(j-r .. j+r)]
+constexpr int AT_ROW_WARPS = 8;
 template <typename T>
-__global__ void k_to_u8_range(const T* __restrict__ in, const double* __restrict__ movie_max, unsigned char* __restrict__ out, long long n) {
+__global__ void __launch_bounds__(AT_ROW_WARPS * 32)
+k_threshold_rows(const T* __restrict__ in, const double* __restrict__ movie_max, unsigned char* __restrict__ u8,
+                 unsigned short* __restrict__ hs, long long n_rows, int Ny, int r, int warps) {
+    extern __shared__ __align__(16) unsigned char atr_smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (warp >= warps) return;
+    unsigned int* pre = reinterpret_cast<unsigned int*>(atr_smem) + (size_t)warp * (Ny + 1);     // pre[k] = sum of the first k bytes
     const T mx = (T)(*movie_max);
-    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x)
-        out[k] = to_u8_range<T>(in[k], mx);
+    for (long long row = (long long)blockIdx.x * warps + warp; row < n_rows; row += (long long)gridDim.x * warps) {
+        const T* src = in + row * Ny;
+        unsigned char* dst8 = u8 + row * Ny;
+        unsigned int carry = 0;
+        if (lane == 0) pre[0] = 0;
+        for (int j0 = 0; j0 < Ny; j0 += 32) {
+            const int j = j0 + lane;
+            unsigned int v = 0;
+            if (j < Ny) {
+                const unsigned char b = to_u8_range<T>(src[j], mx);
+                dst8[j] = b;
+                v = b;
+            }
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int u = __shfl_up_sync(FULL, v, o);
+                if (lane >= o) v += u;
+            }
+            if (j < Ny) pre[j + 1] = carry + v;
+            carry += __shfl_sync(FULL, v, 31);
+        }
+        __syncwarp();
+        const unsigned int first = pre[1], last = pre[Ny] - pre[Ny - 1];
+        unsigned short* dsth = hs + row * Ny;
+        for (int j = lane; j < Ny; j += 32) {
+            const int lo = j - r, hi = j + r;                          // window [lo, hi], clamped columns repeat the edge byte
+            unsigned int s = pre[min(hi, Ny - 1) + 1] - pre[max(lo, 0)];
+            s += (unsigned int)max(-lo, 0) * first + (unsigned int)max(hi - (Ny - 1), 0) * last;
+            dsth[j] = (unsigned short)s;
+        }
+        __syncwarp();
+    }
 }
 
-__global__ void __launch_bounds__(AT_THREADS)
-k_adaptive_threshold(const unsigned char* __restrict__ in, unsigned char* __restrict__ out, int Nx, int Ny, long long plane, int window,
-                     int idelta) {
-    extern __shared__ __align__(16) unsigned char at_smem[];
-    const int r = window / 2, e = AT_TILE + 2 * r;
-    unsigned char* tile = at_smem;                                                   // [e][e]
-    unsigned short* hs = reinterpret_cast<unsigned short*>(at_smem + (((size_t)e * e + 15) / 16) * 16);   // [e][AT_TILE]
-    const unsigned char* f = in + (long long)blockIdx.z * plane;
-    const int c0 = blockIdx.x * AT_TILE, i0 = blockIdx.y * AT_TILE;
-    for (int k = threadIdx.x; k < e * e; k += AT_THREADS) {
-        const int rr = k / e, cc = k - rr * e;
-        const int gi = min(max(i0 - r + rr, 0), Nx - 1), gj = min(max(c0 - r + cc, 0), Ny - 1);
-        tile[k] = f[(long long)gi * Ny + gj];
-    }
-    __syncthreads();
-    // horizontal window sums: thread per staged row (255 * 255 < 65536: the sums fit 16 bits)
-    for (int rr = threadIdx.x; rr < e; rr += AT_THREADS) {
-        const unsigned char* t = tile + (size_t)rr * e;
-        int s = 0;
-        for (int k = 0; k < window; ++k) s += t[k];
-        unsigned short* h = hs + (size_t)rr * AT_TILE;
-        h[0] = (unsigned short)s;
-        for (int c = 1; c < AT_TILE; ++c) {
-            s += (int)t[c + window - 1] - (int)t[c - 1];
-            h[c] = (unsigned short)s;
-        }
-    }
-    __syncthreads();
-    // vertical window sums: thread = column x quarter of the rows
-    const int col = threadIdx.x % AT_TILE, q = threadIdx.x / AT_TILE;
-    constexpr int ROWS = AT_TILE / (AT_THREADS / AT_TILE);
-    const int r0 = q * ROWS;
+// columns: slide the k-tall window of row sums down a strip of AT_STRIP rows; out = (src > mean - idelta) without the
+// division:  mean = round(s / k^2) < src + idelta  <=>  2 s + k^2 < (src + idelta) * 2 k^2  (k odd: no ties)
+constexpr int AT_STRIP = 64;
+__global__ void __launch_bounds__(128)
+k_threshold_cols(const unsigned char* __restrict__ u8, const unsigned short* __restrict__ hs, unsigned char* __restrict__ out, int Nx, int Ny,
+                 long long plane, int window, int idelta) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= Ny) return;
+    const int r = window >> 1, k2 = window * window;
+    const int i0 = blockIdx.y * AT_STRIP, i1 = min(i0 + AT_STRIP, Nx);
+    const long long base = (long long)blockIdx.z * plane + j;
+    const unsigned short* h = hs + base;
     int s = 0;
-    for (int k = 0; k < window; ++k) s += hs[(size_t)(r0 + k) * AT_TILE + col];
-    const int k2 = window * window;
-    for (int rr = r0; rr < r0 + ROWS; ++rr) {
-        if (rr > r0) s += (int)hs[(size_t)(rr + window - 1) * AT_TILE + col] - (int)hs[(size_t)(rr - 1) * AT_TILE + col];
-        const int i = i0 + rr, j = c0 + col;
-        if (i < Nx && j < Ny) {
-            const int mean = (2 * s + k2) / (2 * k2);          // round to nearest; k odd => no ties
-            const int v = tile[(size_t)(rr + r) * e + col + r];
-            out[(long long)blockIdx.z * plane + (long long)i * Ny + j] = (v - mean > -idelta) ? 1 : 0;
-        }
+    for (int a = i0 - r; a <= i0 + r; ++a) s += h[(long long)min(max(a, 0), Nx - 1) * Ny];
+    for (int i = i0; i < i1; ++i) {
+        if (i > i0) s += (int)h[(long long)min(i + r, Nx - 1) * Ny] - (int)h[(long long)max(i - 1 - r, 0) * Ny];
+        const int t = min(max((int)u8[base + (long long)i * Ny] + idelta, 0), 256);
+        out[base + (long long)i * Ny] = (2 * s + k2 < t * 2 * k2) ? 1 : 0;
     }
 }
 
@@ -519,67 +525,77 @@ __global__ void __launch_bounds__(256) k_clahe_hist(const T* __restrict__ in, in
     atomicAdd(h + (long long)((i / g.th) * g.tiles_x + j / g.tw) * CLAHE_BINS + v, 1);
 }
 
-// One CTA per (tile, frame): clip, redistribute, running sum, scale -> 16-bit look-up table.
+// One CTA per (tile, frame): clip, redistribute, running sum, scale -> 16-bit look-up table.  Warp w owns the bins
+// [2048 w, 2048 (w+1)) and reads them as 16-byte vectors.  Pass 1 sums min(h, clip) and the clipped excess per warp; the
+// redistribution (clahe.cpp: +clipped/65536 everywhere, +1 on every `step`-th bin while the remainder lasts) is a closed
+// form of the bin index, so the running sum at the start of a warp's segment follows from the per-warp sums alone and
+// pass 2 (which re-reads the tile's 256 KB from the L2) is a warp scan per 128 bins with no block barrier.
+__device__ __forceinline__ int clahe_extra(int b, int residual, int step, unsigned magic) {
+    // 1 if bin b receives one of the `residual` leftover counts: b = q * step with q < residual
+    if (residual == 0) return 0;
+    if (step == 1) return b < residual ? 1 : 0;
+    unsigned q = __umulhi((unsigned)b, magic);          // b / step for b < 65536 (magic = ceil(2^32 / step)), fixed up below
+    if (q * (unsigned)step > (unsigned)b) --q;
+    return (q * (unsigned)step == (unsigned)b && (int)q < residual) ? 1 : 0;
+}
+
 __global__ void __launch_bounds__(1024) k_clahe_lut(const int* __restrict__ hist, unsigned short* __restrict__ lut, ClaheGeom g) {
-    __shared__ int warp_sum[32];
-    __shared__ int carry_s, clipped_s;
+    __shared__ int s_min[32], s_clip[32];
     const long long t = (long long)blockIdx.y * gridDim.x + blockIdx.x;
-    const int* h = hist + t * CLAHE_BINS;
-    unsigned short* l = lut + t * CLAHE_BINS;
+    const int4* h4 = reinterpret_cast<const int4*>(hist + t * CLAHE_BINS);
+    uint2* l4 = reinterpret_cast<uint2*>(lut + t * CLAHE_BINS);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int batch = 0, residual = 0, step = 1;
-    if (g.clip > 0) {
-        int c = 0;
-        for (int b = threadIdx.x; b < CLAHE_BINS; b += 1024) c += max(h[b] - g.clip, 0);
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(FULL, c, o);
-        if (lane == 0) warp_sum[warp] = c;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            int tot = 0;
-            for (int w = 0; w < 32; ++w) tot += warp_sum[w];
-            clipped_s = tot;
-        }
-        __syncthreads();
-        const int clipped = clipped_s;
-        batch = clipped / CLAHE_BINS;
-        residual = clipped - batch * CLAHE_BINS;
-        step = residual != 0 ? max(CLAHE_BINS / residual, 1) : 1;
+    constexpr int SEG = CLAHE_BINS / 32;                 // bins per warp
+    const int seg = warp * SEG;
+    const int clip = g.clip > 0 ? g.clip : 0x7fffffff;
+    int sum_min = 0, sum_clip = 0;
+#pragma unroll 4
+    for (int tt = 0; tt < SEG / 128; ++tt) {
+        const int4 v = h4[(seg >> 2) + tt * 32 + lane];
+        const int m0 = min(v.x, clip), m1 = min(v.y, clip), m2 = min(v.z, clip), m3 = min(v.w, clip);
+        sum_min += (m0 + m1) + (m2 + m3);
+        sum_clip += ((v.x - m0) + (v.y - m1)) + ((v.z - m2) + (v.w - m3));
     }
-    if (threadIdx.x == 0) carry_s = 0;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sum_min += __shfl_xor_sync(FULL, sum_min, o);
+        sum_clip += __shfl_xor_sync(FULL, sum_clip, o);
+    }
+    if (lane == 0) { s_min[warp] = sum_min; s_clip[warp] = sum_clip; }
     __syncthreads();
-    for (int chunk = 0; chunk < CLAHE_BINS; chunk += 1024) {
-        const int b = chunk + threadIdx.x;
-        int v = h[b];
-        if (g.clip > 0) {
-            v = min(v, g.clip) + batch;
-            if (residual != 0 && b % step == 0 && b / step < residual) v += 1;
-        }
-        int s = v;                                           // inclusive scan over the 1024 bins of the chunk
+    int clipped = 0, before = 0;                         // before = sum of min(h, clip) over the bins below this warp's segment
+    for (int w = 0; w < 32; ++w) {
+        clipped += s_clip[w];
+        before += w < warp ? s_min[w] : 0;
+    }
+    const int batch = clipped / CLAHE_BINS;
+    const int residual = clipped - batch * CLAHE_BINS;
+    const int step = residual != 0 ? max(CLAHE_BINS / residual, 1) : 1;
+    const unsigned magic = step > 1 ? (unsigned)(((1ull << 32) + (unsigned)step - 1) / (unsigned)step) : 0u;
+    // leftover counts handed to bins below `seg`: multiples of step in [0, seg), at most `residual` of them
+    const int extra_before = residual != 0 ? min((seg + step - 1) / step, residual) : 0;
+    int carry = before + batch * seg + extra_before;
+#pragma unroll 2
+    for (int tt = 0; tt < SEG / 128; ++tt) {
+        const int idx = (seg >> 2) + tt * 32 + lane;
+        const int4 v = h4[idx];
+        const int b = idx * 4;
+        const int p0 = min(v.x, clip) + batch + clahe_extra(b, residual, step, magic);
+        const int p1 = p0 + min(v.y, clip) + batch + clahe_extra(b + 1, residual, step, magic);
+        const int p2 = p1 + min(v.z, clip) + batch + clahe_extra(b + 2, residual, step, magic);
+        const int p3 = p2 + min(v.w, clip) + batch + clahe_extra(b + 3, residual, step, magic);
+        int incl = p3;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
-            const int u = __shfl_up_sync(FULL, s, o);
-            if (lane >= o) s += u;
+            const int u = __shfl_up_sync(FULL, incl, o);
+            if (lane >= o) incl += u;
         }
-        if (lane == 31) warp_sum[warp] = s;
-        __syncthreads();
-        if (warp == 0) {
-            int w = warp_sum[lane];
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const int u = __shfl_up_sync(FULL, w, o);
-                if (lane >= o) w += u;
-            }
-            warp_sum[lane] = w;
-        }
-        __syncthreads();
-        const int sum = carry_s + (warp > 0 ? warp_sum[warp - 1] : 0) + s;
+        const int base = carry + incl - p3;
         // lut[i] = saturate_cast<ushort>(sum * lutScale): float product, round half to even
-        const int q = __float2int_rn(__fmul_rn(__int2float_rn(sum), g.lut_scale));
-        l[b] = (unsigned short)min(max(q, 0), 65535);
-        __syncthreads();
-        if (threadIdx.x == 1023) carry_s = sum;
-        __syncthreads();
+        auto q = [&](int sum) { return (unsigned)min(max(__float2int_rn(__fmul_rn(__int2float_rn(sum), g.lut_scale)), 0), 65535); };
+        const unsigned q0 = q(base + p0), q1 = q(base + p1), q2 = q(base + p2), q3 = q(base + p3);
+        l4[idx] = make_uint2(q0 | (q1 << 16), q2 | (q3 << 16));
+        carry += __shfl_sync(FULL, incl, 31);
     }
 }
 

@@ -1300,18 +1300,25 @@ int movie_max_impl(const void* in, long long n, double* out, cudaStream_t stream
 template <typename T>
 int adaptive_threshold_impl(const void* in, const double* movie_max, unsigned char* tmp, unsigned char* out, int window, int idelta,
                             int F, int Nx, int Ny, cudaStream_t stream) {
-    const long long plane = (long long)Nx * Ny, n = plane * F;
-    k_to_u8_range<T><<<stream_grid(n, 256 * 4), 256, 0, stream>>>((const T*)in, movie_max, tmp, n);
-    OFB_CHECK_LAUNCH();
-    auto kern = k_adaptive_threshold;
+    const long long plane = (long long)Nx * Ny, n = plane * F, n_rows = (long long)F * Nx;
+    unsigned short* hs = reinterpret_cast<unsigned short*>(tmp);          // scratch: 16-bit row sums, then the byte plane
+    unsigned char* u8 = tmp + 2 * n;
+    auto kern = k_threshold_rows<T>;
+    const size_t per_warp = (size_t)(Ny + 1) * sizeof(unsigned int);
+    const int warps = (int)std::max<size_t>(1, std::min<size_t>(AT_ROW_WARPS, (96 * 1024) / per_warp));
+    const size_t smem = per_warp * warps;
+    if (smem > 200 * 1024) return fail(-6, "ofb_adaptive_threshold: rows of %d columns do not fit the prefix-sum buffer", Ny);
     static bool configured[MAX_DEVICES] = {false};
     const int dev = device_slot();
     if (!configured[dev]) {
-        OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)adaptive_threshold_smem(255)));
+        OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         configured[dev] = true;
     }
-    dim3 grid((Ny + AT_TILE - 1) / AT_TILE, (Nx + AT_TILE - 1) / AT_TILE, F);
-    kern<<<grid, AT_THREADS, adaptive_threshold_smem(window), stream>>>(tmp, out, Nx, Ny, plane, window, idelta);
+    const int grid = (int)std::min<long long>((n_rows + warps - 1) / warps, (long long)device_sms() * 8);
+    kern<<<grid, AT_ROW_WARPS * 32, smem, stream>>>((const T*)in, movie_max, u8, hs, n_rows, Ny, window / 2, warps);
+    OFB_CHECK_LAUNCH();
+    dim3 cgrid((Ny + 127) / 128, (Nx + AT_STRIP - 1) / AT_STRIP, F);
+    k_threshold_cols<<<cgrid, 128, 0, stream>>>(u8, hs, out, Nx, Ny, plane, window, idelta);
     OFB_CHECK_LAUNCH();
     return 0;
 }

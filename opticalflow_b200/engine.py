@@ -225,8 +225,8 @@ def adaptive_threshold(frames, window_size, threshold):
     frames = frames.contiguous()
     F, Nx, Ny = frames.shape
     mx = movie_max(frames)
-    tmp = torch.empty((F, Nx, Ny), dtype=torch.uint8, device=frames.device)
-    out = torch.empty_like(tmp)
+    tmp = torch.empty((3, F, Nx, Ny), dtype=torch.uint8, device=frames.device)      # 16-bit row sums + the uint8 plane
+    out = torch.empty((F, Nx, Ny), dtype=torch.uint8, device=frames.device)
     _lib.check(_lib.load().ofb_adaptive_threshold(_ptr(frames), _ptr(mx), _ptr(tmp), _ptr(out), int(window_size),
                                                   int(np.ceil(threshold)), F, Nx, Ny, _code(frames), _stream_ptr(frames.device)))
     return out.view(torch.bool)
