@@ -11,7 +11,8 @@
  *   - every data pointer is a DEVICE pointer owned by the caller (e.g. torch.Tensor.data_ptr());
  *     the library never allocates or frees device memory and keeps no global mutable state;
  *   - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are asynchronous on it,
- *     except ofb_solve, which synchronises the stream every `check_every` iterations to test convergence;
+ *     except ofb_solve, which synchronises the stream every `check_every` iterations to test convergence (the counter
+ *     travels through mapped pinned memory, not the copy engine);
  *   - `dtype`: OFB_F32 or OFB_F64 - the arithmetic and storage type of all image/vector arguments;
  *   - B = number of frame pairs in the batch.  Images are [B][Nx][Ny] row-major; vectors are three SoA
  *     planes [B][3][Nx][Ny] in the order ux, uy, remodelling (the reference's interleaved numbering
@@ -66,6 +67,10 @@ const char* ofb_last_error(void);
 void        ofb_default_options(ofb_solve_options* opt);
 /* number of CUDA kernels this library has launched in the calling process (diagnostics, bench.py) */
 long long   ofb_launch_count(void);
+
+/* number of pairs the calling thread's last ofb_solve / ofb_solve_slab left unconverged (-1: unknown); lets a caller
+ * skip its fallback logic without reading converged_out back from the device */
+int         ofb_last_unconverged(void);
 
 /* Bytes of device workspace ofb_solve needs for this shape (caller allocates, contents need not be zeroed). */
 size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond);

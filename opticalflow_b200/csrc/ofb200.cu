@@ -368,6 +368,25 @@ inline cudaStream_t side_stream() {
     return streams[dev];
 }
 
+// Mapped pinned words through which the solve loop reads its counters (k_publish): per host thread and device.
+struct PollBox { int* host = nullptr; int* dev = nullptr; };
+inline PollBox* poll_box() {
+    thread_local PollBox boxes[MAX_DEVICES];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+    PollBox& b = boxes[dev];
+    if (b.host == nullptr) {
+        void *h = nullptr, *d = nullptr;
+        if (cudaHostAlloc(&h, 64, cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        if (cudaHostGetDevicePointer(&d, h, 0) != cudaSuccess) { cudaGetLastError(); cudaFreeHost(h); return nullptr; }
+        b.host = (int*)h;
+        b.dev = (int*)d;
+    }
+    return &b;
+}
+thread_local int g_last_unconverged = -1;
+
 template <typename T> struct Solver {
     int B;
     cudaEvent_t setup_done = nullptr;    // recorded on the side stream after the dense inverse; waited for before its first use
@@ -799,6 +818,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     T* sh_first = S.first_buffer(w.sh);
     const T wj = T(S.first_sweep_weight());
     int host_active = B;
+    PollBox* box = poll_box();
     for (int it = 0; it < max_it; ++it) {
         T *ph = nullptr, *sh = nullptr;
         {   // p = r + beta_k (p - omega v) ; z = w D^-1 p
@@ -836,8 +856,15 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         if ((rc = S.allreduce_acc())) return rc;
         OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : (int*)nullptr);
         if (poll) {
-            OFB_CHECK_CUDA(cudaMemcpyAsync(&host_active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
-            OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+            if (box != nullptr) {
+                k_publish<<<1, 1, 0, stream>>>(w.n_active, box->dev);
+                OFB_CHECK_LAUNCH();
+                OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+                host_active = *(volatile int*)box->host;
+            } else {
+                OFB_CHECK_CUDA(cudaMemcpyAsync(&host_active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
+                OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+            }
             if (host_active == 0) break;
         }
     }
@@ -847,8 +874,17 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         OFB_CHECK_LAUNCH();
         if ((rc = S.exchange_vec(0, x))) return rc;
     }
-    k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out);
+    // the number of pairs that did not converge goes to the host the same way (ofb_last_unconverged)
+    OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active + 1, 0, sizeof(int), stream));
+    k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out, w.n_active + 1);
     OFB_CHECK_LAUNCH();
+    g_last_unconverged = -1;
+    if (box != nullptr) {
+        k_publish<<<1, 1, 0, stream>>>(w.n_active + 1, box->dev + 1);
+        OFB_CHECK_LAUNCH();
+        OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+        g_last_unconverged = *(volatile int*)(box->host + 1);
+    }
     if (S.slab.on && S.slab.comm->box.ok) {
         int err = 0;
         OFB_CHECK_CUDA(cudaMemcpyAsync(&err, S.slab.comm->box.local + 4 * sizeof(unsigned long long), sizeof(int),
@@ -996,6 +1032,8 @@ int ofb_version(void) { return OFB_ABI_VERSION; }
 const char* ofb_last_error(void) { return g_error; }
 
 long long ofb_launch_count(void) { return g_launches.load(); }
+
+int ofb_last_unconverged(void) { return g_last_unconverged; }
 
 void ofb_default_options(ofb_solve_options* opt) {
     if (!opt) return;

@@ -46,6 +46,22 @@ def gaussian_weights(sigma, truncate=4.0):
     return w / w.sum(), radius
 
 
+_weight_cache = {}
+
+
+def _device_weights(sigma, device):
+    """Gaussian taps on the device, uploaded once per (sigma, device): a pageable host->device copy per call would wait
+    on the copy engine behind the frame prefetch of the next chunk."""
+    key = (float(sigma), str(device))
+    hit = _weight_cache.get(key)
+    if hit is None:
+        w, radius = gaussian_weights(sigma)
+        if len(_weight_cache) > 64:
+            _weight_cache.clear()
+        hit = _weight_cache[key] = (torch.from_numpy(w).to(device), radius)
+    return hit
+
+
 def _code(t):
     return _lib.OFB_F32 if t.dtype == torch.float32 else _lib.OFB_F64
 
@@ -55,8 +71,7 @@ def blur(frames, sigma, out=None):
     _require_cuda(frames)
     frames = frames.contiguous()
     F, Nx, Ny = frames.shape
-    w, radius = gaussian_weights(sigma)
-    wd = torch.from_numpy(w).to(frames.device)
+    wd, radius = _device_weights(sigma, frames.device)
     out = torch.empty_like(frames) if out is None else out
     tmp = torch.empty_like(frames)
     _lib.check(_lib.load().ofb_blur(_ptr(frames), _ptr(out), _ptr(tmp), _ptr(wd), radius, F, Nx, Ny, _code(frames),
@@ -161,6 +176,11 @@ def solve(P, b, x, speed_alpha, remodelling_alpha, rtol=1e-6, max_it=1000, optio
                                      ctypes.byref(options), _ptr(ws), nbytes, _ptr(iters), _ptr(relres), _ptr(conv),
                                      B, Nx, Ny, _code(P), _stream_ptr(P.device)))
     return iters, relres, conv
+
+
+def last_unconverged():
+    """Pairs the calling thread's last ``solve`` left unconverged (-1 if unknown): a host integer, no device read."""
+    return int(_lib.load().ofb_last_unconverged())
 
 
 def precondition(P, r, speed_alpha, remodelling_alpha, options=None, workspace=None):

@@ -116,35 +116,48 @@ def _copy_stream(dev):
     return _copy_streams[key]
 
 
-def _default_batch(Nx, Ny, itemsize, n_pairs):
-    # ~12 level-0 vectors + hierarchy per pair; stay under a few GB of workspace
+def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None):
+    """Frame pairs per chunk.  Larger chunks are faster per pair - 16 / 32 / 64 pairs of 1024^2 solve at 775 / 887 / 943
+    pairs per second on a B200: the persistent sweeps get longer row ranges per CTA and the one-CTA-per-pair coarse
+    kernels more CTAs - until ~64.  ~16 level-0 vectors of workspace per pair; bounded by a quarter of the free device
+    memory and 16 GiB."""
     per_pair = 16 * 3 * Nx * Ny * itemsize
-    B = int(max(1, min(n_pairs, (4 << 30) // per_pair, 64)))
+    budget = 16 << 30
+    if dev is not None:
+        try:
+            budget = min(budget, torch.cuda.mem_get_info(dev)[0] // 4)
+        except Exception:
+            pass
+    B = int(max(1, min(n_pairs, budget // per_pair, 64)))
+    # The egress of a chunk (device->host copy, float64 widening: ~0.7 ms per 1024^2 pair on 8 host threads) only starts
+    # when the chunk is solved, so a movie of few chunks is bound by first solve + whole egress, not by the device: keep at
+    # least ~4 chunks in a call as long as a chunk still has >= 16 Mpixel (128 pairs: 32 per chunk, 500 pairs: 64).
+    floor16 = -(-(16 << 20) // (Nx * Ny))
+    B = min(B, max(floor16, n_pairs // 4))
     # one chunk would leave nothing to overlap the device->host egress with: split in two when both halves
     # still fill the machine (>= 4 Mpixel per launch)
     if B >= n_pairs and n_pairs * Nx * Ny >= (8 << 20):
         B = max((n_pairs + 1) // 2, -(-(4 << 20) // (Nx * Ny)))
-    return B
+    return max(1, min(B, n_pairs))
 
 
 def _chunk_schedule(n_pairs, B, pixels, taper=True):
-    """Pair ranges [(k0, k1), ...] of the chunk pipeline: full chunks of B and, with ``taper`` (OFB_TAPER=1), a tapered
-    end - the last B..2B pairs go as halves of what is left (not below ~4 Mpixel per launch).  Nothing overlaps the
-    device->host copy and the widening of the final chunk, so a smaller final chunk shortens that tail (14.6 -> 3.8 ms
-    at 1024^2) - but 4-pair chunks solve at 2.0 ms per pair instead of 1.4 (fixed per-solve costs), and the two cancel:
-    200.9 vs 200.0 ms per 128 pairs on the B200 box.  Measured neutral, so off by default."""
-    if not taper or n_pairs <= B:
-        return [(k, min(k + B, n_pairs)) for k in range(0, n_pairs, B)]
-    floor = max(1, -(-(4 << 20) // max(1, pixels)))
+    """Pair ranges [(k0, k1), ...] of the chunk pipeline: chunks of B and, with ``taper``, one short final chunk of
+    ~B/4 pairs (at least ~16 Mpixel: below that the fixed costs of a solve dominate - 4-pair chunks of 1024^2 run at
+    2.0 ms per pair instead of 1.4).  Nothing overlaps the device->host copy and the float64 widening of the final
+    chunk, so its size sets the tail of the call: a 64-pair chunk of 1024^2 leaves ~58 ms, a 16-pair one 15 ms."""
+    plain = [(k, min(k + B, n_pairs)) for k in range(0, n_pairs, B)]
+    last = max(-(-(16 << 20) // max(1, pixels)), B // 4)
+    if not taper or n_pairs <= B or last >= B or n_pairs - last < 1:
+        return plain
+    main = n_pairs - last
+    n_chunks = -(-main // B)
     bounds, k = [], 0
-    while n_pairs - k > 2 * B:
-        bounds.append((k, k + B))
-        k += B
-    while n_pairs - k > 0:
-        rest = n_pairs - k
-        piece = min(B, rest if rest < 2 * floor else (rest + 1) // 2)
-        bounds.append((k, k + piece))
-        k += piece
+    for c in range(n_chunks):                       # the main part in chunks of B, the short one of them next to the end
+        size = B if (c + 1) * B <= main else main - c * B
+        bounds.append((k, k + size))
+        k += size
+    bounds.append((k, n_pairs))
     return bounds
 
 
@@ -168,6 +181,10 @@ def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace,
     # it does not handle, and the remaining budget is better spent on the fallbacks (which restart from x0 anyway).
     probe = min(int(max_it), PROBE_IT)
     iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, probe, opts, workspace)
+    if engine.last_unconverged() == 0:
+        # every pair converged: no fallback, and no device->host read either - a read here would queue on the copy
+        # engine behind the previous chunk's result planes (tens of ms for a 64-pair chunk)
+        return x, iters, relres, conv, fallback
     passthrough = {k: v for k, v in solver_options.items() if k in ('check_every', 'rows_per_strip', 'flags')}
     robust = engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8, omega_pre=(0.8, 0.8), omega_post=(0.8, 0.8), **passthrough)
     chain = []                                      # (options, solve in float64, iteration budget)
@@ -238,7 +255,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         rtol = min(rtol, 1e-12)
     solver_options = dict(solver_options or {})
     itemsize = 4 if tdtype == torch.float32 else 8
-    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs)
+    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs, dev)
     B = max(1, min(B, n_pairs))
     scale_in = float(delta_t) / float(delta_x)                                 # :800-801
     scale_out = float(delta_x) / float(delta_t)                                # :1189-1190
@@ -266,7 +283,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     timeline = []
     t_setup = time.time()
     try:
-        schedule = _chunk_schedule(n_pairs, B, Nx * Ny, taper=os.environ.get('OFB_TAPER', '0') != '0')
+        schedule = _chunk_schedule(n_pairs, B, Nx * Ny, taper=os.environ.get('OFB_TAPER', '1') != '0')
         uploader.prefetch(source[schedule[0][0]:schedule[0][1] + 1])
         stats = []
         for c, (k0, k1) in enumerate(schedule):

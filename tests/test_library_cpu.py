@@ -96,6 +96,8 @@ def test_chunk_schedule_covers_every_pair_once_and_tapers_the_end():
             sch = _chunk_schedule(n, B, px, taper=taper)
             assert sch[0][0] == 0 and sch[-1][1] == n
             assert all(a[1] == b[0] for a, b in zip(sch, sch[1:])) and all(0 < k1 - k0 <= B for k0, k1 in sch)
-    assert [k1 - k0 for k0, k1 in _chunk_schedule(128, 16, 1 << 20)][-4:] == [16, 8, 4, 4]
+    assert [k1 - k0 for k0, k1 in _chunk_schedule(128, 64, 1 << 20)] == [64, 48, 16]       # one short final chunk
+    assert [k1 - k0 for k0, k1 in _chunk_schedule(499, 64, 1 << 20)][-3:] == [64, 35, 16]
     assert _chunk_schedule(16, 16, 1 << 20) == [(0, 16)]                 # a single chunk is left alone
-    assert [k1 - k0 for k0, k1 in _chunk_schedule(40, 16, 64 * 64)] == [16, 16, 8]     # small frames: no launch below ~4 Mpixel
+    assert [k1 - k0 for k0, k1 in _chunk_schedule(128, 16, 1 << 20)] == [16] * 8           # 16 Mpixel chunks are not split
+    assert [k1 - k0 for k0, k1 in _chunk_schedule(40, 16, 64 * 64)] == [16, 16, 8]         # small frames neither

@@ -1,13 +1,14 @@
-"""Host timeline of the drop-in on the bench workload (65-frame 1024^2 movie, fp32)."""
+"""Host timeline of the drop-in on the bench workload (129-frame 1024^2 movie, fp32):  python tools/e2e_profile.py [B]"""
 import os, sys, time, json
 import numpy as np, torch
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__))); sys.path.insert(0, ROOT)
 from opticalflow_b200 import optical_flow, synthetic
-B = 16
-movie = synthetic.rotating_shearing_movie(1024, 1024, B + 1, seed=2).astype(np.float32)
-REP = int(sys.argv[1]) if len(sys.argv) > 1 else 1            # 1: 64 pairs, 3: 128 pairs (the bench's movie)
-zig = np.concatenate([np.arange(0, B + 1), np.arange(B - 1, -1, -1)] + [np.arange(1, B + 1), np.arange(B - 1, -1, -1)] * REP)
-m = np.ascontiguousarray(movie[zig])
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 64
+movie = synthetic.rotating_shearing_movie(1024, 1024, 17, seed=2).astype(np.float32)
+zig = list(range(17))
+while len(zig) < 129:
+    zig += list(range(15, -1, -1)) + list(range(1, 17))
+m = np.ascontiguousarray(movie[np.array(zig[:129])])
 kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.5, dtype='float32', rtol=1e-6, batch_pairs=B)
 res = None
 for rep in range(6):
