@@ -266,8 +266,9 @@ def run_gpu(args):
 
     traffic = None                                                  # DRAM bytes per launch from the committed ncu --set full capture
     tf = os.path.join(ROOT, 'profiles', 'r01_smoother_traffic.json')
-    if os.path.isfile(tf) and B == 16 and args.dtype == 'float32':
-        traffic = int(json.load(open(tf))['traffic_bytes_per_launch'])
+    if os.path.isfile(tf) and args.dtype == 'float32':
+        captured = json.load(open(tf)).get(str(B))               # keyed by pairs per launch
+        traffic = int(captured['traffic_bytes_per_launch']) if captured else None
 
     # ---- reduce over ranks
     t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device=dev)

@@ -116,7 +116,7 @@ def _copy_stream(dev):
     return _copy_streams[key]
 
 
-def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None):
+def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True):
     """Frame pairs per chunk.  Larger chunks are faster per pair - 16 / 32 / 64 pairs of 1024^2 solve at 775 / 887 / 943
     pairs per second on a B200: the persistent sweeps get longer row ranges per CTA and the one-CTA-per-pair coarse
     kernels more CTAs - until ~64.  ~16 level-0 vectors of workspace per pair; bounded by a quarter of the free device
@@ -129,6 +129,8 @@ def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None):
         except Exception:
             pass
     B = int(max(1, min(n_pairs, budget // per_pair, 64)))
+    if not pipelined:                              # nothing is copied back per chunk (vary_regularisation): just fill the device
+        return B
     # The egress of a chunk (device->host copy, float64 widening: ~0.7 ms per 1024^2 pair on 8 host threads) only starts
     # when the chunk is solved, so a movie of few chunks is bound by first solve + whole egress, not by the device: keep at
     # least ~4 chunks in a call as long as a chunk still has >= 16 Mpixel (128 pairs: 32 per chunk, 500 pairs: 64).
@@ -276,8 +278,9 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     copy_stream = _copy_stream(dev)
     worker = hostio.EgressWorker()
     uploader = hostio.FrameUploader(B + 1, (Nx, Ny), source.dtype, dev)
-    slots = []                                                                 # double-buffered device + pinned planes
-    for s in range(2):
+    slots = []                                                                 # device + pinned planes, three deep: chunk k+2 is
+    n_slots = 3 if n_pairs > 2 * B else 2                                      # solved while k+1 is copied and k is widened
+    for s in range(n_slots):
         slots.append(dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev),
                           pin=hostio.pinned_pool.acquire((nplanes, B + 1, Nx, Ny), tdtype), busy=None))
     timeline = []
@@ -288,7 +291,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         stats = []
         for c, (k0, k1) in enumerate(schedule):
             nb = k1 - k0
-            slot = slots[c % 2]
+            slot = slots[c % n_slots]
             t_chunk = time.perf_counter()
             if slot['busy'] is not None:
                 slot['busy'].wait()                                            # worker has drained this slot's pinned planes
@@ -411,7 +414,7 @@ def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
     cell_beta = np.tile(betas, len(alphas))
     n_cells = cell_alpha.size
     itemsize = 4 if tdtype == torch.float32 else 8
-    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_cells)
+    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_cells, dev, pipelined=False)
     moments = np.zeros((n_cells, 4))
     functional = np.zeros(n_cells)
     converged_last = np.zeros(n_cells, bool)
