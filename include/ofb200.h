@@ -203,6 +203,10 @@ size_t ofb_clahe_workspace_bytes(int frames_in_flight, int tiles_x, int tiles_y)
 int ofb_clahe(const void* in, void* out, double clip_limit, int tiles_x, int tiles_y, void* workspace,
               size_t workspace_bytes, int F, int Nx, int Ny, int dtype, void* stream);
 
+/* float32 -> float64 on the device (n elements, 16-byte aligned buffers): result planes of a float32 solve widened to
+ *     the reference's float64 result format (optical_flow.py:1193-1205) before they leave for pinned host memory. */
+int ofb_widen(const void* in_f32, void* out_f64, long long n, void* stream);
+
 /* Background subtraction of conduct_optical_flow (optical_flow.py:195-198):
  *     out = movie - background where blurred > background, else 0 (blurred = ofb_blur(movie, sigma 10)). */
 int ofb_subtract_background(const void* movie, const void* blurred, void* out, double background, long long n,

@@ -27,7 +27,7 @@ EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
                     'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab',
                     'ofb_liu_shen', 'ofb_movie_max', 'ofb_adaptive_threshold', 'ofb_clahe_workspace_bytes', 'ofb_clahe',
-                    'ofb_subtract_background')
+                    'ofb_subtract_background', 'ofb_widen')
 
 
 class SolveOptions(ctypes.Structure):
@@ -123,6 +123,8 @@ def load():
     lib.ofb_clahe_workspace_bytes.argtypes = [i, i, i]
     lib.ofb_clahe.restype = i
     lib.ofb_clahe.argtypes = [vp, vp, d, i, i, vp, sz, i, i, i, i, vp]
+    lib.ofb_widen.restype = i
+    lib.ofb_widen.argtypes = [vp, vp, ll, vp]
     lib.ofb_subtract_background.restype = i
     lib.ofb_subtract_background.argtypes = [vp, vp, vp, d, ll, i, vp]
     if lib.ofb_version() != ABI_VERSION:

@@ -625,6 +625,23 @@ __global__ void __launch_bounds__(256) k_clahe_interp(const T* __restrict__ in, 
 }
 
 // -----------------------------------------------------------------------------------------------------
+// float32 -> float64 widening of result planes on the device (the reference returns float64 arrays, :1193-1205): the
+// planes then travel device -> pinned result memory as they are and the host cores do no conversion.
+// -----------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_widen(const float* __restrict__ in, double* __restrict__ out, long long n) {
+    const long long n4 = n >> 2;
+    const float4* in4 = reinterpret_cast<const float4*>(in);
+    double2* out2 = reinterpret_cast<double2*>(out);
+    for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n4; k += (long long)gridDim.x * blockDim.x) {
+        const float4 v = in4[k];
+        out2[2 * k] = make_double2((double)v.x, (double)v.y);
+        out2[2 * k + 1] = make_double2((double)v.z, (double)v.w);
+    }
+    for (long long k = 4 * n4 + (long long)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += (long long)gridDim.x * blockDim.x)
+        out[k] = (double)in[k];
+}
+
+// -----------------------------------------------------------------------------------------------------
 // background subtraction (:195-198): out = movie - background where blur(movie, 10) > background, else 0
 // -----------------------------------------------------------------------------------------------------
 template <typename T>

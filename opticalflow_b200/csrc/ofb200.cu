@@ -691,8 +691,8 @@ template <typename T> struct Solver {
             const T* ecv = gather ? window(ec) : ec;
             bool done = false;
             if constexpr (sizeof(T) == 4) {
-                if (g[l].aligned && g[l].Ny % 4 == 0) {
-                    dim3 block(128), grid((g[l].Ny / 4 + 127) / 128, g[l].Nx, B);
+                if (g[l].aligned && g[l].pitch % 4 == 0 && g[l].Ny >= 8) {
+                    dim3 block(128), grid(((g[l].Ny + 3) / 4 + 127) / 128, g[l].Nx, B);
                     OFB_LAUNCH(pdl(), k_prolong_add4, grid, block, 0, stream, gcv, ecv, g[l], cur, active);
                     done = true;
                 }
@@ -1450,6 +1450,14 @@ int ofb_clahe(const void* in, void* out, double clip_limit, int tiles_x, int til
     if (in_flight < 1) return fail(-5, "ofb_clahe: workspace too small: %zu bytes given, %zu per frame needed", workspace_bytes, per_frame);
     return dtype == OFB_F32 ? clahe_impl<float>(in, out, g, workspace, in_flight, F, (cudaStream_t)stream)
                             : clahe_impl<double>(in, out, g, workspace, in_flight, F, (cudaStream_t)stream);
+}
+
+int ofb_widen(const void* in_f32, void* out_f64, long long n, void* stream) {
+    if (n < 1 || !in_f32 || !out_f64) return fail(-1, "ofb_widen: empty input");
+    if (!ptr_aligned16(in_f32) || !ptr_aligned16(out_f64)) return fail(-7, "ofb_widen: buffers must be 16-byte aligned");
+    k_widen<<<stream_grid(n, 256 * 8), 256, 0, (cudaStream_t)stream>>>((const float*)in_f32, (double*)out_f64, n);
+    OFB_CHECK_LAUNCH();
+    return 0;
 }
 
 int ofb_subtract_background(const void* movie, const void* blurred, void* out, double background, long long n, int dtype, void* stream) {

@@ -114,7 +114,8 @@ __global__ void k_prolong_add(Geom gc, const T* __restrict__ coarse, Geom gf, T*
 
 // Vectorised variant: one thread owns four consecutive fine columns (16-byte read-modify-write per plane); the six
 // coarse values it interpolates from (columns 2m, 2m+1, 2m+2 of two coarse rows) come through the read-only path.
-// Requires fp32, Ny % 4 == 0 and 16-byte aligned fine rows.
+// Requires fp32 and 16-byte aligned fine rows with pitch % 4 == 0 (coarse levels pad their pitch: the vector that
+// holds the last columns then also covers pad elements, which are written back unchanged).
 __global__ void __launch_bounds__(128) k_prolong_add4(Geom gc, const float* __restrict__ coarse, Geom gf, float* __restrict__ fine,
                                                       const int* __restrict__ active) {
     pdl_enter();
@@ -137,10 +138,11 @@ __global__ void __launch_bounds__(128) k_prolong_add4(Geom gc, const float* __re
         float* fp = fine + (long long)pair * gf.pair + (long long)q * gf.plane + (long long)i * gf.pitch + j4;
         float4 v = *reinterpret_cast<float4*>(fp);
         const float e0 = 0.25f * (s0 + s1), e1 = 0.5f * s1, e2 = 0.25f * (s1 + s2), e3 = 0.5f * s2;
-        if (j4 > 0) v.x += e0;                                   // column 0 is a ghost column
-        v.y += e1;
-        v.z += e2;
-        if (j4 + 3 < gf.Ny - 1) v.w += e3;                       // column Ny-1 is a ghost column (Ny % 4 == 0)
+        const int last = gf.Ny - 2;                              // columns 0 and Ny-1 are ghost columns
+        if (j4 > 0) v.x += e0;
+        if (j4 + 1 <= last) v.y += e1;
+        if (j4 + 2 <= last) v.z += e2;
+        if (j4 + 3 <= last) v.w += e3;
         *reinterpret_cast<float4*>(fp) = v;
     }
 }

@@ -278,3 +278,12 @@ def subtract_background(frames, blurred, background):
     _lib.check(_lib.load().ofb_subtract_background(_ptr(frames), _ptr(blurred), _ptr(out), float(background), frames.numel(),
                                                    _code(frames), _stream_ptr(frames.device)))
     return out
+
+
+def widen(src, dst):
+    """float32 device tensor -> float64 device tensor of the same shape (``ofb_widen``), on the current stream."""
+    _require_cuda(src, dst)
+    assert src.dtype == torch.float32 and dst.dtype == torch.float64 and src.shape == dst.shape
+    assert src.is_contiguous() and dst.is_contiguous()
+    _lib.check(_lib.load().ofb_widen(_ptr(src), _ptr(dst), src.numel(), _stream_ptr(src.device)))
+    return dst

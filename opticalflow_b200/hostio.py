@@ -152,6 +152,23 @@ class PinnedPool:
 pinned_pool = PinnedPool()
 
 
+def _page_locked_buffer(nbytes):
+    """uint8 array of ``nbytes`` whose pages are locked with cudaHostRegister (exact size: torch's pinned allocator rounds
+    requests up to a power of two, which would double a 1.07 GB result plane).  Unregistered when the array is collected."""
+    import weakref
+    page = 4096
+    size = -(-max(int(nbytes), 1) // page) * page
+    raw = np.empty(size + page, dtype=np.uint8)
+    offset = (-raw.ctypes.data) % page
+    buf = raw[offset:offset + size]
+    cudart = torch.cuda.cudart()
+    err = cudart.cudaHostRegister(buf.ctypes.data, size, 0)
+    if int(err) != 0:
+        raise RuntimeError('cudaHostRegister of %d bytes failed: %s' % (size, err))
+    weakref.finalize(raw, cudart.cudaHostUnregister, buf.ctypes.data)      # runs before raw's memory is released
+    return buf[:nbytes] if nbytes > 0 else buf[:0]
+
+
 class ResultArena:
     """Recycles the memory of result arrays the caller has dropped.
 
@@ -172,34 +189,39 @@ class ResultArena:
             max_idle_bytes = int(os.environ.get('OFB_RESULT_ARENA_BYTES', min(32 << 30, ram // 8)))
         self.max_idle_bytes = int(max_idle_bytes)
         self.free = []                       # idle uint8 buffers
+        self.free_pinned = []                # idle page-locked uint8 buffers
         self.lock = threading.Lock()
 
-    def _give_back(self, buf):
+    def _give_back(self, buf, pinned=False):
         with self.lock:
-            if sum(b.nbytes for b in self.free) + buf.nbytes <= self.max_idle_bytes:
-                self.free.append(buf)
+            pool = self.free_pinned if pinned else self.free
+            if sum(b.nbytes for b in self.free) + sum(b.nbytes for b in self.free_pinned) + buf.nbytes <= self.max_idle_bytes:
+                pool.append(buf)
 
-    def alloc(self, shape, dtype):
+    def alloc(self, shape, dtype, pinned=False):
+        """``pinned``: page-locked memory (cudaHostAlloc through torch) the device can copy results into directly.
+        Pinning costs ~0.1-0.3 s per GB once; recycled buffers stay pinned.  Raises if the memory cannot be pinned."""
         import weakref
         dtype = np.dtype(dtype)
         need = int(np.prod(shape)) * dtype.itemsize
-        if self.max_idle_bytes <= 0 or need < (1 << 20):
+        if not pinned and (self.max_idle_bytes <= 0 or need < (1 << 20)):
             return np.empty(shape, dtype=dtype)
         buf = None
         with self.lock:
+            pool = self.free_pinned if pinned else self.free
             best = None
-            for k, b in enumerate(self.free):
-                if need <= b.nbytes <= need + (need >> 2) and (best is None or b.nbytes < self.free[best].nbytes):
+            for k, b in enumerate(pool):
+                if need <= b.nbytes <= need + (need >> 2) and (best is None or b.nbytes < pool[best].nbytes):
                     best = k
             if best is not None:
-                buf = self.free.pop(best)
+                buf = pool.pop(best)
         if buf is None:
-            buf = np.empty(need, dtype=np.uint8)
+            buf = _page_locked_buffer(need) if pinned else np.empty(need, dtype=np.uint8)
         # numpy collapses .base chains of ndarray views onto the owning array, so the owner the caller's arrays keep
         # alive must be a per-allocation object of our own: a ctypes window onto the buffer.  When the last view of
         # it is gone the finalizer returns the buffer (which the finalizer's argument list keeps alive until then).
         carrier = (ctypes.c_char * need).from_address(buf.ctypes.data)
-        weakref.finalize(carrier, self._give_back, buf)
+        weakref.finalize(carrier, self._give_back, buf, pinned)
         return np.frombuffer(carrier, dtype=dtype).reshape(shape)
 
 

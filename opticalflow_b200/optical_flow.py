@@ -116,7 +116,7 @@ def _copy_stream(dev):
     return _copy_streams[key]
 
 
-def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True):
+def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True, host_widening=True):
     """Frame pairs per chunk.  Larger chunks are faster per pair - 16 / 32 / 64 pairs of 1024^2 solve at 775 / 887 / 943
     pairs per second on a B200: the persistent sweeps get longer row ranges per CTA and the one-CTA-per-pair coarse
     kernels more CTAs - until ~64.  ~16 level-0 vectors of workspace per pair; bounded by a quarter of the free device
@@ -134,8 +134,10 @@ def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True):
     # The egress of a chunk (device->host copy, float64 widening: ~0.7 ms per 1024^2 pair on 8 host threads) only starts
     # when the chunk is solved, so a movie of few chunks is bound by first solve + whole egress, not by the device: keep at
     # least ~4 chunks in a call as long as a chunk still has >= 16 Mpixel (128 pairs: 32 per chunk, 500 pairs: 64).
-    floor16 = -(-(16 << 20) // (Nx * Ny))
-    B = min(B, max(floor16, n_pairs // 4))
+    # (Direct egress has no host stage: the copy engine moves a float64 pair in 0.8 ms, faster than it is solved.)
+    if host_widening:
+        floor16 = -(-(16 << 20) // (Nx * Ny))
+        B = min(B, max(floor16, n_pairs // 4))
     # one chunk would leave nothing to overlap the device->host egress with: split in two when both halves
     # still fill the machine (>= 4 Mpixel per launch)
     if B >= n_pairs and n_pairs * Nx * Ny >= (8 << 20):
@@ -161,6 +163,16 @@ def _chunk_schedule(n_pairs, B, pixels, taper=True):
         k += size
     bounds.append((k, n_pairs))
     return bounds
+
+
+class _EventWaiter:
+    """``wait()`` on a CUDA event, the interface the staged path's worker futures have."""
+
+    def __init__(self, event):
+        self.event = event
+
+    def wait(self):
+        self.event.synchronize()
 
 
 PROBE_IT = 100
@@ -257,18 +269,38 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         rtol = min(rtol, 1e-12)
     solver_options = dict(solver_options or {})
     itemsize = 4 if tdtype == torch.float32 else 8
-    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs, dev)
+    blur = smoothing_sigma is not None
+    arena = hostio.result_arena                                                # recycles dropped result arrays' pages
+    result_bytes = (4 * n_pairs + (T if blur else 0)) * Nx * Ny * 8
+    direct = (os.environ.get('OFB_DIRECT_EGRESS', '1') != '0' and arena.max_idle_bytes > 0
+              and result_bytes <= int(os.environ.get('OFB_DIRECT_EGRESS_BYTES', 16 << 30)))
+    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs, dev, host_widening=not direct)
     B = max(1, min(B, n_pairs))
     scale_in = float(delta_t) / float(delta_x)                                 # :800-801
     scale_out = float(delta_x) / float(delta_t)                                # :1189-1190
     guess = (float(initial_v_x) * scale_in, float(initial_v_y) * scale_in, float(initial_remodelling))
-    blur = smoothing_sigma is not None
 
     source = np.ascontiguousarray(movie_np)
-    arena = hostio.result_arena                                                # recycles dropped result arrays' pages
     original = arena.alloc((T, Nx, Ny), np.float64)                            # :769
-    out = {k: arena.alloc((n_pairs, Nx, Ny), np.float64) for k in ('v_x', 'v_y', 'speed', 'remodelling')}
-    blurred = arena.alloc((T, Nx, Ny), np.float64) if blur else original
+    # Direct egress: the result arrays are page-locked, the planes are widened to float64 on the device and copied
+    # straight into them - the host cores do no conversion (on a slow host the float32 -> float64 widening, not the
+    # device, bounded the call).  Pinning costs ~0.1-0.3 s per GB the first time (recycled by the arena afterwards), so
+    # it is used up to OFB_DIRECT_EGRESS_BYTES (default 16 GiB) of results; beyond that, or if pinning fails, the planes
+    # go through pinned staging and the host copy pool as before.
+    result_names = ('v_x', 'v_y', 'speed', 'remodelling')
+    out, blurred, out_t, blurred_t = None, None, None, None
+    if direct:
+        try:
+            out = {k: arena.alloc((n_pairs, Nx, Ny), np.float64, pinned=True) for k in result_names}
+            blurred = arena.alloc((T, Nx, Ny), np.float64, pinned=True) if blur else original
+            out_t = {k: torch.from_numpy(v) for k, v in out.items()}
+            blurred_t = torch.from_numpy(blurred) if blur else None
+            direct = all(t.is_pinned() for t in out_t.values()) and (blurred_t is None or blurred_t.is_pinned())
+        except Exception:
+            direct = False
+    if not direct:
+        out = {k: arena.alloc((n_pairs, Nx, Ny), np.float64) for k in result_names}
+        blurred = arena.alloc((T, Nx, Ny), np.float64) if blur else original
     functionals = np.zeros((n_pairs, 3))
     info = dict(iterations=np.zeros(n_pairs, np.int32), relative_residual=np.zeros(n_pairs),
                 converged=np.zeros(n_pairs, bool), fallback=np.zeros(n_pairs, bool))
@@ -281,8 +313,13 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     slots = []                                                                 # device + pinned planes, three deep: chunk k+2 is
     n_slots = 3 if n_pairs > 2 * B else 2                                      # solved while k+1 is copied and k is widened
     for s in range(n_slots):
-        slots.append(dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev),
-                          pin=hostio.pinned_pool.acquire((nplanes, B + 1, Nx, Ny), tdtype), busy=None))
+        slot = dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev), pin=None, busy=None)
+        if not direct:
+            slot['pin'] = hostio.pinned_pool.acquire((nplanes, B + 1, Nx, Ny), tdtype)
+        # float64 planes for the direct path (a float64 solve's planes are copied as they are)
+        slot['dev64'] = (torch.empty((nplanes, B + 1, Nx, Ny), dtype=torch.float64, device=dev)
+                         if direct and tdtype != torch.float64 else slot['dev'])
+        slots.append(slot)
     timeline = []
     t_setup = time.time()
     try:
@@ -311,23 +348,43 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
             t_solve = time.perf_counter()
             fields = slot['dev'][:4, :nb]
             _, _, _, _, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out, out=fields)
-            ready = torch.cuda.Event()
-            ready.record(main_stream)
             last_frame = nb + 1 if k1 == n_pairs else nb
-            with torch.cuda.stream(copy_stream):
-                copy_stream.wait_event(ready)
-                for q in range(4):
-                    slot['pin'][q, :nb].copy_(slot['dev'][q, :nb], non_blocking=True)
+            if direct:
+                planes = slot['dev64']
+                if planes is not slot['dev']:
+                    for q in range(4):
+                        engine.widen(slot['dev'][q, :nb], planes[q, :nb])
+                    if blur:
+                        engine.widen(slot['dev'][4, :last_frame], planes[4, :last_frame])
+                ready = torch.cuda.Event()
+                ready.record(main_stream)
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(ready)
+                    for q, name in enumerate(result_names):
+                        out_t[name][k0:k1].copy_(planes[q, :nb], non_blocking=True)
+                    if blur:
+                        blurred_t[k0:k0 + last_frame].copy_(planes[4, :last_frame], non_blocking=True)
+                    copied = torch.cuda.Event()
+                    copied.record(copy_stream)
+                slot['busy'] = _EventWaiter(copied)            # slot reuse waits for the copy engine, not for a host thread
+                slot['original'] = worker.submit(None, [(original[k0:k0 + last_frame], source[k0:k0 + last_frame])])   # :769
+            else:
+                ready = torch.cuda.Event()
+                ready.record(main_stream)
+                with torch.cuda.stream(copy_stream):
+                    copy_stream.wait_event(ready)
+                    for q in range(4):
+                        slot['pin'][q, :nb].copy_(slot['dev'][q, :nb], non_blocking=True)
+                    if blur:
+                        slot['pin'][4, :last_frame].copy_(slot['dev'][4, :last_frame], non_blocking=True)
+                    copied = torch.cuda.Event()
+                    copied.record(copy_stream)
+                # one widening job per chunk: splitting it per plane was measured slower (27 vs 22 ms per chunk)
+                copies = [(out[name][k0:k1], slot['pin'][q, :nb]) for q, name in enumerate(result_names)]
                 if blur:
-                    slot['pin'][4, :last_frame].copy_(slot['dev'][4, :last_frame], non_blocking=True)
-                copied = torch.cuda.Event()
-                copied.record(copy_stream)
-            # one widening job per chunk: splitting it per plane was measured slower (27 vs 22 ms per chunk)
-            copies = [(out[name][k0:k1], slot['pin'][q, :nb]) for q, name in enumerate(('v_x', 'v_y', 'speed', 'remodelling'))]
-            if blur:
-                copies.append((blurred[k0:k0 + last_frame], slot['pin'][4, :last_frame]))
-            copies.append((original[k0:k0 + last_frame], source[k0:k0 + last_frame]))      # float64 copy of the input (:769)
-            slot['busy'] = worker.submit(copied, copies)       # slot reuse (two chunks later) waits for this on the host
+                    copies.append((blurred[k0:k0 + last_frame], slot['pin'][4, :last_frame]))
+                copies.append((original[k0:k0 + last_frame], source[k0:k0 + last_frame]))      # float64 copy of the input (:769)
+                slot['busy'] = worker.submit(copied, copies)       # slot reuse (three chunks later) waits for this on the host
             stats.append(torch.cat([fun, iters.double()[:, None], relres[:, None], conv.double()[:, None],
                                     fb.double()[:, None]], dim=1))
             timeline.append(dict(chunk=c, wait_slot_and_frames=t_take - t_chunk, prepare=t_prep - t_take,
@@ -345,6 +402,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         for slot in slots:
             if slot['busy'] is not None:
                 slot['busy'].wait()
+            if slot.get('original') is not None:
+                slot['original'].wait()
         timeline.append(dict(stats=t_stats - t_loop, drain=time.perf_counter() - t_stats, setup=t_setup - t_start))
     finally:
         worker.close()
@@ -352,7 +411,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         copy_stream.synchronize()
         uploader.close()
         for slot in slots:
-            hostio.pinned_pool.release(slot['pin'])
+            if slot['pin'] is not None:
+                hostio.pinned_pool.release(slot['pin'])
     if verbose and not info['converged'].all():
         print('the solver has not actually converged, the result will be incorrect or inaccurate')
     result = dict()
@@ -375,7 +435,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info['timeline'] = timeline
     info['egress_log'] = list(worker.log)
     info['h2d_bytes'] = int(sum(k1 - k0 + 1 for k0, k1 in schedule) * source[0].nbytes)
-    info['d2h_bytes'] = int((4 * n_pairs + (T if blur else 0)) * Nx * Ny * itemsize)
+    info['d2h_bytes'] = int((4 * n_pairs + (T if blur else 0)) * Nx * Ny * (8 if direct else itemsize))
+    info['direct_egress'] = bool(direct)
     result['solver_info'] = info
     return result
 
