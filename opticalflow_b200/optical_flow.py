@@ -116,7 +116,7 @@ def _copy_stream(dev):
     return _copy_streams[key]
 
 
-def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True, host_widening=True):
+def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True):
     """Frame pairs per chunk.  Larger chunks are faster per pair - 16 / 32 / 64 pairs of 1024^2 solve at 775 / 887 / 943
     pairs per second on a B200: the persistent sweeps get longer row ranges per CTA and the one-CTA-per-pair coarse
     kernels more CTAs - until ~64.  ~16 level-0 vectors of workspace per pair; bounded by a quarter of the free device
@@ -134,10 +134,10 @@ def _default_batch(Nx, Ny, itemsize, n_pairs, dev=None, pipelined=True, host_wid
     # The egress of a chunk (device->host copy, float64 widening: ~0.7 ms per 1024^2 pair on 8 host threads) only starts
     # when the chunk is solved, so a movie of few chunks is bound by first solve + whole egress, not by the device: keep at
     # least ~4 chunks in a call as long as a chunk still has >= 16 Mpixel (128 pairs: 32 per chunk, 500 pairs: 64).
-    # (Direct egress has no host stage: the copy engine moves a float64 pair in 0.8 ms, faster than it is solved.)
-    if host_widening:
-        floor16 = -(-(16 << 20) // (Nx * Ny))
-        B = min(B, max(floor16, n_pairs // 4))
+    # With direct egress (no host stage) the same holds for the copy engine's backlog: 128 pairs as 32-32-32-16-16 take
+    # 180 ms, as 64-48-16 190 ms (the float64 planes of the 48-pair chunk are still on the wire when the last solve ends).
+    floor16 = -(-(16 << 20) // (Nx * Ny))
+    B = min(B, max(floor16, n_pairs // 4))
     # one chunk would leave nothing to overlap the device->host egress with: split in two when both halves
     # still fill the machine (>= 4 Mpixel per launch)
     if B >= n_pairs and n_pairs * Nx * Ny >= (8 << 20):
@@ -274,7 +274,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     result_bytes = (4 * n_pairs + (T if blur else 0)) * Nx * Ny * 8
     direct = (os.environ.get('OFB_DIRECT_EGRESS', '1') != '0' and arena.max_idle_bytes > 0
               and result_bytes <= int(os.environ.get('OFB_DIRECT_EGRESS_BYTES', 16 << 30)))
-    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs, dev, host_widening=not direct)
+    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs, dev)
     B = max(1, min(B, n_pairs))
     scale_in = float(delta_t) / float(delta_x)                                 # :800-801
     scale_out = float(delta_x) / float(delta_t)                                # :1189-1190
