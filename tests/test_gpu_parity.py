@@ -326,3 +326,36 @@ def test_devices_argument_shards_pairs_over_threads(cuda_device):
         assert rel(two[key], one[key]) < 1e-9, key
     assert two['solver_info']['shards'] == [3, 2] and two['converged']
     assert abs(two['L1_functional'] - one['L1_functional']) < 1e-8 * abs(one['L1_functional'])
+
+
+def test_direct_and_staged_egress_return_identical_arrays(cuda_device, monkeypatch):
+    """Direct egress (page-locked result arrays, float64 widening on the device) against the staged path (pinned float32
+    staging, widening by the host copy pool), for a float32 and a float64 solve, over several chunks."""
+    movie = synthetic.translating_movie(96, 128, 6, seed=5).astype(np.float32)
+    kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.0, batch_pairs=2)
+    for dtype in ('float32', 'float64'):
+        monkeypatch.setenv('OFB_DIRECT_EGRESS', '1')
+        direct = optical_flow.variational_optical_flow(movie, dtype=dtype, **kw)
+        assert direct['solver_info']['direct_egress']
+        monkeypatch.setenv('OFB_DIRECT_EGRESS', '0')
+        staged = optical_flow.variational_optical_flow(movie, dtype=dtype, **kw)
+        assert not staged['solver_info']['direct_egress']
+        # the blur has no atomics: bit-identical planes through both paths; two solves of the same pair differ in the
+        # last bits (dot products are summed by atomics), so the fields agree to the solver tolerance, not to the bit
+        for key in ('blurred_data', 'original_data'):
+            assert direct[key].dtype == np.float64 and np.array_equal(direct[key], staged[key]), key
+        for key in ('v_x', 'v_y', 'speed', 'remodelling'):
+            assert direct[key].dtype == np.float64 and direct[key].shape == staged[key].shape
+            assert rel(direct[key], staged[key]) < (1e-4 if dtype == 'float32' else 1e-6), key
+        if dtype == 'float32':      # widened on the device or on the host, every value is a float32
+            assert np.array_equal(direct['v_x'], direct['v_x'].astype(np.float32).astype(np.float64))
+        assert np.array_equal(direct['original_data'], movie.astype(np.float64))
+    # dropped results hand their page-locked buffers back to the arena; the next call of the same shape reuses them
+    import gc
+    from opticalflow_b200 import hostio
+    monkeypatch.setenv('OFB_DIRECT_EGRESS', '1')
+    del direct, staged
+    gc.collect()
+    idle = len(hostio.result_arena.free_pinned)
+    again = optical_flow.variational_optical_flow(movie, dtype='float32', **kw)
+    assert again['solver_info']['direct_egress'] and idle >= 1 and len(hostio.result_arena.free_pinned) < idle
