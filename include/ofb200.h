@@ -42,6 +42,7 @@ extern "C" {
 #define OFB_FLAG_STRIP_ITEMS 64 /* streamed sweeps: fixed-size row strips dealt round-robin instead of the balanced walk (A/B) */
 #define OFB_FLAG_NO_HALF_STEP_EXIT 128 /* BiCGStab: no convergence test after the first half step (A/B measurements) */
 #define OFB_FLAG_PDL 32 /* programmatic dependent launch for the solver-loop kernels (measured neutral to -0.3%: off by default) */
+#define OFB_FLAG_FUSED_PROLONG 512 /* float32 image level: prolongation inside the first post-smoothing sweep instead of its own pass (A/B) */
 #define OFB_FLAG_SERIAL_SETUP 256 /* dense coarsest-level inverse on the solve's own stream instead of beside the first fine sweeps (A/B) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 

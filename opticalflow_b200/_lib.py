@@ -19,6 +19,7 @@ FLAG_PDL = 32
 FLAG_STRIP_ITEMS = 64
 FLAG_NO_HALF_STEP_EXIT = 128
 FLAG_SERIAL_SETUP = 256
+FLAG_FUSED_PROLONG = 512
 ABI_VERSION = 4
 
 # every symbol include/ofb200.h declares

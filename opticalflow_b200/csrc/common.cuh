@@ -99,6 +99,24 @@ __device__ __forceinline__ void store_own(T* __restrict__ rowptr, int j0, int Ny
     }
 }
 
+// Ghost columns of a window row are patched in registers from the lane's own window: column 0 <- column 2,
+// column Ny-1 <- column Ny-1-far_j (window index kg = Ny - j0, mirror at kg - far_j); doubled on ghost rows of
+// solution-type planes (the reference's corner rows).  Linear in the row, so a correction added to a row can be
+// patched separately (fused prolongation in the streamed smoother).
+template <typename T, int MODE>
+__device__ __forceinline__ void patch_ghost_columns(Row<T>& r, bool ghost_row, int j0, const Geom& g) {
+    constexpr int V = VecOf<T>::V;
+    if (j0 == 0) r.v[1] = (MODE == LOAD_SOL && ghost_row) ? r.v[3] + r.v[3] : r.v[3];
+    if (j0 == 1) r.v[0] = (MODE == LOAD_SOL && ghost_row) ? r.v[2] + r.v[2] : r.v[2];
+    const int kg = g.Ny - j0;
+#pragma unroll
+    for (int k = 2; k <= V + 1; ++k)
+        if (kg == k) {
+            const T t = (g.far_j == 2) ? r.v[k - 2] : r.v[k - 1];
+            r.v[k] = (MODE == LOAD_SOL && ghost_row) ? t + t : t;
+        }
+}
+
 // Load one row with halos from `rowptr` (rowptr[j] = column j; global memory or a shared-memory row
 // staged by the streamed sweeps).  `edge_warp` is warp-uniform: true when the warp's column range
 // (with halo) touches column 0 or Ny-1, the only place the ghost remap costs anything.
@@ -130,19 +148,7 @@ __device__ __forceinline__ void load_row_ptr(Row<T>& r, const T* __restrict__ ro
         r.v[0] = left;
         r.v[V + 1] = right;
     }
-    if (MODE != LOAD_RAW && edge_warp) {
-        // ghost columns are patched in registers from the lane's own window: column 0 <- column 2,
-        // column Ny-1 <- column Ny-1-far_j (window index kg = Ny - j0, mirror at kg - far_j)
-        if (j0 == 0) r.v[1] = (MODE == LOAD_SOL && ghost_row) ? r.v[3] + r.v[3] : r.v[3];
-        if (j0 == 1) r.v[0] = (MODE == LOAD_SOL && ghost_row) ? r.v[2] + r.v[2] : r.v[2];
-        const int kg = g.Ny - j0;
-#pragma unroll
-        for (int k = 2; k <= V + 1; ++k)
-            if (kg == k) {
-                const T t = (g.far_j == 2) ? r.v[k - 2] : r.v[k - 1];
-                r.v[k] = (MODE == LOAD_SOL && ghost_row) ? t + t : t;
-            }
-    }
+    if (MODE != LOAD_RAW && edge_warp) patch_ghost_columns<T, MODE>(r, ghost_row, j0, g);
 }
 
 // Load row i of a plane in global memory with halos.

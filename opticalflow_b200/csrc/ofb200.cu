@@ -539,6 +539,20 @@ template <typename T> struct Solver {
         OpSmooth<T> op; op.g = g[l]; op.cen[0] = b; op.xo = xout; op.w = T(wj);
         return sweep(l, xin, op);
     }
+    // first post-smoothing sweep with the prolongation folded in (fp32 image level, streamed sweep only)
+    int smooth_prolong(int l, const T* b, const T* xin, T* xout, double wj, const T* ec, const Geom& gc) {
+        if constexpr (sizeof(T) == 4) {
+            OpSmoothProlong<T> op; op.g = g[l]; op.cen[0] = b; op.xo = xout; op.w = T(wj); op.ec = ec; op.gc = gc;
+            const LevelArgs<T> L = level_args(l);
+            return launch_stream<T, true, OpSmoothProlong<T>>(L, xin, op, B, opt.rows_per_strip, false, stream, pdl());
+        } else {
+            return fail(-9, "fused prolongation is float32 only");
+        }
+    }
+    bool fuse_prolong(int l) const {
+        return sizeof(T) == 4 && l == 0 && use_stream(0) && opt.nu_post >= 1 && !slab.on && g[1].aligned != 0 &&
+               (opt.flags & OFB_FLAG_FUSED_PROLONG) != 0;
+    }
     int residual(int l, const T* b, const T* x, T* r) {
         OpResidual<T, false> op; op.g = g[l]; op.cen[0] = b; op.r = r; op.r2 = nullptr; op.st = w.st; op.acc[0] = 0.0;
         return sweep(l, x, op);
@@ -685,7 +699,8 @@ template <typename T> struct Solver {
             if ((rc = jacobi_zero(lc, w.lb[lc], w.xa[lc], w_pre(0)))) return rc;
             if ((rc = vcycle(lc, w.lb[lc], w.xa[lc], w.xb[lc], &ec))) return rc;
         }
-        {
+        const bool fused = fuse_prolong(l);      // the correction is added inside the first post-smoothing sweep
+        if (!fused) {
             // a distributed fine level below a replicated coarse level interpolates from its window of the coarse grid
             const Geom gcv = gather ? window_geom() : g[lc];
             const T* ecv = gather ? window(ec) : ec;
@@ -703,7 +718,7 @@ template <typename T> struct Solver {
             }
         }
         for (int s = 0; s < opt.nu_post; ++s) {
-            if ((rc = smooth(l, b, cur, alt, w_post(s)))) return rc;
+            if ((rc = (fused && s == 0) ? smooth_prolong(l, b, cur, alt, w_post(s), ec, g[lc]) : smooth(l, b, cur, alt, w_post(s)))) return rc;
             std::swap(cur, alt);
             if ((rc = exchange_vec(l, cur))) return rc;
         }

@@ -56,6 +56,16 @@ template <typename T> struct OpSmooth {
     __device__ __forceinline__ void flush(int) {}
 };
 
+// The first post-smoothing sweep of a level with the coarse-grid correction folded in: x_out = y + w D^-1 (b - S y),
+// y = x + P e.  The streamed sweep stages the two coarse rows a fine window row interpolates from and adds P e to the
+// window as it is loaded (stream_sweep.cuh), so the separate prolongation pass (read x, write x: 6 words per pixel)
+// disappears.  The arithmetic of a row is OpSmooth's.
+template <typename T> struct OpSmoothProlong : OpSmooth<T> {
+    static constexpr bool PROLONG = true;
+    const T* ec;            // coarse correction [B][3][coarse plane]
+    Geom gc;                // its geometry
+};
+
 // r = b - S x ; INIT: also copy to r2 and dots acc[2] += r.r, acc[3] += r.r (initial residual: rhat = r)
 template <typename T, bool INIT> struct OpResidual {
     static constexpr bool NEED_X = true;

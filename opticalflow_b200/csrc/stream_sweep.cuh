@@ -15,6 +15,7 @@
 #include <type_traits>
 #include "pipeline.cuh"
 #include "solver_kernels.cuh"
+#include "transfer.cuh"
 
 namespace ofb {
 
@@ -28,15 +29,31 @@ template <typename T> struct StreamCfg {
     static constexpr int THREADS = (CW + 1) * WARP;
 };
 
+// Ops with `static constexpr bool PROLONG = true` (OpSmoothProlong) get the coarse-grid correction added to the solution
+// window as it is loaded: 3 planes x 2 coarse rows are staged with every window row.
+template <typename Op, typename = void> struct OpProlong : std::false_type {};
+template <typename Op> struct OpProlong<Op, std::void_t<decltype(Op::PROLONG)>> : std::integral_constant<bool, Op::PROLONG> {};
+
+#ifndef OFB_PROLONG_STAGES
+#define OFB_PROLONG_STAGES 3
+#endif
+
 template <typename T, bool FROM_IMAGE, typename Op> struct StreamLayout {
     using C = StreamCfg<T>;
     static constexpr int NWIN = (Op::NEED_X ? 3 : 0) + (FROM_IMAGE ? 1 : 0);      // rows staged one row ahead
+    static constexpr int NCOR = OpProlong<Op>::value ? 6 : 0;                     // coarse correction rows (staged with them)
+    static constexpr int COR_ELEMS = C::TW / 2 + 4;                               // coarse columns a tile interpolates from
+    static constexpr int NCORSLOTS = (NCOR * COR_ELEMS + C::ROW - 1) / C::ROW;    // the six half-width rows are packed: 3 row slots
+    static constexpr int NAHEAD = NWIN + NCORSLOTS;                               // row slots staged one row ahead
     static constexpr int NCENROWS = 3 * Op::NCEN + (FROM_IMAGE ? 0 : NCOEF);      // rows staged at the centre row
-    static constexpr int NROWS = NWIN + NCENROWS;
-    static_assert(NROWS <= WARP, "one producer lane per staged row");
+    static constexpr int NROWS = NAHEAD + NCENROWS;                               // row slots per stage
+    static constexpr int NLANES = NWIN + NCOR + NCENROWS;                         // producer lanes (one per copied row)
+    static_assert(NLANES <= WARP, "one producer lane per staged row");
+    // three CTAs per SM: the correction rows bring a stage to 10 row slots, which fit three deep
+    static constexpr int STAGES = NCOR > 0 ? OFB_PROLONG_STAGES : C::STAGES;
     static constexpr int STAGE_ELEMS = NROWS * C::ROW;
-    static constexpr size_t RING_BYTES = (size_t)C::STAGES * STAGE_ELEMS * sizeof(T);
-    static constexpr size_t SMEM_BYTES = RING_BYTES + 2 * C::STAGES * sizeof(uint64_t);
+    static constexpr size_t RING_BYTES = (size_t)STAGES * STAGE_ELEMS * sizeof(T);
+    static constexpr size_t SMEM_BYTES = RING_BYTES + 2 * STAGES * sizeof(uint64_t);
 };
 
 template <int N> using IC = std::integral_constant<int, N>;
@@ -104,7 +121,9 @@ template <typename T, bool FROM_IMAGE, typename Op>
 __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T> L, const T* __restrict__ x, Op op, int n_items) {
     using C = StreamCfg<T>;
     using Lay = StreamLayout<T, FROM_IMAGE, Op>;
-    constexpr int V = C::V, STAGES = C::STAGES, NROWS = Lay::NROWS, NWIN = Lay::NWIN;
+    constexpr int V = C::V, STAGES = Lay::STAGES, NWIN = Lay::NWIN, NCOR = Lay::NCOR, NAHEAD = Lay::NAHEAD, NLANES = Lay::NLANES;
+    constexpr int NCENROWS = Lay::NCENROWS;
+    constexpr bool PROLONG = OpProlong<Op>::value;
     extern __shared__ __align__(128) unsigned char smem_raw[];
     T* ring = reinterpret_cast<T*>(smem_raw);
     uint64_t* full = reinterpret_cast<uint64_t*>(smem_raw + Lay::RING_BYTES);
@@ -129,6 +148,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
         // then the centre rows: NCEN vectors x 3 planes, then 7 coefficient planes (!FROM_IMAGE).
         const bool is_win = lane < NWIN;
         const bool is_sol = Op::NEED_X && lane < 3;
+        const bool is_cor = PROLONG && lane >= NWIN && lane < NWIN + NCOR;      // plane (lane-NWIN)/2, coarse row a / b
         WorkWalk<T> walk(L, n_items, L.n_pairs);
         int pair, tile, i_begin, i_end;
         while (walk.next(pair, tile, i_begin, i_end)) {
@@ -138,25 +158,45 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
             const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(T);
             const int nk = i_end - i_begin + 2;
             const T* base = nullptr;
-            if (lane < NROWS) {
+            uint32_t cbytes = 0;                    // bytes of one coarse correction row of this tile
+            int cpitch = 0;
+            if constexpr (PROLONG) {
+                const int lo_c = c0 >> 1, hi_c = min(lo_c + Lay::COR_ELEMS, op.gc.pitch);
+                cbytes = (uint32_t)(hi_c - lo_c) * (uint32_t)sizeof(T);
+                cpitch = op.gc.pitch;
+                if (is_cor) base = op.ec + (long long)pair * op.gc.pair + (long long)((lane - NWIN) >> 1) * op.gc.plane + lo_c;
+            }
+            if (lane < NLANES && !is_cor) {
                 if (is_sol) base = x + (long long)pair * g.pair + (long long)lane * g.plane;
                 else if (is_win) base = L.coef + (long long)pair * L.coef_pair;               // image plane
                 else {
-                    const int c = lane - NWIN;
+                    const int c = lane - NWIN - NCOR;
                     if (c < 3 * Op::NCEN) base = op.cen[c / 3] + (long long)pair * g.pair + (long long)(c % 3) * g.plane;
                     else base = L.coef + (long long)pair * L.coef_pair + (long long)(c - 3 * Op::NCEN) * g.plane;
                 }
                 base += lo;
             }
-            const int dst_off = lane * C::ROW + (lo - (c0 - C::HALO));
+            // row slot of the lane's copy: window rows first, then the packed correction rows, then the centre rows
+            const int dst_off = is_cor ? NWIN * C::ROW + (lane - NWIN) * Lay::COR_ELEMS
+                                       : (is_win ? lane : lane - NCOR + Lay::NCORSLOTS) * C::ROW + (lo - (c0 - C::HALO));
             for (int k = 0; k < nk; ++k, ++n) {
                 const int s = n % STAGES;
                 const uint32_t ph = (n / STAGES) & 1u;
                 mbar_wait_sleep(empty + s, ph ^ 1u, 256);
                 const bool cen_valid = k >= 2;
-                if (lane == 0) mbar_arrive_expect_tx(full + s, (uint32_t)(cen_valid ? NROWS : NWIN) * bytes);
+                if (lane == 0) mbar_arrive_expect_tx(full + s, (uint32_t)(cen_valid ? NWIN + NCENROWS : NWIN) * bytes + (uint32_t)NCOR * cbytes);
                 __syncwarp();
-                if (lane < NROWS && (is_win || cen_valid)) {
+                bool cor_done = false;
+                if constexpr (PROLONG) {
+                    if (is_cor) {
+                        // the two coarse rows the fine window row (after its ghost redirect) interpolates from
+                        const int fine = sol_row(i_begin - 1 + k, g);
+                        const int crow = reflect_row((fine + 1 + ((lane - NWIN) & 1)) >> 1, op.gc);
+                        bulk_g2s(ring + s * Lay::STAGE_ELEMS + dst_off, base + (long long)crow * cpitch, cbytes, full + s);
+                        cor_done = true;
+                    }
+                }
+                if (!cor_done && lane < NLANES && (is_win || cen_valid)) {
                     int row;
                     if (is_win) {
                         row = i_begin - 1 + k;
@@ -199,6 +239,48 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                         load_row_ptr<T, LOAD_SOL, true>(ux[sp], stg, ghost_row, j0, g, lane, edge_warp);
                         load_row_ptr<T, LOAD_SOL, true>(uy[sp], stg + C::ROW, ghost_row, j0, g, lane, edge_warp);
                         load_row_ptr<T, LOAD_SOL, true>(gg[sp], stg + 2 * C::ROW, ghost_row, j0, g, lane, edge_warp);
+                        if constexpr (PROLONG) {
+                            // y = x + P e on the window row: bilinear interpolation from the two staged coarse rows.  Window
+                            // column t (fine column j0-1+t, j0 a multiple of 4) takes the coarse columns m+(t>>1), m+((t+1)>>1),
+                            // m = j0/2; coarse ghost columns are read at their mirror image (edge warps only); the ghost-column
+                            // patch of the window is linear, so the correction is patched the same way and added.
+                            const T* cor = ring + s * Lay::STAGE_ELEMS + NWIN * C::ROW - (c0 >> 1);     // cor[r*COR_ELEMS + m] = coarse column m
+                            const int m0 = j0 >> 1;
+                            const bool one_row = (sol_row(iw, g) & 1) != 0;       // odd fine rows sit on a coarse row: both staged rows are it
+                            Row<T>* dst3[3] = {&ux[sp], &uy[sp], &gg[sp]};
+#pragma unroll
+                            for (int q = 0; q < 3; ++q) {
+                                const T* ca = cor + (2 * q) * Lay::COR_ELEMS;
+                                const T* cb = ca + Lay::COR_ELEMS;
+                                T sm_[4];
+                                if (!edge_warp) {
+                                    // four consecutive coarse columns from an even index: two 8-byte loads per coarse row
+                                    const float2 a0 = *reinterpret_cast<const float2*>(ca + m0), a1 = *reinterpret_cast<const float2*>(ca + m0 + 2);
+                                    float2 b0 = a0, b1 = a1;
+                                    if (!one_row) {
+                                        b0 = *reinterpret_cast<const float2*>(cb + m0);
+                                        b1 = *reinterpret_cast<const float2*>(cb + m0 + 2);
+                                    }
+                                    sm_[0] = a0.x + b0.x; sm_[1] = a0.y + b0.y; sm_[2] = a1.x + b1.x; sm_[3] = a1.y + b1.y;
+                                } else {
+#pragma unroll
+                                    for (int t = 0; t < 4; ++t) {
+                                        const int mc = reflect_clamped(m0 + t, op.gc.Ny, op.gc.far_j);
+                                        sm_[t] = ca[mc] + cb[mc];
+                                    }
+                                }
+                                Row<T> er;
+                                er.v[0] = T(0.5) * sm_[0];
+                                er.v[1] = T(0.25) * (sm_[0] + sm_[1]);
+                                er.v[2] = T(0.5) * sm_[1];
+                                er.v[3] = T(0.25) * (sm_[1] + sm_[2]);
+                                er.v[4] = T(0.5) * sm_[2];
+                                er.v[5] = T(0.25) * (sm_[2] + sm_[3]);
+                                if (edge_warp) patch_ghost_columns<T, LOAD_SOL>(er, ghost_row, j0, g);
+#pragma unroll
+                                for (int t = 0; t < V + 2; ++t) dst3[q]->v[t] += er.v[t];
+                            }
+                        }
                     }
                     if constexpr (FROM_IMAGE) load_row_ptr<T, LOAD_RAW, true>(pw[sp], stg + (NWIN - 1) * C::ROW, false, j0, g, lane, false);
                 }
@@ -214,7 +296,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                         T cr[NCOEF][V];
 #pragma unroll
                         for (int q = 0; q < NCOEF; ++q) {
-                            const VT t = *reinterpret_cast<const VT*>(stg + (NWIN + 3 * Op::NCEN + q) * C::ROW + j0);
+                            const VT t = *reinterpret_cast<const VT*>(stg + (NAHEAD + 3 * Op::NCEN + q) * C::ROW + j0);
                             const T* p = reinterpret_cast<const T*>(&t);
 #pragma unroll
                             for (int kk = 0; kk < V; ++kk) cr[q][kk] = p[kk];
@@ -239,7 +321,7 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                             xc[0][kk] = xc[1][kk] = xc[2][kk] = T(0);
                         }
                     }
-                    const CenShared<T, C::ROW> cv{stg + NWIN * C::ROW + j0};
+                    const CenShared<T, C::ROW> cv{stg + NAHEAD * C::ROW + j0};
                     op.row(pair, i, j0, cf, sx, xc, inside, a, be, cv);
                 }
                 __syncwarp();

@@ -359,3 +359,33 @@ def test_direct_and_staged_egress_return_identical_arrays(cuda_device, monkeypat
     idle = len(hostio.result_arena.free_pinned)
     again = optical_flow.variational_optical_flow(movie, dtype='float32', **kw)
     assert again['solver_info']['direct_egress'] and idle >= 1 and len(hostio.result_arena.free_pinned) < idle
+
+
+@pytest.mark.parametrize('shape', [(64, 256), (130, 512), (257, 1028), (96, 1024)])
+def test_fused_prolongation_matches_separate_pass(cuda_device, shape):
+    """float32 image level, OFB_FLAG_FUSED_PROLONG: the first post-smoothing sweep adds the coarse-grid correction to its
+    window as it loads it (same arithmetic as the separate pass, one launch fewer per V-cycle).  One preconditioner
+    application and a whole solve against the default path."""
+    from opticalflow_b200 import _lib
+    rng = np.random.default_rng(shape[1])
+    B = 3
+    P = dev_t(rng.uniform(20, 200, (B,) + shape), cuda_device, torch.float32)
+    r = dev_t(rng.standard_normal((B, 3) + shape), cuda_device, torch.float32)
+    r[:, :, 0, :] = 0; r[:, :, -1, :] = 0; r[:, :, :, 0] = 0; r[:, :, :, -1] = 0
+    alpha, beta = torch.tensor([1e5, 3e5, 1e6]), torch.tensor([1e4, 1e3, 1e5])
+    lib = _lib.load()
+    n0 = lib.ofb_launch_count()
+    plain = engine.precondition(P, r, alpha, beta, engine.make_options('mg'))
+    n1 = lib.ofb_launch_count()
+    fused = engine.precondition(P, r, alpha, beta, engine.make_options('mg', flags=_lib.FLAG_FUSED_PROLONG))
+    n2 = lib.ofb_launch_count()
+    assert (n2 - n1) == (n1 - n0) - 1                                    # the fused path ran
+    inner = (slice(None), slice(None), slice(1, -1), slice(1, -1))
+    assert float((fused[inner] - plain[inner]).abs().max()) <= 1e-5 * float(plain[inner].abs().max())
+    xs = []
+    for flags in (0, _lib.FLAG_FUSED_PROLONG):
+        x = torch.zeros_like(r)
+        it, rr, cv = engine.solve(P, r, x, alpha, beta, 1e-6, 200, engine.make_options('mg', flags=flags))
+        assert int(cv.sum()) == B
+        xs.append((x.cpu().double().numpy(), it.cpu().numpy()))
+    assert rel(xs[0][0], xs[1][0]) < 1e-4 and np.abs(xs[0][1] - xs[1][1]).max() <= 1
