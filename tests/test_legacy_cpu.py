@@ -78,3 +78,11 @@ def test_oracle_against_reference_run_here():
     with contextlib.redirect_stdout(io.StringIO()):
         want = ref.apply_clahe(movie, 3000, 6)
     assert np.array_equal(want, lo.apply_clahe(movie, 3000, 6))
+    # edge cases: a window larger than the frame, no clipping (clipLimit 0), one tile, few grey levels
+    small = rng.uniform(0, 255, (1, 20, 23))
+    assert np.array_equal(ref.apply_adaptive_threshold(small, 51, -2.0), lo.apply_adaptive_threshold(small, 51, -2.0))
+    flat = np.round(rng.uniform(0, 6, (1, 48, 64))) * 100.0
+    for clip, tiles in ((0.0, 4), (50000, 1), (1.0, 3)):
+        with contextlib.redirect_stdout(io.StringIO()):
+            want = ref.apply_clahe(flat, clip, tiles)
+        assert np.array_equal(want, lo.apply_clahe(flat, clip, tiles)), (clip, tiles)

@@ -167,7 +167,8 @@ def test_clahe_matches_reference_golden(cuda_device, golden, case):
 
 @pytest.mark.parametrize('shape,clip,tiles,scale', [((1, 16, 16), 40.0, 2, 1.0), ((3, 130, 75), 500.0, 5, 20.0),
                                                     ((2, 64, 250), 50000, 3, 250.0), ((1, 1024, 1024), 10000, 10, 100.0),
-                                                    ((1, 101, 103), 3.0, 7, 0.2)])
+                                                    ((1, 101, 103), 3.0, 7, 0.2), ((2, 48, 64), 0.0, 4, 30.0),
+                                                    ((1, 40, 40), 50000, 1, 300.0)])
 def test_clahe_matches_oracle(cuda_device, shape, clip, tiles, scale):
     movie = texture(shape[0], shape[1], shape[2], tiles) * scale
     want = lo.apply_clahe(movie, clip, tiles)
