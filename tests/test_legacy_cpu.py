@@ -86,3 +86,18 @@ def test_oracle_against_reference_run_here():
         with contextlib.redirect_stdout(io.StringIO()):
             want = ref.apply_clahe(flat, clip, tiles)
         assert np.array_equal(want, lo.apply_clahe(flat, clip, tiles)), (clip, tiles)
+
+
+@pytest.mark.skipif(not ref_import.reference_available(), reason='reference sources not present (GPU box)')
+def test_liu_shen_oracle_against_reference_numba_on_tiny_frames():
+    """The smallest frames the padded reference arrays allow (2x2, 2x5, 3x3): every pixel is an edge or corner pixel."""
+    ref = ref_import.import_reference()
+    rng = np.random.default_rng(9)
+    for shape, its in (((2, 2), 1), ((2, 5), 3), ((3, 3), 4)):
+        movie = rng.uniform(20, 200, (3,) + shape)
+        gx, gy, gr = rng.standard_normal(shape), rng.standard_normal(shape), rng.standard_normal(shape)
+        want = ref.liu_shen_optical_flow_jit(movie, 1.5, 0.5, 50.0, 1.0, gx, gy, gr, its, 1e-9, True)
+        got = lo.liu_shen_optical_flow(movie, 1.5, 0.5, 50.0, 1.0, gx, gy, gr, its)
+        for g, w in zip(got[:4], want[:4]):
+            assert np.abs(g - w).max() <= 1e-12 * max(1.0, np.abs(w).max()), shape
+        assert got[4] == want[4]
