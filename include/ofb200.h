@@ -46,7 +46,7 @@ extern "C" {
 #define OFB_FLAG_SERIAL_SETUP 256 /* dense coarsest-level inverse on the solve's own stream instead of beside the first fine sweeps (A/B) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 
-#define OFB_ABI_VERSION 4
+#define OFB_ABI_VERSION 5
 
 typedef struct ofb_solve_options {
     int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
@@ -106,10 +106,20 @@ int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, con
 /* K4/K5  solve A x = b: replaces the PETSc KSP solve (optical_flow.py:1081-1132; -ksp_type bcgs, rtol on the
  *     unpreconditioned residual, nonzero initial guess).  x3: in = initial guess, out = solution (ghost ring
  *     completed from the boundary rows).  Ghost-ring entries of b3 must be 0 (the reference never sets them,
- *     :837).  iters_out/relres_out/converged_out: device arrays of length B (may be NULL). */
+ *     :837).  A pair whose b is all zero gets x = 0.
+ *     Diagnostics (optical_flow.py:1135-1157), device arrays of length B, each may be NULL:
+ *       relres_out      |b - A x| / |b| RECOMPUTED from the returned x in fp64 arithmetic - the independent residual the
+ *                       reference prints at :1150-1151;
+ *       recurrence_out  the BiCGStab recurrence residual the iteration stopped on (the KSP's own norm, :1140-1142);
+ *       converged_out   1 when the true residual passes  |b - A x| <= rtol |b| + 2 u |D x|  (u = unit round-off of
+ *                       `dtype`, D = diagonal of A: the part of the residual that rounding x to `dtype` leaves behind;
+ *                       negligible in float64, ~3e-5 |b| in float32 at alpha = 1e5);
+ *       iters_out       BiCGStab iterations.
+ *     A pair whose recurrence converged (or broke down) while its true residual does not pass is restarted from
+ *     r = b - A x, at most twice. */
 int ofb_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta,
               double rtol, int max_it, const ofb_solve_options* opt, void* workspace, size_t workspace_bytes,
-              int* iters_out, double* relres_out, int* converged_out,
+              int* iters_out, double* relres_out, int* converged_out, double* recurrence_out,
               int B, int Nx, int Ny, int dtype, void* stream);
 
 /* One application of the preconditioner z = M^-1 r (testing / diagnostics). */
@@ -165,7 +175,7 @@ size_t ofb_slab_workspace_bytes(int B, int Ny, int dtype, const ofb_slab* slab);
  * convergence decision are identical on all ranks. */
 int ofb_solve_slab(const void* P, const void* b3, void* x3, const double* alpha, const double* beta,
                    double rtol, int max_it, const ofb_solve_options* opt, void* workspace, size_t workspace_bytes,
-                   int* iters_out, double* relres_out, int* converged_out,
+                   int* iters_out, double* relres_out, int* converged_out, double* recurrence_out,
                    int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream);
 /* ofb_epilogue on a slab: functionals/moments are this rank's partial sums over its owned rows. */
 int ofb_epilogue_slab(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma,

@@ -20,7 +20,7 @@ FLAG_STRIP_ITEMS = 64
 FLAG_NO_HALF_STEP_EXIT = 128
 FLAG_SERIAL_SETUP = 256
 FLAG_FUSED_PROLONG = 512
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 # every symbol include/ofb200.h declares
 EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_last_unconverged', 'ofb_workspace_bytes', 'ofb_blur',
@@ -87,7 +87,7 @@ def load():
     lib.ofb_smooth.restype = i
     lib.ofb_smooth.argtypes = [vp, vp, vp, vp, dp, dp, ctypes.POINTER(SolveOptions), i, i, i, i, vp]
     lib.ofb_solve.restype = i
-    lib.ofb_solve.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip,
+    lib.ofb_solve.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip, dp,
                               i, i, i, i, vp]
     lib.ofb_precondition.restype = i
     lib.ofb_precondition.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(SolveOptions), vp, sz, i, i, i, i, vp]
@@ -109,7 +109,7 @@ def load():
     lib.ofb_slab_workspace_bytes.restype = sz
     lib.ofb_slab_workspace_bytes.argtypes = [i, i, i, slabp]
     lib.ofb_solve_slab.restype = i
-    lib.ofb_solve_slab.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip,
+    lib.ofb_solve_slab.argtypes = [vp, vp, vp, dp, dp, d, i, ctypes.POINTER(SolveOptions), vp, sz, ip, dp, ip, dp,
                                    i, i, i, i, slabp, vp]
     lib.ofb_epilogue_slab.restype = i
     lib.ofb_epilogue_slab.argtypes = [vp, vp, vp, vp, vp, vp, vp, dp, dp, dp, dp, d, i, i, i, i, slabp, vp]

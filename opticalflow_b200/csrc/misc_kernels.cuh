@@ -137,7 +137,8 @@ __global__ void k_state_init(PairState* __restrict__ st, int* __restrict__ activ
     PairState s;
     s.rho = s.rho_old = s.alpha = s.omega = 1.0; s.beta_k = 0.0;
     s.acc[0] = s.acc[1] = s.acc[2] = s.acc[3] = 0.0;
-    s.bnorm = 0.0; s.relres = 0.0; s.active = 1; s.iters = 0; s.status = ST_RUNNING; s.half_pending = 0;
+    s.bnorm = 0.0; s.relres = 0.0; s.true_relres = 0.0; s.floor_relres = 0.0;
+    s.active = 1; s.iters = 0; s.status = ST_RUNNING; s.half_pending = 0; s.restarts = 0;
     st[pair] = s;
     active_arr[pair] = 1;
 }
@@ -147,12 +148,15 @@ __global__ void k_state_bnorm(PairState* __restrict__ st, int B) {
     st[pair].bnorm = sqrt(st[pair].acc[0]);
     st[pair].acc[0] = 0.0;
 }
+// relres = the true residual of the returned x (what the reference prints at :1150-1151), recurrence = the BiCGStab
+// recurrence residual the iteration stopped on (the KSP's own norm, :1140-1142)
 __global__ void k_state_export(const PairState* __restrict__ st, int B, int* __restrict__ iters, double* __restrict__ relres,
-                               int* __restrict__ converged, int* __restrict__ n_unconverged) {
+                               int* __restrict__ converged, int* __restrict__ n_unconverged, double* __restrict__ recurrence) {
     const int pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= B) return;
     if (iters) iters[pair] = st[pair].iters;
-    if (relres) relres[pair] = st[pair].relres;
+    if (relres) relres[pair] = st[pair].true_relres;
+    if (recurrence) recurrence[pair] = st[pair].relres;
     const bool ok = st[pair].status == ST_CONVERGED;
     if (converged) converged[pair] = ok ? 1 : 0;
     if (n_unconverged && !ok) atomicAdd(n_unconverged, 1);
@@ -245,6 +249,54 @@ __global__ void k_apply_full(Geom g, const T* __restrict__ P, const T* __restric
     }
     T* o = y + (long long)pair * g.pair + (long long)i * g.pitch + j;
     o[0] = out[0]; o[g.plane] = out[1]; o[2 * g.plane] = out[2];
+}
+
+// ------------------------------------------------------------------ true residual of a returned solution
+// |b - A x|^2 -> st.acc[0] and |D x|^2 -> st.acc[1] (D = diagonal of A) over the interior rows, evaluated in fp64
+// arithmetic whatever the storage type: the independent check the reference prints (:1150-1151).  x must have its ghost
+// ring completed (k_fill_ghosts): the boundary rows of the reference system then hold exactly and contribute 0.
+template <typename T>
+__global__ void __launch_bounds__(128) k_true_residual(Geom g, const T* __restrict__ P, const T* __restrict__ x, const T* __restrict__ b,
+                                                       const double* __restrict__ alpha, const double* __restrict__ beta,
+                                                       PairState* __restrict__ st) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int pair = blockIdx.z;
+    double acc[2] = {0.0, 0.0};
+    if (j >= 1 && j <= g.Ny - 2) {
+        const T* xb = x + (long long)pair * g.pair;
+        const T* bb = b + (long long)pair * g.pair;
+        const T* img = P + (long long)pair * g.img_pair;
+        const double a = alpha[pair], be = beta[pair];
+        auto at = [&](int q, int ii, int jj) -> double { return (double)xb[q * g.plane + (long long)ii * g.pitch + jj]; };
+        for (int i = 1 + blockIdx.y; i <= g.Nx - 2; i += gridDim.y) {
+            Row<double> pm, pc, pp;
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                pm.v[c] = (double)img[(long long)(i - 1) * g.pitch + j - 1 + c];
+                pc.v[c] = (double)img[(long long)i * g.pitch + j - 1 + c];
+                pp.v[c] = (double)img[(long long)(i + 1) * g.pitch + j - 1 + c];
+            }
+            const Coef<double> c = coef_from_image<double>(pm, pc, pp, 1);
+            double y[3];
+            apply_at<double>(c, at, i, j, a, be, y);
+            const long long o = (long long)i * g.pitch + j;
+            const double r0 = (double)bb[o] - y[0], r1 = (double)bb[g.plane + o] - y[1], r2 = (double)bb[2 * g.plane + o] - y[2];
+            acc[0] += r0 * r0 + r1 * r1 + r2 * r2;
+            const double d0 = (c.IIxx - 2.0 * c.II - 4.0 * a) * at(0, i, j), d1 = (c.IIyy - 2.0 * c.II - 4.0 * a) * at(1, i, j);
+            const double d2 = (-1.0 - 4.0 * be) * at(2, i, j);
+            acc[1] += d0 * d0 + d1 * d1 + d2 * d2;
+        }
+    }
+    block_accumulate<2>(acc, st[pair].acc);
+}
+
+// the exact solution of a pair with b = 0 (two identical frames) is x = 0, whatever the initial guess
+template <typename T>
+__global__ void k_zero_trivial(const PairState* __restrict__ st, long long n_per_pair, long long pair_stride, T* __restrict__ x) {
+    const int pair = blockIdx.y;
+    if (st[pair].bnorm != 0.0) return;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n_per_pair; e += (long long)gridDim.x * blockDim.x)
+        x[(long long)pair * pair_stride + e] = T(0);
 }
 
 // ------------------------------------------------------------------ K6 epilogue

@@ -79,7 +79,7 @@ constexpr int MAX_DEVICES = 64;
 
 struct DeviceInfo { int sms; };
 inline int device_sms() {
-    static int sms[MAX_DEVICES] = {0};
+    static std::atomic<int> sms[MAX_DEVICES];
     int dev = 0;
     cudaGetDevice(&dev);
     dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
@@ -98,7 +98,7 @@ int launch_stream(LevelArgs<T> L, const T* x, const Op& op, int B, int rows_per_
     using C = StreamCfg<T>;
     using Lay = StreamLayout<T, FROM_IMAGE, Op>;
     auto kern = k_stream<T, FROM_IMAGE, Op>;
-    static int ctas_per_sm[MAX_DEVICES] = {0};
+    static std::atomic<int> ctas_per_sm[MAX_DEVICES];        // zero-initialised; filled once per device
     int dev = 0;
     cudaGetDevice(&dev);
     dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
@@ -369,7 +369,10 @@ inline cudaStream_t side_stream() {
 }
 
 // Mapped pinned words through which the solve loop reads its counters (k_publish): per host thread and device.
-struct PollBox { int* host = nullptr; int* dev = nullptr; };
+struct PollBox {
+    int* host = nullptr; int* dev = nullptr;
+    ~PollBox() { if (host != nullptr) cudaFreeHost(host); }      // thread_local: released when the host thread ends
+};
 inline PollBox* poll_box() {
     thread_local PollBox boxes[MAX_DEVICES];
     int dev = 0;
@@ -585,7 +588,7 @@ template <typename T> struct Solver {
             const int use_smem = mbytes <= 200 * 1024 ? 1 : 0;
             auto kern = k_coarse_setup<T>;
             if (use_smem) {
-                static bool configured[MAX_DEVICES] = {false};
+                static std::atomic<bool> configured[MAX_DEVICES];      // zero-initialised; set once per device
                 int dev = 0;
                 cudaGetDevice(&dev);
                 dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
@@ -640,7 +643,7 @@ template <typename T> struct Solver {
         A.dense = plan.dense ? 1 : 0; A.dense_n = plan.dense_n; A.Minv = w.dense_Minv;
         A.coarse_sweeps = opt.coarse_sweeps; A.w_coarse = opt.omega;
         auto kern = k_coarse_vcycle<T>;
-        static bool configured[MAX_DEVICES] = {false};
+        static std::atomic<bool> configured[MAX_DEVICES];      // zero-initialised; set once per device
         int dev = 0;
         cudaGetDevice(&dev);
         dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
@@ -791,7 +794,7 @@ int init_solver(Solver<T>& S, const void* P, const double* alpha, const double* 
 template <typename T>
 int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
                const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
-               int* converged_out, int B, int Nx, int Ny, void* stream_, const ofb_slab* sl = nullptr) {
+               int* converged_out, double* recurrence_out, int B, int Nx, int Ny, void* stream_, const ofb_slab* sl = nullptr) {
     Solver<T> S;
     memset(&S.slab, 0, sizeof(S.slab));
     int rc = init_solver<T>(S, P, alpha, beta, opt, workspace, workspace_bytes, B, Nx, Ny, stream_, b3, x3, sl);
@@ -813,6 +816,10 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     if ((rc = S.allreduce_acc())) return rc;
     k_state_bnorm<<<sb, 128, 0, stream>>>(w.st, B);
     OFB_CHECK_LAUNCH();
+    if (!S.slab.on) {   // b = 0 (two identical frames): the solution is x = 0 whatever the initial guess says
+        k_zero_trivial<T><<<blas_grid, tb, 0, stream>>>(w.st, nvec, nvec, x);
+        OFB_CHECK_LAUNCH();
+    }
     // p and v enter the first direction update multiplied by beta_k = 0; they must be finite
     OFB_CHECK_CUDA(cudaMemsetAsync(w.p, 0, sizeof(T) * nvec * B, stream));
     OFB_CHECK_CUDA(cudaMemsetAsync(w.v, 0, sizeof(T) * nvec * B, stream));
@@ -834,7 +841,23 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
     const T wj = T(S.first_sweep_weight());
     int host_active = B;
     PollBox* box = poll_box();
-    for (int it = 0; it < max_it; ++it) {
+    // read a device counter on the host: through the mapped pinned word when there is one (a 4-byte device->host copy
+    // would queue on the copy engine behind another stream's bulk transfers)
+    auto read_counter = [&](const int* dev_counter, int slot, int* out) -> int {
+        if (box != nullptr) {
+            k_publish<<<1, 1, 0, stream>>>(dev_counter, box->dev + slot);
+            OFB_CHECK_LAUNCH();
+            OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+            *out = *(volatile int*)(box->host + slot);
+        } else {
+            OFB_CHECK_CUDA(cudaMemcpyAsync(out, dev_counter, sizeof(int), cudaMemcpyDeviceToHost, stream));
+            OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+        }
+        return 0;
+    };
+    int it = 0;
+    for (int round = 0;; ++round) {
+    for (; it < max_it && host_active > 0; ++it) {
         T *ph = nullptr, *sh = nullptr;
         {   // p = r + beta_k (p - omega v) ; z = w D^-1 p
             OpDirJacobi<T, 0> op; op.g = g0; op.cen[0] = w.r; op.cen[1] = w.v; op.cen[2] = w.p; op.d = w.p; op.z = ph_first; op.w = wj; op.st = w.st; op.acc[0] = 0.0;
@@ -870,35 +893,45 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         if (poll) OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active, 0, sizeof(int), stream));
         if ((rc = S.allreduce_acc())) return rc;
         OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : (int*)nullptr);
-        if (poll) {
-            if (box != nullptr) {
-                k_publish<<<1, 1, 0, stream>>>(w.n_active, box->dev);
-                OFB_CHECK_LAUNCH();
-                OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
-                host_active = *(volatile int*)box->host;
-            } else {
-                OFB_CHECK_CUDA(cudaMemcpyAsync(&host_active, w.n_active, sizeof(int), cudaMemcpyDeviceToHost, stream));
-                OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
-            }
-            if (host_active == 0) break;
-        }
+        if (poll && (rc = read_counter(w.n_active, 0, &host_active))) return rc;
     }
-    {
+    {   // complete the ghost ring: x now solves the reference's full system, boundary rows included
         const int ring = 2 * Nx + 2 * Ny;
         k_fill_ghosts<T><<<dim3((ring + 127) / 128, B), 128, 0, stream>>>(g0, x);
         OFB_CHECK_LAUNCH();
         if ((rc = S.exchange_vec(0, x))) return rc;
     }
+    {   // the independent residual the reference prints (:1150-1151), in fp64 arithmetic, and the verdict on it
+        dim3 grid((Ny + 127) / 128, std::min(std::max(Nx - 2, 1), 64), B);
+        k_true_residual<T><<<grid, 128, 0, stream>>>(g0, S.P, (const T*)x, b, alpha, beta, w.st);
+        OFB_CHECK_LAUNCH();
+        if ((rc = S.allreduce_acc())) return rc;
+        OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active + 2, 0, sizeof(int), stream));
+        const double u = sizeof(T) == 4 ? 5.9604644775390625e-08 : 1.1102230246251565e-16;
+        k_verify<<<sb, 128, 0, stream>>>(w.st, w.active, B, rtol, max_it, u, w.n_active + 2);
+        OFB_CHECK_LAUNCH();
+        int reactivated = 0;
+        if (max_it > 0 && it < max_it && round < MAX_RESTARTS) { if ((rc = read_counter(w.n_active + 2, 2, &reactivated))) return rc; }
+        if (reactivated == 0) break;
+        // restart BiCGStab for the re-activated pairs from the true residual: r = rhat = b - S x
+        S.active = w.active;
+        OpResidual<T, true> op; op.g = g0; op.cen[0] = b; op.r = w.r; op.r2 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
+        if ((rc = S.sweep(0, x, op))) return rc;
+        if ((rc = S.allreduce_acc())) return rc;
+        k_restart<<<sb, 128, 0, stream>>>(w.st, B);
+        OFB_CHECK_LAUNCH();
+        host_active = reactivated;
+    }
+    }
     // the number of pairs that did not converge goes to the host the same way (ofb_last_unconverged)
     OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active + 1, 0, sizeof(int), stream));
-    k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out, w.n_active + 1);
+    k_state_export<<<sb, 128, 0, stream>>>(w.st, B, iters_out, relres_out, converged_out, w.n_active + 1, recurrence_out);
     OFB_CHECK_LAUNCH();
     g_last_unconverged = -1;
     if (box != nullptr) {
-        k_publish<<<1, 1, 0, stream>>>(w.n_active + 1, box->dev + 1);
-        OFB_CHECK_LAUNCH();
-        OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
-        g_last_unconverged = *(volatile int*)(box->host + 1);
+        int unconv = -1;
+        if ((rc = read_counter(w.n_active + 1, 1, &unconv))) return rc;
+        g_last_unconverged = unconv;
     }
     if (S.slab.on && S.slab.comm->box.ok) {
         int err = 0;
@@ -948,7 +981,7 @@ int blur_impl(const void* in, void* out, void* tmp, const double* weights, int r
         while (TH > 8 && smem_for(TH) > 96 * 1024) TH /= 2;
         TH = std::min(TH, std::max(8, (Nx + 7) / 8 * 8));
         auto kern = k_blur_tile<T>;
-        static bool configured[MAX_DEVICES] = {false};
+        static std::atomic<bool> configured[MAX_DEVICES];      // zero-initialised; set once per device
         int dev = 0;
         cudaGetDevice(&dev);
         dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
@@ -1118,14 +1151,14 @@ int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, con
 
 int ofb_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
               const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
-              int* converged_out, int B, int Nx, int Ny, int dtype, void* stream) {
+              int* converged_out, double* recurrence_out, int B, int Nx, int Ny, int dtype, void* stream) {
     if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
     if (max_it < 0) return fail(-8, "max_it must be >= 0");
     return dtype == OFB_F32
                ? solve_impl<float>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
-                                   converged_out, B, Nx, Ny, stream)
+                                   converged_out, recurrence_out, B, Nx, Ny, stream)
                : solve_impl<double>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
-                                    converged_out, B, Nx, Ny, stream);
+                                    converged_out, recurrence_out, B, Nx, Ny, stream);
 }
 
 int ofb_precondition(const void* P, const void* r3, void* z3, const double* alpha, const double* beta, const ofb_solve_options* opt,
@@ -1248,15 +1281,15 @@ size_t ofb_slab_workspace_bytes(int B, int Ny, int dtype, const ofb_slab* slab) 
 
 int ofb_solve_slab(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, double rtol, int max_it,
                    const ofb_solve_options* opt, void* workspace, size_t workspace_bytes, int* iters_out, double* relres_out,
-                   int* converged_out, int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream) {
+                   int* converged_out, double* recurrence_out, int B, int Nx_local, int Ny, int dtype, const ofb_slab* slab, void* stream) {
     if (int rc = check_shape(B, std::max(Nx_local, 5), Ny, dtype)) return rc;
     if (slab == nullptr) return fail(-24, "bad slab descriptor");
     if (max_it < 0) return fail(-8, "max_it must be >= 0");
     return dtype == OFB_F32
                ? solve_impl<float>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
-                                   converged_out, B, Nx_local, Ny, stream, slab)
+                                   converged_out, recurrence_out, B, Nx_local, Ny, stream, slab)
                : solve_impl<double>(P, b3, x3, alpha, beta, rtol, max_it, opt, workspace, workspace_bytes, iters_out, relres_out,
-                                    converged_out, B, Nx_local, Ny, stream, slab);
+                                    converged_out, recurrence_out, B, Nx_local, Ny, stream, slab);
 }
 
 int ofb_epilogue_slab(const void* P, const void* C, const void* x3, void* vx, void* vy, void* speed, void* gamma, double* functionals,
@@ -1293,7 +1326,7 @@ int liu_shen_impl(const void* P, const void* C, void* vx, void* vy, void* speed,
                   int iterations, double scale, int B, int Nx, int Ny, cudaStream_t stream) {
     using Cfg = LsCfg<T>;
     auto kern = k_liu_shen_step<T>;
-    static bool configured[MAX_DEVICES] = {false};
+    static std::atomic<bool> configured[MAX_DEVICES];      // zero-initialised; set once per device
     const int dev = device_slot();
     if (!configured[dev]) {
         OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Cfg::SMEM));
@@ -1307,7 +1340,7 @@ int liu_shen_impl(const void* P, const void* C, void* vx, void* vy, void* speed,
     using S = LsStream<T>;
     auto skern = k_liu_shen_stream<T>;
     const bool streamed = vec_ok && Ny >= 64 && !getenv("OFB_LIU_SHEN_TILED");
-    static int stream_ctas[MAX_DEVICES] = {0};
+    static std::atomic<int> stream_ctas[MAX_DEVICES];
     int sgrid = 0, tiles_x = 0;
     if (streamed) {
         if (stream_ctas[dev] == 0) {
@@ -1361,7 +1394,7 @@ int adaptive_threshold_impl(const void* in, const double* movie_max, unsigned ch
     const int warps = (int)std::max<size_t>(1, std::min<size_t>(AT_ROW_WARPS, (96 * 1024) / per_warp));
     const size_t smem = per_warp * warps;
     if (smem > 200 * 1024) return fail(-6, "ofb_adaptive_threshold: rows of %d columns do not fit the prefix-sum buffer", Ny);
-    static bool configured[MAX_DEVICES] = {false};
+    static std::atomic<bool> configured[MAX_DEVICES];      // zero-initialised; set once per device
     const int dev = device_slot();
     if (!configured[dev]) {
         OFB_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));

@@ -158,10 +158,12 @@ class Workspace:
 _default_workspace = Workspace()
 
 
-def solve(P, b, x, speed_alpha, remodelling_alpha, rtol=1e-6, max_it=1000, options=None, workspace=None):
+def solve(P, b, x, speed_alpha, remodelling_alpha, rtol=1e-6, max_it=1000, options=None, workspace=None, recurrence=None):
     """K4/K5: solve A x = b in place (x: in = initial guess, out = solution).
 
-    Returns ``(iterations int32[B], relres float64[B], converged int32[B])`` as device tensors."""
+    Returns ``(iterations int32[B], relres float64[B], converged int32[B])`` as device tensors; ``relres`` is the true
+    residual |b - A x| / |b| of the returned x (reference :1150-1151).  ``recurrence`` (optional float64[B] device
+    tensor) receives the BiCGStab recurrence residual the iteration stopped on."""
     _require_cuda(P, b, x)
     B, Nx, Ny = P.shape
     assert b.shape == (B, 3, Nx, Ny) and x.shape == b.shape and b.dtype == P.dtype and x.dtype == P.dtype
@@ -174,7 +176,7 @@ def solve(P, b, x, speed_alpha, remodelling_alpha, rtol=1e-6, max_it=1000, optio
     conv = torch.zeros(B, dtype=torch.int32, device=P.device)
     _lib.check(_lib.load().ofb_solve(_ptr(P), _ptr(b), _ptr(x), _ptr(a), _ptr(be), float(rtol), int(max_it),
                                      ctypes.byref(options), _ptr(ws), nbytes, _ptr(iters), _ptr(relres), _ptr(conv),
-                                     B, Nx, Ny, _code(P), _stream_ptr(P.device)))
+                                     _ptr(recurrence), B, Nx, Ny, _code(P), _stream_ptr(P.device)))
     return iters, relres, conv
 
 

@@ -260,6 +260,7 @@ class FrameUploader:
 
     def _upload(self, frames_np, slot):
         try:
+            torch.cuda.set_device(self.device)          # helper thread: a fresh thread has device 0 current
             src = np.ascontiguousarray(frames_np)
             if self.events[slot] is not None:
                 self.events[slot].synchronize()         # the staging buffer is free once its previous copy has completed

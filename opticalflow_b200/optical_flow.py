@@ -19,6 +19,7 @@ Differences from the reference that a caller can observe (all documented in DESI
 Keyword-only extras (defaults preserve reference behaviour): ``dtype``, ``rtol``, ``max_it``,
 ``preconditioner``, ``device``, ``batch_pairs``, ``verbose``.
 """
+import functools
 import os
 import time
 
@@ -94,6 +95,23 @@ def _device(device):
     return torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
 
 
+def _on_device(fn):
+    """Run ``fn`` with the requested GPU as the calling thread's current CUDA device.  ``libofb200.so`` keys its per-device
+    state (SM count, occupancy, side stream, poll words, function attributes) on ``cudaGetDevice()`` and launches on the
+    stream torch made for that device; a fresh host thread - the ``devices=[...]`` driver starts one per GPU - has device 0
+    current, so every entry point sets the device itself."""
+    @functools.wraps(fn)
+    def wrapper(*args, **kwargs):
+        device = kwargs.get('device')
+        devices = kwargs.get('devices')
+        if device is None and devices is not None and len(devices) == 1:
+            device = devices[0]
+        with torch.cuda.device(_device(device)):
+            return fn(*args, **kwargs)
+    return wrapper
+
+
+@_on_device
 def blur_movie(movie, smoothing_sigma, *, dtype='float64', device=None):
     """Per-frame Gaussian blur (optical_flow.py:282-306), computed on the GPU, returned as float64."""
     dev = _device(device)
@@ -188,17 +206,18 @@ def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace,
     x = x0.clone()
     opts = engine.make_options(preconditioner, **solver_options)
     fallback = torch.zeros(B, dtype=torch.bool, device=P.device)
+    recur = torch.zeros(B, dtype=torch.float64, device=P.device)
     if opts.precond != _lib.PRECOND_MG:
-        iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace)
-        return x, iters, relres, conv, fallback
+        iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace, recurrence=recur)
+        return x, iters, relres, conv, fallback, recur
     # The cycle needs 6-10 iterations where it works; a pair still running after PROBE_IT iterations is in a regime
     # it does not handle, and the remaining budget is better spent on the fallbacks (which restart from x0 anyway).
     probe = min(int(max_it), PROBE_IT)
-    iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, probe, opts, workspace)
+    iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, probe, opts, workspace, recurrence=recur)
     if engine.last_unconverged() == 0:
         # every pair converged: no fallback, and no device->host read either - a read here would queue on the copy
         # engine behind the previous chunk's result planes (tens of ms for a 64-pair chunk)
-        return x, iters, relres, conv, fallback
+        return x, iters, relres, conv, fallback, recur
     passthrough = {k: v for k, v in solver_options.items() if k in ('check_every', 'rows_per_strip', 'flags')}
     robust = engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8, omega_pre=(0.8, 0.8), omega_post=(0.8, 0.8), **passthrough)
     chain = []                                      # (options, solve in float64, iteration budget)
@@ -221,17 +240,20 @@ def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace,
             bb, xb, ws = engine.build_rhs(Pb, Cb), x0[bad].double().contiguous(), engine.Workspace()
         else:
             Pb, bb, xb, ws = P[bad].contiguous(), b[bad].contiguous(), x0[bad].clone(), workspace
-        it2, rr2, cv2 = engine.solve(Pb, bb, xb, a_b, be_b, rtol, budget, fb_opts, ws)
+        rc2 = torch.zeros(bad.numel(), dtype=torch.float64, device=P.device)
+        it2, rr2, cv2 = engine.solve(Pb, bb, xb, a_b, be_b, rtol, budget, fb_opts, ws, recurrence=rc2)
         better = (cv2 == 1) | (rr2 < relres[bad])
         sel = bad[better]
         x[sel] = xb[better].to(x.dtype)
         iters[sel] = it2[better] + iters[sel]
         relres[sel] = rr2[better]
+        recur[sel] = rc2[better]
         conv[sel] = cv2[better]
         fallback[sel] = True
-    return x, iters, relres, conv, fallback
+    return x, iters, relres, conv, fallback, recur
 
 
+@_on_device
 def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, remodelling_alpha=1000.0,
                              smoothing_sigma=None, initial_v_x=0.0, initial_v_y=0.0, initial_remodelling=0.0,
                              use_direct_solver=False, *, dtype='float64', rtol=1e-6, max_it=1000,
@@ -302,8 +324,10 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         out = {k: arena.alloc((n_pairs, Nx, Ny), np.float64) for k in result_names}
         blurred = arena.alloc((T, Nx, Ny), np.float64) if blur else original
     functionals = np.zeros((n_pairs, 3))
+    # relative_residual: |b - A x| / |b| recomputed from the returned x (what the reference prints, :1150-1151);
+    # recurrence_residual: the solver's own norm when it stopped (:1140-1142)
     info = dict(iterations=np.zeros(n_pairs, np.int32), relative_residual=np.zeros(n_pairs),
-                converged=np.zeros(n_pairs, bool), fallback=np.zeros(n_pairs, bool))
+                recurrence_residual=np.zeros(n_pairs), converged=np.zeros(n_pairs, bool), fallback=np.zeros(n_pairs, bool))
     workspace = engine.Workspace()
     nplanes = 5 if blur else 4                                                 # v_x, v_y, speed, remodelling (, blurred)
     main_stream = torch.cuda.current_stream(dev)
@@ -343,8 +367,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
             for q in range(3):
                 x0[:, q] = guess[q]
             t_prep = time.perf_counter()
-            x, iters, relres, conv, fb = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
-                                                      preconditioner, workspace, solver_options)
+            x, iters, relres, conv, fb, recur = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
+                                                             preconditioner, workspace, solver_options)
             t_solve = time.perf_counter()
             fields = slot['dev'][:4, :nb]
             _, _, _, _, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out, out=fields)
@@ -386,7 +410,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                 copies.append((original[k0:k0 + last_frame], source[k0:k0 + last_frame]))      # float64 copy of the input (:769)
                 slot['busy'] = worker.submit(copied, copies)       # slot reuse (three chunks later) waits for this on the host
             stats.append(torch.cat([fun, iters.double()[:, None], relres[:, None], conv.double()[:, None],
-                                    fb.double()[:, None]], dim=1))
+                                    fb.double()[:, None], recur[:, None]], dim=1))
             timeline.append(dict(chunk=c, wait_slot_and_frames=t_take - t_chunk, prepare=t_prep - t_take,
                                  solve=t_solve - t_prep, submit=time.perf_counter() - t_solve))
         t_loop = time.perf_counter()
@@ -396,6 +420,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         info['relative_residual'][:] = packed[:, 4]
         info['converged'][:] = packed[:, 5] != 0
         info['fallback'][:] = packed[:, 6] != 0
+        info['recurrence_residual'][:] = packed[:, 7]
         if verbose:
             print('iterations %s, residuals %s' % (info['iterations'], info['relative_residual']))
         t_stats = time.perf_counter()
@@ -406,13 +431,21 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                 slot['original'].wait()
         timeline.append(dict(stats=t_stats - t_loop, drain=time.perf_counter() - t_stats, setup=t_setup - t_start))
     finally:
-        worker.close()
-        torch.cuda.current_stream(dev).synchronize()
-        copy_stream.synchronize()
-        uploader.close()
-        for slot in slots:
-            if slot['pin'] is not None:
-                hostio.pinned_pool.release(slot['pin'])
+        # nothing may still be writing into the result arrays or the staging slots when they are handed back; an egress
+        # worker error (re-raised by close()) comes last so that it cannot skip the other steps
+        try:
+            torch.cuda.current_stream(dev).synchronize()
+            copy_stream.synchronize()
+        finally:
+            try:
+                uploader.close()
+            finally:
+                try:
+                    for slot in slots:
+                        if slot['pin'] is not None:
+                            hostio.pinned_pool.release(slot['pin'])
+                finally:
+                    worker.close()
     if verbose and not info['converged'].all():
         print('the solver has not actually converged, the result will be incorrect or inaccurate')
     result = dict()
@@ -441,6 +474,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     return result
 
 
+@_on_device
 def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
                         remodelling_alpha_values=np.arange(500, 2000, 500), filename=None, **kwargs):
     """Grid of regularisation weights -> summary statistics (optical_flow.py:1918-1998).
@@ -494,8 +528,8 @@ def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
                 x0[:, q] = guess[q]
             a = torch.from_numpy(cell_alpha[c0:c1]).to(dev)
             be = torch.from_numpy(cell_beta[c0:c1]).to(dev)
-            x, iters, relres, conv, fb = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace,
-                                                      solver_options)
+            x, iters, relres, conv, fb, _ = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace,
+                                                         solver_options)
             _, _, _, _, fun, mom = engine.epilogue(P, C, x, a, be, float(delta_x) / float(delta_t))
             moments[c0:c1] += mom.cpu().numpy()
             fun = fun.cpu().numpy()
@@ -533,6 +567,7 @@ def _to_device_float(movie, dev, dtype=None):
     return hostio.as_native_tensor(movie).to(dev).to(tdtype)
 
 
+@_on_device
 def apply_adaptive_threshold(movie, window_size=51, threshold=0.0, *, device=None):
     """OpenCV mean adaptive threshold of every frame (optical_flow.py:308-338), on the GPU.
 
@@ -544,6 +579,7 @@ def apply_adaptive_threshold(movie, window_size=51, threshold=0.0, *, device=Non
     return engine.adaptive_threshold(frames, window_size, threshold).cpu().numpy()
 
 
+@_on_device
 def apply_clahe(movie, clipLimit=50000, tile_number=10, *, device=None, verbose=False):
     """OpenCV CLAHE of every frame on ``movie.astype(uint16)`` (optical_flow.py:340-374), on the GPU.
 
@@ -561,6 +597,7 @@ def apply_clahe(movie, clipLimit=50000, tile_number=10, *, device=None, verbose=
     return out
 
 
+@_on_device
 def subtract_background(movie, background, *, thresholding_sigma=10, dtype='float64', device=None):
     """Background subtraction of ``conduct_optical_flow`` (optical_flow.py:195-198; inline there, a function here):
     ``movie - background`` where the ``sigma=10`` blur of the movie exceeds ``background``, 0 elsewhere."""
@@ -584,6 +621,7 @@ def _guess(value, n_pairs, Nx, Ny):
     return plane
 
 
+@_on_device
 def liu_shen_optical_flow_jit(movie, delta_x=1.0, delta_t=1.0, alpha=100, remodelling_alpha=1.0, initial_v_x=None,
                               initial_v_y=None, initial_remodelling=None, max_iterations=10, tolerance=1e-9,
                               include_remodelling=True, *, dtype='float64', device=None, batch_pairs=None):

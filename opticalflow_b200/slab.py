@@ -117,7 +117,7 @@ def solve_slab(P_ext, C_ext, slab, speed_alpha, remodelling_alpha, rtol=1e-6, ma
     conv = torch.zeros(1, dtype=torch.int32, device=dev)
     _lib.check(lib.ofb_solve_slab(engine._ptr(P), engine._ptr(b), engine._ptr(x), engine._ptr(a), engine._ptr(be), float(rtol),
                                   int(max_it), ctypes.byref(opt), engine._ptr(ws), nbytes, engine._ptr(iters), engine._ptr(relres),
-                                  engine._ptr(conv), 1, Nx_loc, Ny, code, ctypes.byref(slab), engine._stream_ptr(dev)))
+                                  engine._ptr(conv), None, 1, Nx_loc, Ny, code, ctypes.byref(slab), engine._stream_ptr(dev)))
     return x, iters, relres, conv
 
 

@@ -114,7 +114,40 @@ def make_legacy():
     print('legacy_callers', {k: v.shape for k, v in payload.items() if k.endswith('_out') or k.endswith('_vx')})
 
 
+def make_large():
+    """One frame pair at a BENCH size through the unmodified reference (config d-2: 512^2 actin-like movie, about five
+    minutes and 7 GB in SuperLU).  The full fields would be 6 MB; the fixture keeps every 8th pixel, the central 64 x 64
+    block and the three outermost rows/columns of each field (the boundary overwrite), which pins a global solve."""
+    import time
+    movie = synthetic.actin_like_movie(512, 512, 2, seed=1)
+    kwargs = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.5)
+    t0 = time.perf_counter()
+    result, residuals, log = ref_import.reference_solve(movie, **kwargs)
+    seconds = time.perf_counter() - t0
+    payload = dict(residuals=np.asarray(residuals), reference_seconds=np.array(seconds),
+                   movie_checksum=np.array([movie.sum(), (movie ** 2).sum()]),
+                   functionals=np.array([result['L1_functional'], result['remodelling_functional'], result['speed_functional']]))
+    for key in ('v_x', 'v_y', 'speed', 'remodelling'):
+        f = result[key][0]
+        payload[key + '_sub8'] = f[::8, ::8].copy()
+        payload[key + '_centre'] = f[224:288, 224:288].copy()
+        payload[key + '_top'] = f[:3].copy(); payload[key + '_bottom'] = f[-3:].copy()
+        payload[key + '_left'] = f[:, :3].copy(); payload[key + '_right'] = f[:, -3:].copy()
+        payload[key + '_norm'] = np.array(np.linalg.norm(f))
+    for k, v in kwargs.items():
+        payload['kw_' + k] = np.array(v, dtype=np.float64)
+    np.savez_compressed(os.path.join(GOLDEN, 'actin512_pair0_sample.npz'), **payload)
+    phases = [line for line in log.splitlines() if 'took' in line or 'time' in line.lower()]
+    print('actin512_pair0_sample: %.1f s in the reference, residual %.2e' % (seconds, max(residuals)))
+    print('\n'.join(phases[:12]))
+
+
 if __name__ == '__main__':
+    if '--large-only' in sys.argv:
+        make_large()
+        sys.exit(0)
     if '--legacy-only' not in sys.argv:
         main()
     make_legacy()
+    if '--large' in sys.argv:
+        make_large()

@@ -39,7 +39,7 @@ def test_bad_arguments_are_reported_not_crashed(built_library):
     assert b'5x5' in built_library.ofb_last_error()
     rc = built_library.ofb_build_rhs(None, None, None, 0, 64, 64, _lib.OFB_F32, None)
     assert rc < 0 and b'batch' in built_library.ofb_last_error()
-    rc = built_library.ofb_solve(None, None, None, None, None, 1e-6, 10, None, None, 0, None, None, None,
+    rc = built_library.ofb_solve(None, None, None, None, None, 1e-6, 10, None, None, 0, None, None, None, None,
                                  1, 64, 64, 7, None)
     assert rc < 0 and b'dtype' in built_library.ofb_last_error()
 

@@ -24,7 +24,8 @@ def load_golden(name):
 
 
 GOLDEN_NAMES = sorted(os.path.splitext(os.path.basename(p))[0] for p in glob.glob(os.path.join(GOLDEN_DIR, '*.npz'))
-                      if not os.path.basename(p).startswith('legacy_'))      # legacy_*.npz: tests/test_legacy_*.py
+                      if not os.path.basename(p).startswith('legacy_')        # legacy_*.npz: tests/test_legacy_*.py
+                      and not os.path.basename(p).endswith('_sample.npz'))    # samples of bench-size solves: -m gpu tests
 
 
 def test_golden_fixtures_exist():
