@@ -223,6 +223,24 @@ int ofb_widen(const void* in_f32, void* out_f64, long long n, void* stream);
 int ofb_subtract_background(const void* movie, const void* blurred, void* out, double background, long long n,
                             int dtype, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * ofb_blur as the two-launch separable blur (axis 0 then axis 1, the order of scipy.ndimage.gaussian_filter), with
+ * the intermediate plane in a file-scope device array of OFB_BLUR_NOALLOC_MAX_BYTES inside the library instead of a
+ * caller-provided `tmp`.  The call allocates nothing (no cudaMalloc/cudaFree, no allocating library routine); the
+ * caller still passes in, out and the device array of 2*radius+1 normalised weights.  Limits and sharing:
+ *   - F*Nx*Ny*sizeof(dtype) must not exceed OFB_BLUR_NOALLOC_MAX_BYTES (16 MiB: four 1024^2 float32 frames, two
+ *     float64 ones); larger requests return -12 with a message, use ofb_blur there;
+ *   - every GPU that loads the library holds the array until the process exits;
+ *   - all calls on a GPU share it and it keeps the last call's contents (the first pass overwrites every element the
+ *     second reads, so nothing needs clearing); two calls that overlap on one GPU - different streams, or different
+ *     host threads - race on it: serialise them. */
+#define OFB_BLUR_NOALLOC_MAX_BYTES (16u << 20)
+int ofb_blur_noalloc(const void* in, void* out, const double* weights, int radius,
+                     int F, int Nx, int Ny, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

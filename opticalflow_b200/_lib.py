@@ -28,7 +28,8 @@ EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
                     'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab',
                     'ofb_liu_shen', 'ofb_movie_max', 'ofb_adaptive_threshold', 'ofb_clahe_workspace_bytes', 'ofb_clahe',
-                    'ofb_subtract_background', 'ofb_widen')
+                    'ofb_subtract_background', 'ofb_widen', 'ofb_blur_noalloc')
+BLUR_NOALLOC_MAX_BYTES = 16 << 20
 
 
 class SolveOptions(ctypes.Structure):
@@ -128,6 +129,8 @@ def load():
     lib.ofb_widen.argtypes = [vp, vp, ll, vp]
     lib.ofb_subtract_background.restype = i
     lib.ofb_subtract_background.argtypes = [vp, vp, vp, d, ll, i, vp]
+    lib.ofb_blur_noalloc.restype = i
+    lib.ofb_blur_noalloc.argtypes = [vp, vp, dp, i, i, i, i, i, vp]
     if lib.ofb_version() != ABI_VERSION:
         raise OfbError('libofb200.so ABI version %d != expected %d' % (lib.ofb_version(), ABI_VERSION))
     _lib = lib

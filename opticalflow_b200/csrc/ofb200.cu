@@ -1520,3 +1520,64 @@ int ofb_subtract_background(const void* movie, const void* blurred, void* out, d
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// Allocation-free variant (no counterpart in the reference)
+// =====================================================================================================
+// Callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc) get the
+// two-pass Gaussian blur with its intermediate plane in a file-scope device array instead of a caller buffer.
+// Every GPU that loads the library holds OFB_BLUR_NOALLOC_MAX_BYTES until the process exits.  All calls share the
+// array: it keeps the last call's contents (pass 1 overwrites every element pass 2 reads, so nothing needs clearing)
+// and calls that overlap on one GPU race on it.
+namespace {
+
+static __device__ __align__(256) unsigned char g_blur_scratch[OFB_BLUR_NOALLOC_MAX_BYTES];
+
+// In host code `g_blur_scratch` is a host-side stand-in, not a device address: resolve the address once per device,
+// with that device current, and hand the kernels the resolved pointer.
+int blur_scratch_address(void** out) {
+    static std::atomic<void*> resolved[MAX_DEVICES];          // zero-initialised
+    int dev = 0;
+    OFB_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return fail(-11, "device ordinal %d out of range", dev);
+    void* p = resolved[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        OFB_CHECK_CUDA(cudaGetSymbolAddress(&p, g_blur_scratch));
+        if (p == nullptr) return fail(-11, "cudaGetSymbolAddress returned a null scratch address");
+        resolved[dev].store(p, std::memory_order_release);
+    }
+    *out = p;
+    return 0;
+}
+
+template <typename T>
+int blur_noalloc_impl(const void* in, void* out, void* scratch, const double* weights, int radius, int F, int Nx, int Ny,
+                      cudaStream_t stream) {
+    const long long fs = (long long)Nx * Ny;
+    dim3 block(128), grid((Ny + 127) / 128, Nx, F);
+    k_blur_axis<T, 0><<<grid, block, 0, stream>>>((const T*)in, (T*)scratch, Nx, Ny, fs, weights, radius);
+    OFB_CHECK_LAUNCH();
+    k_blur_axis<T, 1><<<grid, block, 0, stream>>>((const T*)scratch, (T*)out, Nx, Ny, fs, weights, radius);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int ofb_blur_noalloc(const void* in, void* out, const double* weights, int radius, int F, int Nx, int Ny, int dtype,
+                                void* stream) {
+    if (F < 1 || Nx < 1 || Ny < 1) return fail(-1, "ofb_blur_noalloc: bad shape %d x %d x %d", F, Nx, Ny);
+    if (dtype != OFB_F32 && dtype != OFB_F64) return fail(-3, "dtype must be OFB_F32 or OFB_F64 (got %d)", dtype);
+    if (radius < 0 || !weights || !in || !out) return fail(-6, "ofb_blur_noalloc: null pointer or negative radius");
+    if (in == out) return fail(-7, "ofb_blur_noalloc: in/out must not alias");
+    if (Ny > 65535 * 128 || Nx > 65535 || F > 65535) return fail(-1, "ofb_blur_noalloc: shape %d x %d x %d exceeds the launch grid", F, Nx, Ny);
+    const unsigned long long need = (unsigned long long)F * Nx * Ny * (dtype == OFB_F32 ? 4ull : 8ull);
+    if (need > (unsigned long long)OFB_BLUR_NOALLOC_MAX_BYTES)
+        return fail(-12, "ofb_blur_noalloc: %d x %d x %d frames need %llu bytes of scratch, the built-in array holds %llu "
+                         "(OFB_BLUR_NOALLOC_MAX_BYTES); use ofb_blur with a caller-provided tmp", F, Nx, Ny, need,
+                    (unsigned long long)OFB_BLUR_NOALLOC_MAX_BYTES);
+    void* scratch = nullptr;
+    if (int rc = blur_scratch_address(&scratch)) return rc;
+    return dtype == OFB_F32 ? blur_noalloc_impl<float>(in, out, scratch, weights, radius, F, Nx, Ny, (cudaStream_t)stream)
+                            : blur_noalloc_impl<double>(in, out, scratch, weights, radius, F, Nx, Ny, (cudaStream_t)stream);
+}
