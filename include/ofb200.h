@@ -46,6 +46,8 @@ extern "C" {
 #define OFB_FLAG_SERIAL_SETUP 256 /* dense coarsest-level inverse on the solve's own stream instead of beside the first fine sweeps (A/B) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 
+#define OFB_FLAG_POLL_AHEAD 1024 /* ofb_solve: enqueue iteration k+1 before reading iteration k's convergence count (measured slower: off by default) */
+
 #define OFB_ABI_VERSION 5
 
 typedef struct ofb_solve_options {
@@ -72,6 +74,8 @@ long long   ofb_launch_count(void);
 /* number of pairs the calling thread's last ofb_solve / ofb_solve_slab left unconverged (-1: unknown); lets a caller
  * skip its fallback logic without reading converged_out back from the device */
 int         ofb_last_unconverged(void);
+/* number of pairs the calling thread's last ofb_solve / ofb_solve_slab restarted from their true residual (ofb_solve) */
+int         ofb_last_restarts(void);
 
 /* Bytes of device workspace ofb_solve needs for this shape (caller allocates, contents need not be zeroed). */
 size_t ofb_workspace_bytes(int B, int Nx, int Ny, int dtype, int precond);
@@ -111,9 +115,12 @@ int ofb_smooth(const void* P, const void* b3, const void* x_in, void* x_out, con
  *       relres_out      |b - A x| / |b| RECOMPUTED from the returned x in fp64 arithmetic - the independent residual the
  *                       reference prints at :1150-1151;
  *       recurrence_out  the BiCGStab recurrence residual the iteration stopped on (the KSP's own norm, :1140-1142);
- *       converged_out   1 when the true residual passes  |b - A x| <= rtol |b| + 2 u |D x|  (u = unit round-off of
- *                       `dtype`, D = diagonal of A: the part of the residual that rounding x to `dtype` leaves behind;
- *                       negligible in float64, ~3e-5 |b| in float32 at alpha = 1e5);
+ *       converged_out   1 when the true residual passes  |b - A x| <= rtol |b| + 8 u |D x|  (u = unit round-off of
+ *                       `dtype`, D = diagonal of A; a row of A carries about four times its diagonal in absolute
+ *                       off-diagonals, so 8 u |D x| ~ 2 u |A| |x|: the residual that storing x and the iterates in
+ *                       `dtype` leaves behind whatever the solver does - negligible in float64, a few 1e-5 |b| in
+ *                       float32 at alpha = 1e5, where the KSP's own test (the recurrence residual, which is what the
+ *                       reference's `converged` reports, :1135-1138) still reaches rtol);
  *       iters_out       BiCGStab iterations.
  *     A pair whose recurrence converged (or broke down) while its true residual does not pass is restarted from
  *     r = b - A x, at most twice. */

@@ -20,10 +20,11 @@ FLAG_STRIP_ITEMS = 64
 FLAG_NO_HALF_STEP_EXIT = 128
 FLAG_SERIAL_SETUP = 256
 FLAG_FUSED_PROLONG = 512
+FLAG_POLL_AHEAD = 1024
 ABI_VERSION = 5
 
 # every symbol include/ofb200.h declares
-EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_last_unconverged', 'ofb_workspace_bytes', 'ofb_blur',
+EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_last_unconverged', 'ofb_last_restarts', 'ofb_workspace_bytes', 'ofb_blur',
                     'ofb_build_rhs', 'ofb_apply', 'ofb_apply_eliminated', 'ofb_smooth', 'ofb_solve', 'ofb_precondition',
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
                     'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab',
@@ -75,6 +76,8 @@ def load():
     lib.ofb_launch_count.argtypes = []
     lib.ofb_last_unconverged.restype = i
     lib.ofb_last_unconverged.argtypes = []
+    lib.ofb_last_restarts.restype = i
+    lib.ofb_last_restarts.argtypes = []
     lib.ofb_workspace_bytes.restype = sz
     lib.ofb_workspace_bytes.argtypes = [i, i, i, i, i]
     lib.ofb_blur.restype = i

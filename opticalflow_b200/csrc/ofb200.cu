@@ -389,6 +389,7 @@ inline PollBox* poll_box() {
     return &b;
 }
 thread_local int g_last_unconverged = -1;
+thread_local int g_last_restarts = 0;         // pairs the calling thread's last solve restarted from their true residual
 
 template <typename T> struct Solver {
     int B;
@@ -855,7 +856,32 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         }
         return 0;
     };
+    // OFB_FLAG_POLL_AHEAD: the host stays one iteration ahead of the device - iteration k+1 is enqueued BEFORE iteration
+    // k's count of running pairs is read (from the mapped word its k_publish wrote, after an event, no stream
+    // synchronisation), so the device never waits for the host at an iteration boundary; every kernel honours the
+    // per-pair activity mask, so the surplus iteration that is already queued when the count reads 0 runs as no-ops.
+    // Measured on the B200 (64 pairs of 1024^2, profiles/r02_poll_ahead_ab.txt): 68.8 vs 67.7 ms per step on one GPU,
+    // 80.1 vs 78.2 ms on two - the ~58 empty launches of the surplus iteration (~17 us each: 444 persistent CTAs set up
+    // their rings) cost more than the bubble they remove, which is ~0.3 ms per iteration because the host enqueues an
+    // iteration 30x faster than the device runs it.  Off by default.
+    struct PollEvents {
+        cudaEvent_t ev[2] = {nullptr, nullptr};
+        ~PollEvents() { for (cudaEvent_t e : ev) if (e != nullptr) cudaEventDestroy(e); }
+    } pe;
+    bool ahead = box != nullptr && (S.opt.flags & OFB_FLAG_POLL_AHEAD) != 0;
+    if (ahead)
+        for (int k = 0; k < 2; ++k)
+            if (cudaEventCreateWithFlags(&pe.ev[k], cudaEventDisableTiming) != cudaSuccess) { cudaGetLastError(); pe.ev[k] = nullptr; ahead = false; }
+    int pending = -1;                   // iteration whose count has been published but not read yet
+    auto read_pending = [&]() -> int {
+        if (pending < 0) return 0;
+        OFB_CHECK_CUDA(cudaEventSynchronize(pe.ev[pending & 1]));
+        host_active = *(volatile int*)(box->host + 4 + (pending & 1));
+        pending = -1;
+        return 0;
+    };
     int it = 0;
+    g_last_restarts = 0;
     for (int round = 0;; ++round) {
     for (; it < max_it && host_active > 0; ++it) {
         T *ph = nullptr, *sh = nullptr;
@@ -893,8 +919,20 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         if (poll) OFB_CHECK_CUDA(cudaMemsetAsync(w.n_active, 0, sizeof(int), stream));
         if ((rc = S.allreduce_acc())) return rc;
         OFB_LAUNCH(S.pdl(), k_scalars, dim3(sb), dim3(128), 0, stream, w.st, w.active, B, 3, rtol, max_it, poll ? w.n_active : (int*)nullptr);
-        if (poll && (rc = read_counter(w.n_active, 0, &host_active))) return rc;
+        if (!ahead) {
+            if (poll && (rc = read_counter(w.n_active, 0, &host_active))) return rc;
+            continue;
+        }
+        if (poll) {
+            k_publish<<<1, 1, 0, stream>>>(w.n_active, box->dev + 4 + (it & 1));
+            OFB_CHECK_LAUNCH();
+            OFB_CHECK_CUDA(cudaEventRecord(pe.ev[it & 1], stream));
+        }
+        if ((rc = read_pending())) return rc;            // the previous poll: this iteration is already queued behind it
+        if (poll) pending = it;
     }
+    if (host_active > 0 && (rc = read_pending())) return rc;
+    pending = -1;
     {   // complete the ghost ring: x now solves the reference's full system, boundary rows included
         const int ring = 2 * Nx + 2 * Ny;
         k_fill_ghosts<T><<<dim3((ring + 127) / 128, B), 128, 0, stream>>>(g0, x);
@@ -913,6 +951,7 @@ int solve_impl(const void* P, const void* b3, void* x3, const double* alpha, con
         int reactivated = 0;
         if (max_it > 0 && it < max_it && round < MAX_RESTARTS) { if ((rc = read_counter(w.n_active + 2, 2, &reactivated))) return rc; }
         if (reactivated == 0) break;
+        g_last_restarts += reactivated;
         // restart BiCGStab for the re-activated pairs from the true residual: r = rhat = b - S x
         S.active = w.active;
         OpResidual<T, true> op; op.g = g0; op.cen[0] = b; op.r = w.r; op.r2 = w.rhat; op.st = w.st; op.acc[0] = 0.0;
@@ -1082,6 +1121,8 @@ const char* ofb_last_error(void) { return g_error; }
 long long ofb_launch_count(void) { return g_launches.load(); }
 
 int ofb_last_unconverged(void) { return g_last_unconverged; }
+
+int ofb_last_restarts(void) { return g_last_restarts; }
 
 void ofb_default_options(ofb_solve_options* opt) {
     if (!opt) return;

@@ -295,10 +295,10 @@ __global__ void k_scalars(PairState* __restrict__ st, int* __restrict__ active_a
 }
 
 // After the loop: judge every pair on the TRUE residual of its x (acc[0] = |b - A x|^2, acc[1] = |D x|^2 from
-// k_true_residual).  A pair passes when |b - A x| <= rtol |b| + 2 u |D x| - the normwise backward-error form of the
-// reference's test (:1120, :1150-1151): x is stored in a type with unit round-off u, and rounding a perfect solution to
-// that type already leaves ~u |D x| in the residual (float32, alpha = 1e5: ~3e-5 |b|), so the recurrence residual can
-// reach rtol while the true one cannot.  A pair that fails although its recurrence converged, or whose recurrence broke
+// k_true_residual).  A pair passes when |b - A x| <= rtol |b| + 8 u |D x| - the normwise backward-error form of the
+// reference's test (:1120, :1150-1151): x and the iterates are stored in a type with unit round-off u, which leaves
+// ~2 u |A| |x| ~ 8 u |D x| in the residual whatever the solver does (float32, alpha = 1e5: a few 1e-5 |b|), so the
+// recurrence residual can reach rtol while the true one cannot.  A pair that fails although its recurrence converged, or whose recurrence broke
 // down, is re-activated (at most MAX_RESTARTS times): the loop restarts BiCGStab from x with r := b - A x.
 constexpr int MAX_RESTARTS = 2;
 __global__ void k_verify(PairState* __restrict__ st, int* __restrict__ active_arr, int B, double rtol, int max_it, double unit_roundoff,
@@ -308,7 +308,7 @@ __global__ void k_verify(PairState* __restrict__ st, int* __restrict__ active_ar
     PairState s = st[pair];
     s.true_relres = (s.bnorm > 0.0) ? sqrt(s.acc[0]) / s.bnorm : 0.0;
     s.floor_relres = (s.bnorm > 0.0) ? unit_roundoff * sqrt(s.acc[1]) / s.bnorm : 0.0;
-    const bool ok = isfinite(s.true_relres) && s.true_relres <= rtol + 2.0 * s.floor_relres;
+    const bool ok = isfinite(s.true_relres) && s.true_relres <= rtol + 8.0 * s.floor_relres;
     s.active = 0;
     if (ok) s.status = ST_CONVERGED;
     else if (s.status == ST_CONVERGED || s.status == ST_BREAKDOWN) {

@@ -185,6 +185,11 @@ def last_unconverged():
     return int(_lib.load().ofb_last_unconverged())
 
 
+def last_restarts():
+    """Pairs the calling thread's last ``solve`` restarted from their true residual (a host integer)."""
+    return int(_lib.load().ofb_last_restarts())
+
+
 def precondition(P, r, speed_alpha, remodelling_alpha, options=None, workspace=None):
     """One application z = M^-1 r of the solver's preconditioner (diagnostics/tests)."""
     _require_cuda(P, r)

@@ -112,6 +112,18 @@ def parallel_copy(pairs, piece_bytes=4 << 20):
         f.result()
 
 
+def speed_from_velocities(v_x, v_y, out, piece_bytes=4 << 20):
+    """out = sqrt(v_x^2 + v_y^2) (optical_flow.py:1191) on the host copy pool, in pieces.  ``speed`` is a function of two
+    arrays that cross the host link anyway; computing it here instead of shipping it takes 8 of the 42 MB per 1024^2 pair
+    off that link, which is what bounds the call once several GPUs share one host (profiles/r02_d2h_ceiling.txt)."""
+    pool = copy_pool()
+    a, b, o = v_x.reshape(-1), v_y.reshape(-1), out.reshape(-1)
+    step = max(1, piece_bytes // o.itemsize)
+    futures = [pool.submit(np.hypot, a[k:k + step], b[k:k + step], o[k:k + step]) for k in range(0, o.size, step)]
+    for f in futures:
+        f.result()
+
+
 def _helper_threads(divisor):
     """CPU copy threads for a helper thread: a share of the cores, so that ingest, egress and the kernel-launching
     thread do not oversubscribe the host."""
@@ -169,6 +181,27 @@ def _page_locked_buffer(nbytes):
     return buf[:nbytes] if nbytes > 0 else buf[:0]
 
 
+def _host_ram_bytes():
+    try:
+        return os.sysconf('SC_PAGE_SIZE') * os.sysconf('SC_PHYS_PAGES')
+    except (ValueError, OSError):
+        return 64 << 30
+
+
+def _ranks_on_this_host():
+    return max(1, int(os.environ.get('LOCAL_WORLD_SIZE', '1') or 1))
+
+
+def direct_egress_limit():
+    """Bytes of result arrays one call may page-lock for direct egress (OFB_DIRECT_EGRESS_BYTES): by default a quarter of
+    the host's RAM shared by the ranks on it, at least 16 GiB and at most 96 GiB - the 500-frame 1024^2 movie of
+    config d-3 returns 25 GB of float64."""
+    env = os.environ.get('OFB_DIRECT_EGRESS_BYTES')
+    if env:
+        return int(env)
+    return int(min(96 << 30, max(16 << 30, _host_ram_bytes() // 4 // _ranks_on_this_host())))
+
+
 class ResultArena:
     """Recycles the memory of result arrays the caller has dropped.
 
@@ -177,16 +210,12 @@ class ResultArena:
     widening itself.  `alloc` hands out arrays carved from buffers whose previous arrays are all gone (a weakref
     finalizer on the carrier view returns the buffer), so a caller that processes movie after movie - or calls in a
     loop - writes into pages that are already mapped.  Contents are uninitialised, like numpy.empty.  At most
-    `max_idle_bytes` are kept while idle (OFB_RESULT_ARENA_BYTES, default min(32 GiB, RAM/8); 0 disables recycling)."""
+    `max_idle_bytes` are kept while idle - page-locked buffers included, which are unregistered when they are dropped
+    (OFB_RESULT_ARENA_BYTES, default min(48 GiB, RAM / 4 / ranks on this host); 0 disables recycling)."""
 
     def __init__(self, max_idle_bytes=None):
-        import os
         if max_idle_bytes is None:
-            try:
-                ram = os.sysconf('SC_PAGE_SIZE') * os.sysconf('SC_PHYS_PAGES')
-            except (ValueError, OSError):
-                ram = 64 << 30
-            max_idle_bytes = int(os.environ.get('OFB_RESULT_ARENA_BYTES', min(32 << 30, ram // 8)))
+            max_idle_bytes = int(os.environ.get('OFB_RESULT_ARENA_BYTES', min(48 << 30, _host_ram_bytes() // 4 // _ranks_on_this_host())))
         self.max_idle_bytes = int(max_idle_bytes)
         self.free = []                       # idle uint8 buffers
         self.free_pinned = []                # idle page-locked uint8 buffers
@@ -315,23 +344,27 @@ class EgressWorker:
             task = self.tasks.get()
             if task is None:
                 return
-            event, copies, done = task
+            event, copies, post, done = task
             try:
                 t0 = time.perf_counter()
                 if event is not None:
                     event.synchronize()
                 t1 = time.perf_counter()
-                parallel_copy([(dst_np, src_t.numpy() if isinstance(src_t, torch.Tensor) else src_t) for dst_np, src_t in copies])
+                if copies:
+                    parallel_copy([(dst_np, src_t.numpy() if isinstance(src_t, torch.Tensor) else src_t) for dst_np, src_t in copies])
+                if post is not None:
+                    post()
                 self.log.append((t1 - t0, time.perf_counter() - t1))
             except Exception as exc:                    # surfaced by close()
                 self.error = exc
             finally:
                 done.set()
 
-    def submit(self, event, copies):
-        """copies: list of (destination numpy view, source CPU tensor).  Returns a threading.Event set when done."""
+    def submit(self, event, copies, post=None):
+        """copies: list of (destination numpy view, source CPU tensor); post: a callable run after them (both after
+        `event`, a CUDA event, has completed).  Returns a threading.Event set when done."""
         done = threading.Event()
-        self.tasks.put((event, copies, done))
+        self.tasks.put((event, copies, post, done))
         return done
 
     def close(self):

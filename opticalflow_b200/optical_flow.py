@@ -258,7 +258,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                              smoothing_sigma=None, initial_v_x=0.0, initial_v_y=0.0, initial_remodelling=0.0,
                              use_direct_solver=False, *, dtype='float64', rtol=1e-6, max_it=1000,
                              preconditioner='mg', device=None, batch_pairs=None, verbose=False,
-                             solver_options=None, devices=None):
+                             solver_options=None, devices=None, result_dtype='float64', outputs=None):
     """Variational optical flow with net remodelling on every consecutive frame pair of ``movie``.
 
     Signature, defaults, units and result keys follow optical_flow.py:715-1210: ``movie[T,Nx,Ny]``; velocities
@@ -268,13 +268,21 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     The frame pairs are processed in chunks of ``batch_pairs``: while the device solves chunk k+1, chunk k's
     planes travel device -> pinned memory on a copy stream and are widened to float64 by a worker thread.
     ``devices=[...]`` shards the pairs over several GPUs (contiguous ranges, one host thread per device, no
-    collective; sharding.py)."""
+    collective; sharding.py).
+
+    The reference returns ~42 MB of float64 per 1024^2 pair (:1189-1205); at several hundred pairs per second and GPU
+    that is what the host link carries, not the solve.  Two opt-in keywords cut it (defaults keep the reference's
+    dictionary): ``result_dtype='float32'`` returns the field arrays, ``blurred_data`` and ``original_data`` as
+    float32 (``original_data`` is then the caller's movie itself when that already is float32);
+    ``outputs=('v_x', 'v_y', 'remodelling')`` names the arrays to ship - keys left out of
+    ``('v_x', 'v_y', 'speed', 'remodelling', 'blurred_data', 'original_data')`` are absent from the result
+    (``speed`` is ``np.hypot(v_x, v_y)``, ``blurred_data`` is ``blur_movie(movie, smoothing_sigma)``)."""
     if devices is not None and len(devices) > 1:
         kw = dict(delta_x=delta_x, delta_t=delta_t, speed_alpha=speed_alpha, remodelling_alpha=remodelling_alpha,
                   smoothing_sigma=smoothing_sigma, initial_v_x=initial_v_x, initial_v_y=initial_v_y,
                   initial_remodelling=initial_remodelling, use_direct_solver=use_direct_solver, dtype=dtype, rtol=rtol,
                   max_it=max_it, preconditioner=preconditioner, batch_pairs=batch_pairs, verbose=verbose,
-                  solver_options=solver_options)
+                  solver_options=solver_options, result_dtype=result_dtype, outputs=outputs)
         return sharding.solve_on_devices(movie, list(devices), lambda frames, dev: variational_optical_flow(frames, device=dev, **kw),
                                          delta_x, delta_t)
     if devices is not None and len(devices) == 1:
@@ -293,9 +301,23 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     itemsize = 4 if tdtype == torch.float32 else 8
     blur = smoothing_sigma is not None
     arena = hostio.result_arena                                                # recycles dropped result arrays' pages
-    result_bytes = (4 * n_pairs + (T if blur else 0)) * Nx * Ny * 8
+    wire = np.dtype(result_dtype)
+    if wire not in (np.dtype(np.float32), np.dtype(np.float64)):
+        raise ValueError("result_dtype must be 'float64' or 'float32', got %r" % (result_dtype,))
+    wire_t = torch.float32 if wire == np.float32 else torch.float64
+    all_outputs = ('v_x', 'v_y', 'speed', 'remodelling', 'blurred_data', 'original_data')
+    wanted = all_outputs if outputs is None else tuple(outputs)
+    if set(wanted) - set(all_outputs):
+        raise ValueError('outputs must be taken from %r, got %r' % (all_outputs, outputs))
+    result_names = ('v_x', 'v_y', 'speed', 'remodelling')
+    shipped = tuple(q for q, name in enumerate(result_names) if name in wanted)     # plane numbers that leave the device
+    ship_blur = blur and 'blurred_data' in wanted
+    # speed = sqrt(v_x^2 + v_y^2) (:1191) is computed on the host from the two arrays that arrive anyway when all three
+    # are returned: 8 of the 42 MB per 1024^2 pair less on the host link (OFB_HOST_SPEED=0: ship the device's plane)
+    host_speed = all(k in wanted for k in ('v_x', 'v_y', 'speed')) and os.environ.get('OFB_HOST_SPEED', '1') != '0'
+    result_bytes = ((len(shipped) - (1 if host_speed else 0)) * n_pairs + (T if ship_blur else 0)) * Nx * Ny * wire.itemsize
     direct = (os.environ.get('OFB_DIRECT_EGRESS', '1') != '0' and arena.max_idle_bytes > 0
-              and result_bytes <= int(os.environ.get('OFB_DIRECT_EGRESS_BYTES', 16 << 30)))
+              and result_bytes <= hostio.direct_egress_limit())
     B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_pairs, dev)
     B = max(1, min(B, n_pairs))
     scale_in = float(delta_t) / float(delta_x)                                 # :800-801
@@ -303,26 +325,33 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     guess = (float(initial_v_x) * scale_in, float(initial_v_y) * scale_in, float(initial_remodelling))
 
     source = np.ascontiguousarray(movie_np)
-    original = arena.alloc((T, Nx, Ny), np.float64)                            # :769
-    # Direct egress: the result arrays are page-locked, the planes are widened to float64 on the device and copied
-    # straight into them - the host cores do no conversion (on a slow host the float32 -> float64 widening, not the
-    # device, bounded the call).  Pinning costs ~0.1-0.3 s per GB the first time (recycled by the arena afterwards), so
-    # it is used up to OFB_DIRECT_EGRESS_BYTES (default 16 GiB) of results; beyond that, or if pinning fails, the planes
-    # go through pinned staging and the host copy pool as before.
-    result_names = ('v_x', 'v_y', 'speed', 'remodelling')
+    if 'original_data' not in wanted:
+        original = None
+    elif source.dtype == wire:
+        original = source                                                      # nothing to convert (float32 contract only)
+    else:
+        original = arena.alloc((T, Nx, Ny), wire)                              # :769
+    convert_original = original is not None and original is not source
+    # Direct egress: the result arrays are page-locked, the planes are converted to the result type on the device and
+    # copied straight into them - the host cores do no conversion (on a slow host the float32 -> float64 widening, not
+    # the device, bounded the call).  Pinning costs ~0.1-0.3 s per GB the first time (recycled by the arena afterwards);
+    # it is used up to hostio.direct_egress_limit() bytes of results per call; beyond that, or if pinning fails, the
+    # planes go through pinned staging and the host copy pool.
     out, blurred, out_t, blurred_t = None, None, None, None
     if direct:
         try:
-            out = {k: arena.alloc((n_pairs, Nx, Ny), np.float64, pinned=True) for k in result_names}
-            blurred = arena.alloc((T, Nx, Ny), np.float64, pinned=True) if blur else original
-            out_t = {k: torch.from_numpy(v) for k, v in out.items()}
-            blurred_t = torch.from_numpy(blurred) if blur else None
+            out = {result_names[q]: arena.alloc((n_pairs, Nx, Ny), wire, pinned=not (host_speed and q == 2)) for q in shipped}
+            blurred = arena.alloc((T, Nx, Ny), wire, pinned=True) if ship_blur else None
+            out_t = {k: torch.from_numpy(v) for k, v in out.items() if not (host_speed and k == 'speed')}
+            blurred_t = torch.from_numpy(blurred) if ship_blur else None
             direct = all(t.is_pinned() for t in out_t.values()) and (blurred_t is None or blurred_t.is_pinned())
         except Exception:
             direct = False
     if not direct:
-        out = {k: arena.alloc((n_pairs, Nx, Ny), np.float64) for k in result_names}
-        blurred = arena.alloc((T, Nx, Ny), np.float64) if blur else original
+        host_speed = False                                                      # the staged path's host threads are busy widening
+        out = {result_names[q]: arena.alloc((n_pairs, Nx, Ny), wire) for q in shipped}
+        blurred = arena.alloc((T, Nx, Ny), wire) if ship_blur else None
+    wire_planes = tuple(q for q in shipped if not (host_speed and q == 2))        # planes copied device -> host
     functionals = np.zeros((n_pairs, 3))
     # relative_residual: |b - A x| / |b| recomputed from the returned x (what the reference prints, :1150-1151);
     # recurrence_residual: the solver's own norm when it stopped (:1140-1142)
@@ -340,11 +369,12 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         slot = dict(dev=torch.empty((nplanes, B + 1, Nx, Ny), dtype=tdtype, device=dev), pin=None, busy=None)
         if not direct:
             slot['pin'] = hostio.pinned_pool.acquire((nplanes, B + 1, Nx, Ny), tdtype)
-        # float64 planes for the direct path (a float64 solve's planes are copied as they are)
-        slot['dev64'] = (torch.empty((nplanes, B + 1, Nx, Ny), dtype=torch.float64, device=dev)
-                         if direct and tdtype != torch.float64 else slot['dev'])
+        # planes in the result type for the direct path (planes that already have it are copied as they are)
+        slot['dev64'] = (torch.empty((nplanes, B + 1, Nx, Ny), dtype=wire_t, device=dev)
+                         if direct and tdtype != wire_t else slot['dev'])
         slots.append(slot)
     timeline = []
+    host_jobs = []                                                             # host-side work on result arrays (speed, input copy)
     t_setup = time.time()
     try:
         schedule = _chunk_schedule(n_pairs, B, Nx * Ny, taper=os.environ.get('OFB_TAPER', '1') != '0')
@@ -376,38 +406,47 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
             if direct:
                 planes = slot['dev64']
                 if planes is not slot['dev']:
-                    for q in range(4):
-                        engine.widen(slot['dev'][q, :nb], planes[q, :nb])
-                    if blur:
-                        engine.widen(slot['dev'][4, :last_frame], planes[4, :last_frame])
+                    convert = engine.widen if wire_t == torch.float64 else (lambda src, dst: dst.copy_(src))
+                    for q in wire_planes:
+                        convert(slot['dev'][q, :nb], planes[q, :nb])
+                    if ship_blur:
+                        convert(slot['dev'][4, :last_frame], planes[4, :last_frame])
                 ready = torch.cuda.Event()
                 ready.record(main_stream)
                 with torch.cuda.stream(copy_stream):
                     copy_stream.wait_event(ready)
-                    for q, name in enumerate(result_names):
-                        out_t[name][k0:k1].copy_(planes[q, :nb], non_blocking=True)
-                    if blur:
+                    for q in wire_planes:
+                        out_t[result_names[q]][k0:k1].copy_(planes[q, :nb], non_blocking=True)
+                        if host_speed and q == 1:              # v_x and v_y of the chunk have landed: speed can start
+                            landed = torch.cuda.Event()
+                            landed.record(copy_stream)
+                    if ship_blur:
                         blurred_t[k0:k0 + last_frame].copy_(planes[4, :last_frame], non_blocking=True)
                     copied = torch.cuda.Event()
                     copied.record(copy_stream)
                 slot['busy'] = _EventWaiter(copied)            # slot reuse waits for the copy engine, not for a host thread
-                slot['original'] = worker.submit(None, [(original[k0:k0 + last_frame], source[k0:k0 + last_frame])])   # :769
+                if convert_original:
+                    host_jobs.append(worker.submit(None, [(original[k0:k0 + last_frame], source[k0:k0 + last_frame])]))   # :769
+                if host_speed:
+                    host_jobs.append(worker.submit(landed, [], functools.partial(hostio.speed_from_velocities, out['v_x'][k0:k1],
+                                                                                 out['v_y'][k0:k1], out['speed'][k0:k1])))
             else:
                 ready = torch.cuda.Event()
                 ready.record(main_stream)
                 with torch.cuda.stream(copy_stream):
                     copy_stream.wait_event(ready)
-                    for q in range(4):
+                    for q in shipped:
                         slot['pin'][q, :nb].copy_(slot['dev'][q, :nb], non_blocking=True)
-                    if blur:
+                    if ship_blur:
                         slot['pin'][4, :last_frame].copy_(slot['dev'][4, :last_frame], non_blocking=True)
                     copied = torch.cuda.Event()
                     copied.record(copy_stream)
                 # one widening job per chunk: splitting it per plane was measured slower (27 vs 22 ms per chunk)
-                copies = [(out[name][k0:k1], slot['pin'][q, :nb]) for q, name in enumerate(result_names)]
-                if blur:
+                copies = [(out[result_names[q]][k0:k1], slot['pin'][q, :nb]) for q in shipped]
+                if ship_blur:
                     copies.append((blurred[k0:k0 + last_frame], slot['pin'][4, :last_frame]))
-                copies.append((original[k0:k0 + last_frame], source[k0:k0 + last_frame]))      # float64 copy of the input (:769)
+                if convert_original:
+                    copies.append((original[k0:k0 + last_frame], source[k0:k0 + last_frame]))      # float64 copy of the input (:769)
                 slot['busy'] = worker.submit(copied, copies)       # slot reuse (three chunks later) waits for this on the host
             stats.append(torch.cat([fun, iters.double()[:, None], relres[:, None], conv.double()[:, None],
                                     fb.double()[:, None], recur[:, None]], dim=1))
@@ -427,8 +466,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         for slot in slots:
             if slot['busy'] is not None:
                 slot['busy'].wait()
-            if slot.get('original') is not None:
-                slot['original'].wait()
+        for job in host_jobs:
+            job.wait()
         timeline.append(dict(stats=t_stats - t_loop, drain=time.perf_counter() - t_stats, setup=t_setup - t_start))
     finally:
         # nothing may still be writing into the result arrays or the staging slots when they are handed back; an egress
@@ -449,14 +488,15 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     if verbose and not info['converged'].all():
         print('the solver has not actually converged, the result will be incorrect or inaccurate')
     result = dict()
-    result['v_x'] = out['v_x']
-    result['v_y'] = out['v_y']
-    result['speed'] = out['speed']
-    result['remodelling'] = out['remodelling']
-    result['original_data'] = original
+    for name in result_names:
+        if name in out:
+            result[name] = out[name]
+    if original is not None:
+        result['original_data'] = original
     result['delta_x'] = delta_x
     result['delta_t'] = delta_t
-    result['blurred_data'] = blurred
+    if 'blurred_data' in wanted:
+        result['blurred_data'] = blurred if blur else original if original is not None else source.astype(wire)
     result['converged'] = bool(info['converged'][-1])
     result['L1_functional'] = float(np.sum(functionals[:, 0]))
     result['remodelling_functional'] = float(np.sum(functionals[:, 2]))
@@ -468,7 +508,8 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info['timeline'] = timeline
     info['egress_log'] = list(worker.log)
     info['h2d_bytes'] = int(sum(k1 - k0 + 1 for k0, k1 in schedule) * source[0].nbytes)
-    info['d2h_bytes'] = int((4 * n_pairs + (T if blur else 0)) * Nx * Ny * (8 if direct else itemsize))
+    info['d2h_bytes'] = int((len(wire_planes) * n_pairs + (T if ship_blur else 0)) * Nx * Ny * (wire.itemsize if direct else itemsize))
+    info['speed_on_host'] = bool(host_speed)
     info['direct_egress'] = bool(direct)
     result['solver_info'] = info
     return result

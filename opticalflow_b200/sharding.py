@@ -15,7 +15,7 @@ import numpy as np
 
 FIELD_KEYS = ('v_x', 'v_y', 'speed', 'remodelling')
 SUM_KEYS = ('L1_functional', 'remodelling_functional', 'speed_functional')
-INFO_ARRAY_KEYS = ('iterations', 'relative_residual', 'converged', 'fallback', 'speed_functional_per_pair')
+INFO_ARRAY_KEYS = ('iterations', 'relative_residual', 'recurrence_residual', 'converged', 'fallback', 'speed_functional_per_pair')
 
 
 def pair_range(rank, world, n_pairs):
@@ -39,15 +39,21 @@ def merge_results(parts, movie, delta_x, delta_t):
     if not parts:
         raise ValueError('no shard produced a result')
     result = {}
+    # keys a caller left out with outputs=(...) are absent from every shard; the result type follows result_dtype
     for key in FIELD_KEYS:
-        result[key] = np.concatenate([p[key] for p in parts], axis=0)
-    result['original_data'] = np.asarray(movie).astype(np.float64)
+        if all(key in p for p in parts):
+            result[key] = np.concatenate([p[key] for p in parts], axis=0)
+    wire = next((result[k].dtype for k in FIELD_KEYS if k in result), np.dtype(np.float64))
+    first = parts[0]
+    if 'original_data' in first:
+        result['original_data'] = np.asarray(movie).astype(wire, copy=False)
     result['delta_x'] = delta_x
     result['delta_t'] = delta_t
-    if parts[0].get('blurred_is_original', parts[0]['blurred_data'] is parts[0]['original_data']):
-        result['blurred_data'] = result['original_data']
-    else:       # shards overlap by one frame: drop the duplicate first frame of every shard but the first
-        result['blurred_data'] = np.concatenate([parts[0]['blurred_data']] + [p['blurred_data'][1:] for p in parts[1:]], axis=0)
+    if 'blurred_data' in first:
+        if first.get('blurred_is_original', first['blurred_data'] is first.get('original_data')):
+            result['blurred_data'] = result['original_data'] if 'original_data' in result else np.asarray(movie).astype(wire, copy=False)
+        else:   # shards overlap by one frame: drop the duplicate first frame of every shard but the first
+            result['blurred_data'] = np.concatenate([first['blurred_data']] + [p['blurred_data'][1:] for p in parts[1:]], axis=0)
     result['converged'] = bool(parts[-1]['converged'])                   # last pair only, optical_flow.py:1202
     for key in SUM_KEYS:
         result[key] = float(sum(p[key] for p in parts))
@@ -56,7 +62,7 @@ def merge_results(parts, movie, delta_x, delta_t):
     for key in INFO_ARRAY_KEYS:
         if all(key in i for i in infos):
             info[key] = np.concatenate([np.atleast_1d(i[key]) for i in infos])
-    info['shards'] = [len(p['v_x']) for p in parts]
+    info['shards'] = [len(np.atleast_1d(i.get('iterations', ()))) for i in infos]
     for key in ('h2d_bytes', 'd2h_bytes'):
         if all(key in i for i in infos):
             info[key] = int(sum(i[key] for i in infos))
@@ -98,8 +104,10 @@ def solve_distributed(movie, solve_fn, delta_x=1.0, delta_t=1.0, group=None, dst
     frames = shard_frames(movie, rank, world)
     part = solve_fn(frames) if frames.shape[0] >= 2 else None
     if part is not None:                 # original_data is rebuilt from the movie on dst: do not ship it
-        same = part['blurred_data'] is part['original_data']
-        part = dict(part, original_data=None, blurred_is_original=same)
+        same = 'blurred_data' in part and part['blurred_data'] is part.get('original_data')
+        part = dict(part, blurred_is_original=same)
+        if 'original_data' in part:
+            part['original_data'] = None
         if same:
             part['blurred_data'] = None
     gathered = [None] * world if rank == dst else None

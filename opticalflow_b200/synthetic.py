@@ -58,19 +58,22 @@ def actin_like_movie(Nx=512, Ny=512, n_frames=100, seed=1, n_filaments=400, shif
     return movie
 
 
-def rotating_shearing_movie(Nx=1024, Ny=1024, n_frames=500, seed=2, omega=1e-3, shear=5e-4):
-    """Config d-3: frame t = frame 0 warped by t * v(r), v = omega z x (r-c) + shear (y-cy) x_hat.
-
-    Warp is a backward bicubic (Catmull-Rom) lookup with clamped coordinates."""
+def rotating_shearing_frames(Nx, Ny, indices, seed=2, omega=1e-3, shear=5e-4):
+    """Frames ``indices`` of the config d-3 movie (any subset, any order): a frame depends on frame 0 only, so a pool of
+    processes can generate a long movie in pieces (bench.py)."""
     base = textured_frame(Nx, Ny, seed=seed)
     ii, jj = np.meshgrid(np.arange(Nx, dtype=np.float64), np.arange(Ny, dtype=np.float64), indexing='ij')
     cx, cy = (Nx - 1) / 2.0, (Ny - 1) / 2.0
     vx = -omega * (jj - cy) + shear * (jj - cy)
     vy = omega * (ii - cx)
-    frames = [base]
-    for t in range(1, n_frames):
-        frames.append(_bicubic_sample(base, ii - t * vx, jj - t * vy))
-    return np.stack(frames)
+    return np.stack([base if t == 0 else _bicubic_sample(base, ii - t * vx, jj - t * vy) for t in indices])
+
+
+def rotating_shearing_movie(Nx=1024, Ny=1024, n_frames=500, seed=2, omega=1e-3, shear=5e-4):
+    """Config d-3: frame t = frame 0 warped by t * v(r), v = omega z x (r-c) + shear (y-cy) x_hat.
+
+    Warp is a backward bicubic (Catmull-Rom) lookup with clamped coordinates."""
+    return rotating_shearing_frames(Nx, Ny, range(n_frames), seed, omega, shear)
 
 
 def _bicubic_sample(img, x, y):

@@ -9,10 +9,13 @@ are injected for them first.  ``skimage.filters.gaussian`` is stubbed by its
 documented delegation ``scipy.ndimage.gaussian_filter(mode='nearest',
 truncate=4.0)`` - parity of the blur against real skimage is therefore unpinned.
 
-``/root/reference`` does not exist on the GPU box: nothing that runs there may
-import this file.  It is used by ``oracle/make_golden.py`` (fixture generator)
-and by the ``not gpu`` tests that validate ``oracle/flow_oracle.py`` against the
-reference when the reference is present.
+``/root/reference`` does not exist on the GPU box.  ``oracle/build_ref.py`` (run by
+``__graft_entry__.build()`` in the build container) places an untouched copy of the one
+reference module this path consists of in ``oracle/_ref/`` - a build output, git-ignored,
+never committed - which travels to the box with the snapshot; this importer falls back to
+it.  Used by ``oracle/make_golden.py`` (fixture generator), by the ``not gpu`` tests that
+validate ``oracle/flow_oracle.py`` against the reference, and by ``bench.py``'s reference
+arm / ``cpu_baseline`` leg (the reference's own CPU code timed on the box's host cores).
 """
 import contextlib
 import io
@@ -22,7 +25,8 @@ import types
 
 import numpy as np
 
-REFERENCE_SOURCE_DIR = '/root/reference/source'
+_CANDIDATES = ('/root/reference/source', os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref'))
+REFERENCE_SOURCE_DIR = next((d for d in _CANDIDATES if os.path.isfile(os.path.join(d, 'optical_flow.py'))), _CANDIDATES[0])
 
 
 def reference_available():

@@ -254,10 +254,10 @@ def check_movie_against_oracle_operator(movie, kw, iteration_cap):
         assert abs(got64['solver_info']['relative_residual'][k] - res) < 1e-2 * res + 1e-13
         # float32: the frames the device solved on are its own float32 blur (returned widened, exactly); x is stored in
         # float32, so |b - A x| cannot go below ~u |D x| whatever the solver does - the bar is the backward-error form
-        # rtol |b| + 2 u |D x| (include/ofb200.h), and the forward error against the float64 answer the stated 1e-3 / 1e-2 px
+        # rtol |b| + 8 u |D x| (include/ofb200.h), and the forward error against the float64 answer the stated 1e-3 / 1e-2 px
         P32, C32 = got32['blurred_data'][k], got32['blurred_data'][k + 1]
         res32, dscale = oracle_residual(P32, C32, raw_solution(got32, k), alpha, beta)
-        assert res32 <= 1e-6 + 2 * U32 * dscale, (k, res32, U32 * dscale)
+        assert res32 <= 1e-6 + 8 * U32 * dscale, (k, res32, U32 * dscale)
         assert abs(got32['solver_info']['relative_residual'][k] - res32) < 1e-3 * res32
         assert got32['solver_info']['recurrence_residual'][k] <= 1e-6
     for key in ('v_x', 'v_y', 'remodelling'):
@@ -335,7 +335,7 @@ def test_true_residual_output_is_the_oracle_residual(cuda_device, dtype):
             res = np.linalg.norm(bk - fo.apply_operator(P, x[k].cpu().double().numpy(), alphas[k], betas[k])) / np.linalg.norm(bk)
         assert abs(float(rr[k]) - res) < 1e-3 * res + 1e-14, (float(rr[k]), res)
         assert float(rec[k]) <= rtol
-        assert res <= rtol + 2 * (U64 if dtype == torch.float64 else U32) * dscale
+        assert res <= rtol + 8 * (U64 if dtype == torch.float64 else U32) * dscale
 
 
 def test_identical_frames_give_zero_whatever_the_guess(cuda_device):
