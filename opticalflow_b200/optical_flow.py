@@ -515,16 +515,62 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     return result
 
 
-@_on_device
+def _sweep_pairs(movie_np, first_pair, last_pair, cell_alpha, cell_beta, dev, tdtype, smoothing_sigma, guess, scale, rtol, max_it,
+                 preconditioner, solver_options, batch_entries):
+    """Pairs [first_pair, last_pair) of the movie x every (alpha, beta) cell on one device.  Returns host arrays
+    (moments [cells, 4], functional [cells], converged of the last pair handled [cells])."""
+    n_cells = cell_alpha.size
+    _, Nx, Ny = movie_np.shape
+    a_dev = torch.from_numpy(cell_alpha).to(dev)
+    b_dev = torch.from_numpy(cell_beta).to(dev)
+    mom_dev = torch.zeros((n_cells, 4), dtype=torch.float64, device=dev)
+    fun_dev = torch.zeros(n_cells, dtype=torch.float64, device=dev)
+    conv_dev = torch.zeros(n_cells, dtype=torch.int32, device=dev)
+    workspace = engine.Workspace()
+    # entries = (pair, cell), pairs outermost, solved in batches that span pairs: 4 pairs x 16 cells fill a 64-entry solve
+    pairs_per_batch = max(1, batch_entries // n_cells)
+    cells_per_batch = min(n_cells, batch_entries)
+    for k0 in range(first_pair, last_pair, pairs_per_batch):
+        k1 = min(k0 + pairs_per_batch, last_pair)
+        frames = hostio.as_native_tensor(movie_np[k0:k1 + 1]).to(dev).to(tdtype)
+        if smoothing_sigma is not None:
+            frames = engine.blur(frames, smoothing_sigma)               # shared by every cell of the pair
+        for c0 in range(0, n_cells, cells_per_batch):
+            c1 = min(c0 + cells_per_batch, n_cells)
+            nc, npairs = c1 - c0, k1 - k0
+            # entry e = (pair k0 + e // nc, cell c0 + e % nc)
+            P = frames[:-1].repeat_interleave(nc, dim=0)
+            C = frames[1:].repeat_interleave(nc, dim=0)
+            a = a_dev[c0:c1].repeat(npairs)
+            be = b_dev[c0:c1].repeat(npairs)
+            x0 = torch.empty((nc * npairs, 3, Nx, Ny), dtype=tdtype, device=dev)
+            for q in range(3):
+                x0[:, q] = guess[q]
+            x, iters, relres, conv, fb, _ = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace, solver_options)
+            _, _, _, _, fun, mom = engine.epilogue(P, C, x, a, be, scale)
+            mom_dev[c0:c1] += mom.view(npairs, nc, 4).sum(dim=0)
+            # L1 + 'speed' (= remodelling, :1205) + remodelling
+            fun_dev[c0:c1] += (fun[:, 0] + 2.0 * fun[:, 2]).view(npairs, nc).sum(dim=0)
+            conv_dev[c0:c1] = conv.view(npairs, nc)[-1]
+    packed = torch.cat([mom_dev, fun_dev[:, None], conv_dev.double()[:, None]], dim=1).cpu().numpy()     # the one device -> host read
+    return packed[:, :4], packed[:, 4], packed[:, 5] != 0
+
+
 def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
                         remodelling_alpha_values=np.arange(500, 2000, 500), filename=None, **kwargs):
     """Grid of regularisation weights -> summary statistics (optical_flow.py:1918-1998).
 
     Every (speed_alpha, remodelling_alpha) cell is what ``variational_optical_flow(movie, speed_alpha=...,
     remodelling_alpha=..., **kwargs)`` would give, but the cells are solved together: the blurred frames are
-    shared on the device and the cells of a frame pair form one batch with per-entry weights; means,
-    variances and the functional are reduced on the device (epilogue moments), no field is copied back."""
-    dev = _device(kwargs.pop('device', None))
+    shared on the device, the (pair, cell) entries form batches with per-entry weights that span frame pairs (4 pairs
+    x 16 cells fill a 64-entry solve); means, variances and the functional are accumulated on the device (epilogue
+    moments) and read once at the end - no field is copied back.  ``devices=[...]`` shards the frame pairs over several
+    GPUs (pairs outermost, one host thread per device, partial sums added on the host)."""
+    devices = kwargs.pop('devices', None)
+    device = kwargs.pop('device', None)
+    if devices is None or len(devices) == 0:
+        devices = [device]
+    devs = [_device(d) for d in devices]
     tdtype, _ = engine.resolve_dtype(kwargs.pop('dtype', 'float64'))
     rtol = kwargs.pop('rtol', 1e-6)
     max_it = kwargs.pop('max_it', 1000)
@@ -550,33 +596,25 @@ def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
     cell_beta = np.tile(betas, len(alphas))
     n_cells = cell_alpha.size
     itemsize = 4 if tdtype == torch.float32 else 8
-    B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_cells, dev, pipelined=False)
-    moments = np.zeros((n_cells, 4))
-    functional = np.zeros(n_cells)
-    converged_last = np.zeros(n_cells, bool)
-    workspace = engine.Workspace()
-    for k in range(n_pairs):
-        frames = torch.from_numpy(movie_np[k:k + 2]).to(dev).to(tdtype)
-        if smoothing_sigma is not None:
-            frames = engine.blur(frames, smoothing_sigma)
-        for c0 in range(0, n_cells, B):
-            c1 = min(c0 + B, n_cells)
-            nb = c1 - c0
-            P = frames[0:1].expand(nb, Nx, Ny).contiguous()
-            C = frames[1:2].expand(nb, Nx, Ny).contiguous()
-            x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
-            for q in range(3):
-                x0[:, q] = guess[q]
-            a = torch.from_numpy(cell_alpha[c0:c1]).to(dev)
-            be = torch.from_numpy(cell_beta[c0:c1]).to(dev)
-            x, iters, relres, conv, fb, _ = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace,
-                                                         solver_options)
-            _, _, _, _, fun, mom = engine.epilogue(P, C, x, a, be, float(delta_x) / float(delta_t))
-            moments[c0:c1] += mom.cpu().numpy()
-            fun = fun.cpu().numpy()
-            functional[c0:c1] += fun[:, 0] + 2.0 * fun[:, 2]        # L1 + 'speed' (= remodelling, :1205) + remodelling
-            if k == n_pairs - 1:
-                converged_last[c0:c1] = conv.cpu().numpy() != 0
+    scale = float(delta_x) / float(delta_t)
+
+    def shard(rank):
+        start, stop = sharding.pair_range(rank, len(devs), n_pairs)
+        if stop <= start:
+            return None
+        with torch.cuda.device(devs[rank]):
+            B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_cells * (stop - start), devs[rank], pipelined=False)
+            return _sweep_pairs(movie_np, start, stop, cell_alpha, cell_beta, devs[rank], tdtype, smoothing_sigma, guess, scale, rtol,
+                                max_it, preconditioner, solver_options, B)
+
+    if len(devs) == 1:
+        parts = [shard(0)]
+    else:
+        parts = sharding.run_on_threads(shard, len(devs))
+    parts = [p for p in parts if p is not None]
+    moments = sum(p[0] for p in parts)
+    functional = sum(p[1] for p in parts)
+    converged_last = parts[-1][2]                                        # the shard that holds the last pair (:1202)
     count = float(n_pairs * Nx * Ny)
     shape = (len(alphas), len(betas))
     speed_mean = moments[:, 0] / count

@@ -70,6 +70,26 @@ def merge_results(parts, movie, delta_x, delta_t):
     return result
 
 
+def run_on_threads(fn, world):
+    """fn(rank) on one host thread per rank; returns the list of results, re-raises the first error."""
+    parts, errors = [None] * world, []
+
+    def work(rank):
+        try:
+            parts[rank] = fn(rank)
+        except Exception as exc:        # re-raised on the calling thread
+            errors.append(exc)
+
+    threads = [threading.Thread(target=work, args=(r,)) for r in range(world)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]
+    return parts
+
+
 def solve_on_devices(movie, devices, solve_fn, delta_x=1.0, delta_t=1.0):
     """One host thread per device; `solve_fn(frames, device)` returns a result dict for its shard."""
     movie = np.asarray(movie)

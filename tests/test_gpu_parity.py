@@ -167,10 +167,15 @@ def test_dropin_256_config_d1(cuda_device):
     assert got64['solver_info']['iterations'][0] <= 40
 
 
-def test_vary_regularisation_matches_loop(cuda_device):
+@pytest.mark.parametrize('variant', ['default', 'cells_split', 'batch_spans_pairs', 'two_threads'])
+def test_vary_regularisation_matches_loop(cuda_device, variant):
+    """2 pairs x 6 cells against a loop of oracle calls (optical_flow.py:1960-1983): the cells of a pair in one batch,
+    a pair's cells split over batches, one batch spanning both pairs, and the pairs sharded over two host threads."""
     movie = synthetic.translating_movie(40, 48, 3, seed=12)
     alphas, betas = np.array([2e4, 1e5]), np.array([1e3, 1e4, 1e5])
-    got = optical_flow.vary_regularisation(movie, alphas, betas, smoothing_sigma=2.0, rtol=1e-11, max_it=20000)
+    extra = {'default': {}, 'cells_split': dict(batch_pairs=4), 'batch_spans_pairs': dict(batch_pairs=12),
+             'two_threads': dict(devices=['cuda:0', 'cuda:0'])}[variant]
+    got = optical_flow.vary_regularisation(movie, alphas, betas, smoothing_sigma=2.0, rtol=1e-11, max_it=20000, **extra)
     assert got['speed_means'].shape == (2, 3) and got['converged'].dtype == bool
     for i, a in enumerate(alphas):
         for j, b in enumerate(betas):
@@ -180,6 +185,21 @@ def test_vary_regularisation_matches_loop(cuda_device):
             assert abs(got['remodelling_means'][i, j] - np.mean(ref['remodelling'])) < 1e-6 * abs(np.mean(ref['remodelling'])) + 1e-12
             total = ref['L1_functional'] + ref['speed_functional'] + ref['remodelling_functional']
             assert abs(got['functional'][i, j] - total) < 1e-6 * total
+            assert got['converged'][i, j]
+
+
+def test_vary_regularisation_128_two_pairs_six_cells_float32(cuda_device):
+    """The sweep at 128^2 in float32 (what config d-4 runs), 2 pairs x 6 cells in one 12-entry solve, against the oracle loop."""
+    movie = synthetic.rotating_shearing_movie(128, 128, 3, seed=2)
+    alphas, betas = np.array([4.64e4, 1e5, 1e6]), np.array([1e3, 1e4])
+    got = optical_flow.vary_regularisation(movie, alphas, betas, smoothing_sigma=2.5, dtype='float32', rtol=1e-6)
+    for i, a in enumerate(alphas):
+        for j, b in enumerate(betas):
+            ref = fo.variational_optical_flow(movie, speed_alpha=a, remodelling_alpha=b, smoothing_sigma=2.5)
+            assert abs(got['speed_means'][i, j] - np.mean(ref['speed'])) < 1e-3 * np.mean(ref['speed'])
+            assert abs(got['remodelling_means'][i, j] - np.mean(ref['remodelling'])) < 1e-3 * abs(np.mean(ref['remodelling'])) + 1e-6
+            total = ref['L1_functional'] + ref['speed_functional'] + ref['remodelling_functional']
+            assert abs(got['functional'][i, j] - total) < 2e-3 * total
             assert got['converged'][i, j]
 
 
