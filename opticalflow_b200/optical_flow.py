@@ -258,7 +258,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                              smoothing_sigma=None, initial_v_x=0.0, initial_v_y=0.0, initial_remodelling=0.0,
                              use_direct_solver=False, *, dtype='float64', rtol=1e-6, max_it=1000,
                              preconditioner='mg', device=None, batch_pairs=None, verbose=False,
-                             solver_options=None, devices=None, result_dtype='float64', outputs=None):
+                             solver_options=None, devices=None, result_dtype='float64', outputs=None, warm_start=False):
     """Variational optical flow with net remodelling on every consecutive frame pair of ``movie``.
 
     Signature, defaults, units and result keys follow optical_flow.py:715-1210: ``movie[T,Nx,Ny]``; velocities
@@ -269,6 +269,11 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     planes travel device -> pinned memory on a copy stream and are widened to float64 by a worker thread.
     ``devices=[...]`` shards the pairs over several GPUs (contiguous ranges, one host thread per device, no
     collective; sharding.py).
+
+    ``warm_start=True`` follows the reference's habit of seeding a pair with an earlier pair's solution (:803-806): the
+    pairs of a chunk are solved together, so every pair of chunk c starts from the solution of the LAST pair of chunk
+    c-1 (the first chunk from ``initial_*``).  The answer changes within the solver tolerance only; on slowly varying
+    flow it saves iterations.  Off by default: pairs then depend on the chunking.
 
     The reference returns ~42 MB of float64 per 1024^2 pair (:1189-1205); at several hundred pairs per second and GPU
     that is what the host link carries, not the solve.  Two opt-in keywords cut it (defaults keep the reference's
@@ -282,7 +287,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                   smoothing_sigma=smoothing_sigma, initial_v_x=initial_v_x, initial_v_y=initial_v_y,
                   initial_remodelling=initial_remodelling, use_direct_solver=use_direct_solver, dtype=dtype, rtol=rtol,
                   max_it=max_it, preconditioner=preconditioner, batch_pairs=batch_pairs, verbose=verbose,
-                  solver_options=solver_options, result_dtype=result_dtype, outputs=outputs)
+                  solver_options=solver_options, result_dtype=result_dtype, outputs=outputs, warm_start=warm_start)
         return sharding.solve_on_devices(movie, list(devices), lambda frames, dev: variational_optical_flow(frames, device=dev, **kw),
                                          delta_x, delta_t)
     if devices is not None and len(devices) == 1:
@@ -312,9 +317,11 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     result_names = ('v_x', 'v_y', 'speed', 'remodelling')
     shipped = tuple(q for q, name in enumerate(result_names) if name in wanted)     # plane numbers that leave the device
     ship_blur = blur and 'blurred_data' in wanted
-    # speed = sqrt(v_x^2 + v_y^2) (:1191) is computed on the host from the two arrays that arrive anyway when all three
-    # are returned: 8 of the 42 MB per 1024^2 pair less on the host link (OFB_HOST_SPEED=0: ship the device's plane)
-    host_speed = all(k in wanted for k in ('v_x', 'v_y', 'speed')) and os.environ.get('OFB_HOST_SPEED', '1') != '0'
+    # OFB_HOST_SPEED=1: speed = sqrt(v_x^2 + v_y^2) (:1191) computed on the host from the two arrays that arrive anyway
+    # instead of being shipped (8 of the 42 MB per 1024^2 pair less on the host link).  Off by default: measured on the
+    # pool's 8-GPU box it gains nothing at 1-2 ranks (789 / 1169 vs 1147 frame-pairs/s) and loses at 4 and 8 (1228 vs
+    # 1277, 1414 vs 1713), where the host's memory system, not the link, is what saturates (profiles/r02_d2h_ceiling.txt)
+    host_speed = all(k in wanted for k in ('v_x', 'v_y', 'speed')) and os.environ.get('OFB_HOST_SPEED', '0') == '1'
     result_bytes = ((len(shipped) - (1 if host_speed else 0)) * n_pairs + (T if ship_blur else 0)) * Nx * Ny * wire.itemsize
     direct = (os.environ.get('OFB_DIRECT_EGRESS', '1') != '0' and arena.max_idle_bytes > 0
               and result_bytes <= hostio.direct_egress_limit())
@@ -375,6 +382,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         slots.append(slot)
     timeline = []
     host_jobs = []                                                             # host-side work on result arrays (speed, input copy)
+    previous_last = None                                                       # warm_start: solution of the previous chunk's last pair
     t_setup = time.time()
     try:
         schedule = _chunk_schedule(n_pairs, B, Nx * Ny, taper=os.environ.get('OFB_TAPER', '1') != '0')
@@ -394,12 +402,17 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                 frames = engine.blur(frames, smoothing_sigma, out=slot['dev'][4, :nb + 1])     # :770-771
             P, C = frames[:-1], frames[1:]
             x0 = torch.empty((nb, 3, Nx, Ny), dtype=tdtype, device=dev)
-            for q in range(3):
-                x0[:, q] = guess[q]
+            if warm_start and previous_last is not None:
+                x0[:] = previous_last                                          # :803-806, across chunks
+            else:
+                for q in range(3):
+                    x0[:, q] = guess[q]
             t_prep = time.perf_counter()
             x, iters, relres, conv, fb, recur = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
                                                              preconditioner, workspace, solver_options)
             t_solve = time.perf_counter()
+            if warm_start:
+                previous_last = x[-1:].clone()
             fields = slot['dev'][:4, :nb]
             _, _, _, _, fun, _ = engine.epilogue(P, C, x, speed_alpha, remodelling_alpha, scale_out, out=fields)
             last_frame = nb + 1 if k1 == n_pairs else nb
@@ -528,7 +541,7 @@ def _sweep_pairs(movie_np, first_pair, last_pair, cell_alpha, cell_beta, dev, td
     conv_dev = torch.zeros(n_cells, dtype=torch.int32, device=dev)
     workspace = engine.Workspace()
     # entries = (pair, cell), pairs outermost, solved in batches that span pairs: 4 pairs x 16 cells fill a 64-entry solve
-    pairs_per_batch = max(1, batch_entries // n_cells)
+    pairs_per_batch = max(1, int(round(batch_entries / float(n_cells))))     # 11 cells: 6 pairs = 66 entries, not 5 = 55
     cells_per_batch = min(n_cells, batch_entries)
     for k0 in range(first_pair, last_pair, pairs_per_batch):
         k1 = min(k0 + pairs_per_batch, last_pair)

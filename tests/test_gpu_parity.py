@@ -513,6 +513,50 @@ def test_direct_and_staged_egress_return_identical_arrays(cuda_device, monkeypat
     assert again['solver_info']['direct_egress'] and idle >= 1 and len(hostio.result_arena.free_pinned) < idle
 
 
+def test_warm_start_changes_iterations_not_answers(cuda_device):
+    """warm_start=True (the reference's seeding of a pair with an earlier solution, :803-806, across chunks): same fields
+    within the solver tolerance, fewer iterations on a stationary flow."""
+    movie = synthetic.translating_movie(96, 128, 9, seed=5)
+    kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.0, batch_pairs=2, rtol=1e-9)
+    cold = optical_flow.variational_optical_flow(movie, **kw)
+    warm = optical_flow.variational_optical_flow(movie, warm_start=True, **kw)
+    assert cold['solver_info']['converged'].all() and warm['solver_info']['converged'].all()
+    for key in ('v_x', 'v_y', 'remodelling'):
+        assert rel(warm[key], cold[key]) < 1e-6, key
+    assert (warm['solver_info']['iterations'][:2] == cold['solver_info']['iterations'][:2]).all()       # first chunk: same start
+    assert warm['solver_info']['iterations'][2:].sum() < cold['solver_info']['iterations'][2:].sum()
+
+
+def test_result_dtype_and_outputs_keep_the_values(cuda_device, monkeypatch):
+    """Opt-in contracts: result_dtype='float32' and outputs=(...) return the same numbers as the reference-shaped default
+    (to float32 rounding), leave out exactly the keys not asked for, on the direct and on the staged egress path; and
+    speed computed on the host (OFB_HOST_SPEED=1) is sqrt(v_x^2 + v_y^2) of the returned arrays."""
+    movie = synthetic.translating_movie(96, 128, 6, seed=5).astype(np.float32)
+    kw = dict(speed_alpha=1e5, remodelling_alpha=1e4, smoothing_sigma=2.0, batch_pairs=2, dtype='float32')
+    full = optical_flow.variational_optical_flow(movie, **kw)
+    for direct in ('1', '0'):
+        monkeypatch.setenv('OFB_DIRECT_EGRESS', direct)
+        lean = optical_flow.variational_optical_flow(movie, result_dtype='float32', outputs=('v_x', 'v_y', 'remodelling'), **kw)
+        assert lean['solver_info']['direct_egress'] == (direct == '1')
+        assert not ({'speed', 'blurred_data', 'original_data'} & set(lean))
+        for key in ('v_x', 'v_y', 'remodelling'):
+            assert lean[key].dtype == np.float32 and rel(lean[key], full[key]) < 1e-4, key
+        assert lean['converged'] == full['converged'] and abs(lean['L1_functional'] - full['L1_functional']) < 1e-3 * full['L1_functional']
+        assert lean['solver_info']['d2h_bytes'] * 42 < full['solver_info']['d2h_bytes'] * 13       # 12 of the 40 bytes per pixel
+        f32 = optical_flow.variational_optical_flow(movie, result_dtype='float32', **kw)
+        assert set(f32) == set(full) and f32['original_data'] is not None
+        for key in ('v_x', 'v_y', 'speed', 'remodelling', 'blurred_data', 'original_data'):
+            assert f32[key].dtype == np.float32 and rel(f32[key], full[key]) < 1e-4, key
+    monkeypatch.setenv('OFB_DIRECT_EGRESS', '1')
+    monkeypatch.setenv('OFB_HOST_SPEED', '1')
+    host = optical_flow.variational_optical_flow(movie, **kw)
+    assert host['solver_info']['speed_on_host'] and host['speed'].dtype == np.float64
+    assert np.abs(host['speed'] - np.sqrt(host['v_x'] ** 2 + host['v_y'] ** 2)).max() < 1e-14
+    assert rel(host['speed'], full['speed']) < 1e-4
+    with pytest.raises(ValueError):
+        optical_flow.variational_optical_flow(movie, outputs=('v_x', 'vorticity'), **kw)
+
+
 @pytest.mark.parametrize('shape', [(64, 256), (130, 512), (257, 1028), (96, 1024)])
 def test_fused_prolongation_matches_separate_pass(cuda_device, shape):
     """float32 image level, OFB_FLAG_FUSED_PROLONG: the first post-smoothing sweep adds the coarse-grid correction to its

@@ -72,10 +72,7 @@ def main():
                               converged=conv.astype(int).tolist(), speed_means=[float('%.4g' % v) for v in res['speed_means'][:, 0]])),
               flush=True)
         hi = alphas >= 4e4                      # the cells the multigrid cycle converges (DESIGN.md regime map)
-        t0 = time.perf_counter()
-        res = optical_flow.vary_regularisation(movie, alphas[hi], np.array([1e4]), dtype='float32', smoothing_sigma=2.5)
-        torch.cuda.synchronize()
-        s = time.perf_counter() - t0
+        s, res = timed(lambda: optical_flow.vary_regularisation(movie, alphas[hi], np.array([1e4]), dtype='float32', smoothing_sigma=2.5))
         print(json.dumps(dict(config='d-4, the %d cells with alpha >= 4.6e4' % int(hi.sum()), pairs=n, seconds=round(s, 3),
                               solves_per_s=round(int(hi.sum()) * n / s, 1), converged_cells=int(res['converged'].sum()))), flush=True)
 
