@@ -14,6 +14,10 @@ def main(path, out=None, note=''):
     else:
         s = idx[-2] if len(idx) >= 2 and idx[-1] - idx[-2] > 200 else idx[-1]
         e = idx[-1] if s != idx[-1] else len(rows)
+    # a device step of bench.py ends with the epilogue; what follows (the smoother-only roofline loop) is not the step
+    ends = [i for i, (k, g, t) in enumerate(rows) if 'k_epilogue' in k and s <= i < e]
+    if ends:
+        e = ends[0] + 1
     agg = collections.defaultdict(lambda: [0, 0.0])
     for k, g, t in rows[s:e]:
         k = k.split('(ofb::')[0].split('(long')[0].split('(int')[0].split('(const')[0]
