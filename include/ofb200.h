@@ -48,7 +48,7 @@ extern "C" {
 
 #define OFB_FLAG_POLL_AHEAD 1024 /* ofb_solve: enqueue iteration k+1 before reading iteration k's convergence count (measured slower: off by default) */
 
-#define OFB_ABI_VERSION 5
+#define OFB_ABI_VERSION 6
 
 typedef struct ofb_solve_options {
     int    precond;        /* OFB_PRECOND_*            default OFB_PRECOND_MG */
@@ -229,6 +229,27 @@ int ofb_widen(const void* in_f32, void* out_f64, long long n, void* stream);
  *     out = movie - background where blurred > background, else 0 (blurred = ofb_blur(movie, sigma 10)). */
 int ofb_subtract_background(const void* movie, const void* blurred, void* out, double background, long long n,
                             int dtype, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Sparse direct solve: replaces the reference's SuperLU branch (optical_flow.py:1146-1147, use_direct_solver=True) and
+ * serves as the fallback where the operator is indefinite and no preconditioned Krylov method converges (small
+ * speed_alpha).  Multifrontal LU in fp64 on a geometric nested dissection of the interior pixels; the plan (index
+ * arrays that depend on the frame shape only) is built on the host (opticalflow_b200/ndplan.py) and handed in as
+ * `levels`, root first: per level the padded pixel counts and DEVICE arrays of int32 pixel ids (i * (Ny-2) + j over the
+ * interior, -1 = padding).  The array of structs itself lives in host memory.  Dense kernels are cuBLAS / cuSOLVER.
+ * One pair is factorised and solved at a time; a 1024^2 frame needs ~28 GB of workspace.  relres_out (device, B
+ * doubles, may be NULL): |b - A x| / |b| recomputed from the returned x (:1150-1151).  x3: out only.
+ * ------------------------------------------------------------------------------------------------------- */
+typedef struct ofb_nd_level {
+    int n_nodes, n_own, n_border, reserved;
+    const int* own;             /* [n_nodes][n_own]     pixels the node eliminates */
+    const int* border;          /* [n_nodes][n_border]  ring of pixels around its rectangle */
+    const int* parent_slot;     /* [n_nodes][n_border]  position of each border pixel in the parent's front */
+} ofb_nd_level;
+size_t ofb_direct_workspace_bytes(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny);
+int ofb_direct_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta,
+                     const ofb_nd_level* levels, int n_levels, void* workspace, size_t workspace_bytes,
+                     double* relres_out, int B, int Nx, int Ny, int dtype, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Allocation-free variant.  NO COUNTERPART IN THE REFERENCE: added for

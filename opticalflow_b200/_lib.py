@@ -21,7 +21,7 @@ FLAG_NO_HALF_STEP_EXIT = 128
 FLAG_SERIAL_SETUP = 256
 FLAG_FUSED_PROLONG = 512
 FLAG_POLL_AHEAD = 1024
-ABI_VERSION = 5
+ABI_VERSION = 6
 
 # every symbol include/ofb200.h declares
 EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb_launch_count', 'ofb_last_unconverged', 'ofb_last_restarts', 'ofb_workspace_bytes', 'ofb_blur',
@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
                     'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab',
                     'ofb_liu_shen', 'ofb_movie_max', 'ofb_adaptive_threshold', 'ofb_clahe_workspace_bytes', 'ofb_clahe',
-                    'ofb_subtract_background', 'ofb_widen', 'ofb_blur_noalloc')
+                    'ofb_subtract_background', 'ofb_widen', 'ofb_blur_noalloc', 'ofb_direct_workspace_bytes', 'ofb_direct_solve')
 BLUR_NOALLOC_MAX_BYTES = 16 << 20
 
 
@@ -46,6 +46,12 @@ class Slab(ctypes.Structure):
     _fields_ = [('rank', ctypes.c_int), ('world', ctypes.c_int), ('Nx_global', ctypes.c_int),
                 ('rows_per_rank', ctypes.c_int), ('gather_level', ctypes.c_int), ('reserved', ctypes.c_int),
                 ('comm', ctypes.c_void_p)]
+
+
+class NdLevel(ctypes.Structure):
+    """ofb_nd_level: one level of the nested-dissection plan (include/ofb200.h); pointers are device addresses."""
+    _fields_ = [('n_nodes', ctypes.c_int), ('n_own', ctypes.c_int), ('n_border', ctypes.c_int), ('reserved', ctypes.c_int),
+                ('own', ctypes.c_void_p), ('border', ctypes.c_void_p), ('parent_slot', ctypes.c_void_p)]
 
 
 class OfbError(RuntimeError):
@@ -132,6 +138,10 @@ def load():
     lib.ofb_widen.argtypes = [vp, vp, ll, vp]
     lib.ofb_subtract_background.restype = i
     lib.ofb_subtract_background.argtypes = [vp, vp, vp, d, ll, i, vp]
+    lib.ofb_direct_workspace_bytes.restype = sz
+    lib.ofb_direct_workspace_bytes.argtypes = [ctypes.POINTER(NdLevel), i, i, i, i]
+    lib.ofb_direct_solve.restype = i
+    lib.ofb_direct_solve.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(NdLevel), i, vp, sz, dp, i, i, i, i, vp]
     lib.ofb_blur_noalloc.restype = i
     lib.ofb_blur_noalloc.argtypes = [vp, vp, dp, i, i, i, i, i, vp]
     if lib.ofb_version() != ABI_VERSION:

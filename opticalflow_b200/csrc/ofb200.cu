@@ -15,6 +15,7 @@
 #include "halo_exchange.cuh"
 #include "coarse_fused.cuh"
 #include "legacy_kernels.cuh"
+#include "direct_solver.cuh"
 
 using namespace ofb;
 
@@ -1622,3 +1623,244 @@ extern "C" int ofb_blur_noalloc(const void* in, void* out, const double* weights
     return dtype == OFB_F32 ? blur_noalloc_impl<float>(in, out, scratch, weights, radius, F, Nx, Ny, (cudaStream_t)stream)
                             : blur_noalloc_impl<double>(in, out, scratch, weights, radius, F, Nx, Ny, (cudaStream_t)stream);
 }
+
+// =====================================================================================================
+// Sparse direct solve (direct_solver.cuh): replaces the SuperLU branch, optical_flow.py:1146-1147
+// =====================================================================================================
+namespace {
+
+#define OFB_CHECK_CUBLAS(expr)                                                                   \
+    do {                                                                                         \
+        cublasStatus_t s__ = (expr);                                                             \
+        if (s__ != CUBLAS_STATUS_SUCCESS) return fail(-3000 - (int)s__, "%s: cuBLAS status %d", #expr, (int)s__); \
+    } while (0)
+#define OFB_CHECK_CUSOLVER(expr)                                                                 \
+    do {                                                                                         \
+        cusolverStatus_t s__ = (expr);                                                           \
+        if (s__ != CUSOLVER_STATUS_SUCCESS) return fail(-4000 - (int)s__, "%s: cuSOLVER status %d", #expr, (int)s__); \
+    } while (0)
+
+constexpr int ND_BATCHED_MAX = 128;       // owned variables per node up to which the batched cuBLAS LU is used
+
+struct DenseHandles { cublasHandle_t blas = nullptr; cusolverDnHandle_t solver = nullptr; };
+int dense_handles(DenseHandles** out) {
+    static DenseHandles handles[MAX_DEVICES];
+    static std::mutex mu;
+    int dev = 0;
+    OFB_CHECK_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= MAX_DEVICES) return fail(-11, "device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(mu);
+    DenseHandles& h = handles[dev];
+    if (h.blas == nullptr) OFB_CHECK_CUBLAS(cublasCreate(&h.blas));
+    if (h.solver == nullptr) OFB_CHECK_CUSOLVER(cusolverDnCreate(&h.solver));
+    *out = &h;
+    return 0;
+}
+
+struct NdWorkspace {
+    NdLevel lv[64];
+    double *w, *z, *u, *getrf_work;
+    double **Fptr, **F12ptr, **zptr;
+    PairState* st;
+    int* active;            // per-pair flags k_state_init wants (unused here)
+    int* scratch_info;      // devInfo of the triangular solves (getrf's verdict stays in NdLevel::info)
+    int getrf_lwork;
+    size_t bytes;
+};
+
+// `levels` describe the plan (device index arrays); carve the fronts and the scratch vectors out of `base`.
+int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, void* base, NdWorkspace* W, cusolverDnHandle_t solver) {
+    if (n_levels < 1 || n_levels > 64) return fail(-50, "direct solve: bad number of levels %d", n_levels);
+    size_t off = 0;
+    auto take = [&](size_t nbytes) { void* p = base ? (char*)base + off : nullptr; off = align_up(off + nbytes, 256); return p; };
+    size_t max_nodes = 0, max_z = 0, max_u = 0;
+    int lwork = 0;
+    for (int l = 0; l < n_levels; ++l) {
+        NdLevel& L = W->lv[l];
+        L.n_nodes = levels[l].n_nodes; L.n_own = levels[l].n_own; L.n_border = levels[l].n_border;
+        if (L.n_nodes < 1 || L.n_own < 1 || L.n_border < 1) return fail(-50, "direct solve: bad level %d", l);
+        L.own = levels[l].own; L.border = levels[l].border; L.parent_slot = levels[l].parent_slot;
+        const size_t nf = (size_t)L.nf();
+        L.F = (double*)take((size_t)L.n_nodes * nf * nf * sizeof(double));
+        L.piv = (int*)take((size_t)L.n_nodes * L.no3() * sizeof(int));
+        L.info = (int*)take((size_t)L.n_nodes * sizeof(int));
+        max_nodes = std::max(max_nodes, (size_t)L.n_nodes);
+        max_z = std::max(max_z, (size_t)L.n_nodes * L.no3());
+        max_u = std::max(max_u, (size_t)L.n_nodes * L.nb3());
+        if (L.no3() > ND_BATCHED_MAX && solver != nullptr) {
+            int lw = 0;
+            OFB_CHECK_CUSOLVER(cusolverDnDgetrf_bufferSize(solver, L.no3(), L.no3(), nullptr, (int)nf, &lw));
+            lwork = std::max(lwork, lw);
+        }
+    }
+    const size_t M = (size_t)(Nx - 2) * (Ny - 2);
+    W->w = (double*)take(3 * M * sizeof(double));
+    W->z = (double*)take(max_z * sizeof(double));
+    W->u = (double*)take(max_u * sizeof(double));
+    W->Fptr = (double**)take(max_nodes * sizeof(double*));
+    W->F12ptr = (double**)take(max_nodes * sizeof(double*));
+    W->zptr = (double**)take(max_nodes * sizeof(double*));
+    W->getrf_lwork = lwork;
+    W->getrf_work = (double*)take((size_t)std::max(lwork, 1) * sizeof(double));
+    W->st = (PairState*)take(sizeof(PairState) * (size_t)B);
+    W->active = (int*)take(sizeof(int) * (size_t)B);
+    W->scratch_info = (int*)take(sizeof(int) * 4);
+    W->bytes = off;
+    return 0;
+}
+
+template <typename T>
+int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, const double* beta, const ofb_nd_level* levels,
+                int n_levels, void* workspace, size_t workspace_bytes, double* relres_out, int B, int Nx, int Ny, cudaStream_t stream) {
+    DenseHandles* H = nullptr;
+    if (int rc = dense_handles(&H)) return rc;
+    OFB_CHECK_CUBLAS(cublasSetStream(H->blas, stream));
+    OFB_CHECK_CUSOLVER(cusolverDnSetStream(H->solver, stream));
+    NdWorkspace W;
+    if (int rc = nd_carve(levels, n_levels, B, Nx, Ny, workspace, &W, H->solver)) return rc;
+    if (workspace == nullptr || workspace_bytes < W.bytes)
+        return fail(-4, "direct solve: workspace too small: need %zu bytes, got %zu", W.bytes, workspace_bytes);
+    LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny, 2, 2, 0.0, 0.0};
+    const Geom g = make_geom<T>(lp, false);
+    const long long M = (long long)(Nx - 2) * (Ny - 2);
+    const double one = 1.0, minus_one = -1.0;
+    std::vector<int> infos;
+    for (int pair = 0; pair < B; ++pair) {
+        const T* img = (const T*)P_ + (long long)pair * g.img_pair;
+        const T* b = (const T*)b3 + (long long)pair * g.pair;
+        T* x = (T*)x3 + (long long)pair * g.pair;
+        // ---- numeric factorisation, leaves to root
+        for (int l = n_levels - 1; l >= 0; --l) {
+            const NdLevel& L = W.lv[l];
+            const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
+            const long long stride = (long long)nf * nf;
+            OFB_CHECK_CUDA(cudaMemsetAsync(L.F, 0, sizeof(double) * stride * L.n_nodes, stream));
+            k_nd_assemble<T><<<dim3(L.n_nodes, no3, (nf + 127) / 128), 128, 0, stream>>>(L, g, img, alpha, beta, pair);
+            OFB_CHECK_LAUNCH();
+            if (l + 1 < n_levels) {
+                const NdLevel& C = W.lv[l + 1];
+                for (int parity = 0; parity < 2; ++parity) {
+                    k_nd_extend_add<<<dim3(C.n_nodes / 2, C.nb3(), (C.nb3() + 127) / 128), 128, 0, stream>>>(C, L, parity);
+                    OFB_CHECK_LAUNCH();
+                }
+            }
+            if (no3 <= ND_BATCHED_MAX) {
+                k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
+                OFB_CHECK_LAUNCH();
+                OFB_CHECK_CUBLAS(cublasDgetrfBatched(H->blas, no3, W.Fptr, nf, L.piv, L.info, L.n_nodes));
+                int info = 0;
+                OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, nb3, (const double* const*)W.Fptr, nf, L.piv, W.F12ptr, nf,
+                                                     &info, L.n_nodes));
+                if (info != 0) return fail(-51, "direct solve: cublasDgetrsBatched argument %d invalid", -info);
+            } else {
+                for (int n = 0; n < L.n_nodes; ++n) {
+                    double* F = L.F + stride * n;
+                    OFB_CHECK_CUSOLVER(cusolverDnDgetrf(H->solver, no3, no3, F, nf, W.getrf_work, L.piv + (long long)n * no3, L.info + n));
+                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->solver, CUBLAS_OP_N, no3, nb3, F, nf, L.piv + (long long)n * no3,
+                                                        F + (long long)no3 * nf, nf, W.scratch_info));
+                }
+            }
+            // S = F22 - F21 X, in place in the F22 block of every front of the level
+            OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, nb3, no3, &minus_one, L.F + no3, nf, stride,
+                                                       L.F + (long long)no3 * nf, nf, stride, &one, L.F + (long long)no3 * nf + no3, nf,
+                                                       stride, L.n_nodes));
+        }
+        // a zero pivot anywhere makes the factorisation useless: report it instead of returning garbage
+        for (int l = 0; l < n_levels; ++l) {
+            infos.resize(W.lv[l].n_nodes);
+            OFB_CHECK_CUDA(cudaMemcpyAsync(infos.data(), W.lv[l].info, sizeof(int) * W.lv[l].n_nodes, cudaMemcpyDeviceToHost, stream));
+            OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
+            for (int n = 0; n < W.lv[l].n_nodes; ++n)
+                if (infos[n] != 0) return fail(-52, "direct solve: singular front (pair %d, level %d, node %d, pivot %d)", pair, l, n, infos[n]);
+        }
+        // ---- forward sweep, leaves to root: z = F11^-1 w[own]; w[own] = z; w[border] -= F21 z
+        k_nd_load_rhs<T><<<dim3((Ny - 2 + 127) / 128, Nx - 2, 3), 128, 0, stream>>>(g, b, W.w);
+        OFB_CHECK_LAUNCH();
+        for (int l = n_levels - 1; l >= 0; --l) {
+            const NdLevel& L = W.lv[l];
+            const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
+            const long long stride = (long long)nf * nf;
+            k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
+            OFB_CHECK_LAUNCH();
+            if (no3 <= ND_BATCHED_MAX) {
+                k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
+                OFB_CHECK_LAUNCH();
+                int info = 0;
+                OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, 1, (const double* const*)W.Fptr, nf, L.piv, W.zptr, no3, &info,
+                                                     L.n_nodes));
+            } else {
+                for (int n = 0; n < L.n_nodes; ++n)
+                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->solver, CUBLAS_OP_N, no3, 1, L.F + stride * n, nf, L.piv + (long long)n * no3,
+                                                        W.z + (long long)n * no3, no3, W.scratch_info));
+            }
+            k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
+            OFB_CHECK_LAUNCH();
+            const double zero = 0.0;
+            OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, 1, no3, &one, L.F + no3, nf, stride, W.z, no3, no3,
+                                                       &zero, W.u, nb3, nb3, L.n_nodes));
+            k_nd_scatter_border<<<dim3(L.n_nodes, (nb3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.u);
+            OFB_CHECK_LAUNCH();
+        }
+        // ---- backward sweep, root to leaves: x[own] = z - X x[border]
+        for (int l = 0; l < n_levels; ++l) {
+            const NdLevel& L = W.lv[l];
+            const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
+            const long long stride = (long long)nf * nf;
+            k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
+            OFB_CHECK_LAUNCH();
+            k_nd_gather<<<dim3(L.n_nodes, (nb3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.u, 1);
+            OFB_CHECK_LAUNCH();
+            OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, no3, 1, nb3, &minus_one, L.F + (long long)no3 * nf, nf,
+                                                       stride, W.u, nb3, nb3, &one, W.z, no3, no3, L.n_nodes));
+            k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
+            OFB_CHECK_LAUNCH();
+        }
+        k_nd_store_solution<T><<<dim3((Ny + 127) / 128, Nx, 3), 128, 0, stream>>>(g, W.w, x);
+        OFB_CHECK_LAUNCH();
+        const int ring = 2 * Nx + 2 * Ny;
+        k_fill_ghosts<T><<<dim3((ring + 127) / 128, 1), 128, 0, stream>>>(g, x);
+        OFB_CHECK_LAUNCH();
+    }
+    // the reference's independent residual (:1150-1151) of what is returned, in fp64
+    const long long nvec = g.pair;
+    const int sb = (B + 127) / 128;
+    const dim3 blas_grid((unsigned)std::min<long long>((nvec + 1023) / 1024, 148 * 8), B);
+    k_state_init<<<sb, 128, 0, stream>>>(W.st, W.active, B);
+    OFB_CHECK_LAUNCH();
+    k_norm2<T><<<blas_grid, 256, 0, stream>>>(nvec, nvec, (const T*)b3, W.st);
+    OFB_CHECK_LAUNCH();
+    k_state_bnorm<<<sb, 128, 0, stream>>>(W.st, B);
+    OFB_CHECK_LAUNCH();
+    k_true_residual<T><<<dim3((Ny + 127) / 128, std::min(std::max(Nx - 2, 1), 64), B), 128, 0, stream>>>(g, (const T*)P_, (const T*)x3,
+                                                                                                     (const T*)b3, alpha, beta, W.st);
+    OFB_CHECK_LAUNCH();
+    k_nd_relres<<<sb, 128, 0, stream>>>(W.st, relres_out, B);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t ofb_direct_workspace_bytes(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny) {
+    if (levels == nullptr || B < 1 || Nx < 5 || Ny < 5) return 0;
+    DenseHandles* H = nullptr;
+    if (dense_handles(&H)) return 0;
+    NdWorkspace W;
+    if (nd_carve(levels, n_levels, B, Nx, Ny, nullptr, &W, H->solver)) return 0;
+    return W.bytes;
+}
+
+int ofb_direct_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, const ofb_nd_level* levels,
+                     int n_levels, void* workspace, size_t workspace_bytes, double* relres_out, int B, int Nx, int Ny, int dtype,
+                     void* stream) {
+    if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
+    if (!P || !b3 || !x3 || !alpha || !beta || !levels) return fail(-6, "ofb_direct_solve: null pointer");
+    return dtype == OFB_F32 ? direct_impl<float>(P, b3, x3, alpha, beta, levels, n_levels, workspace, workspace_bytes, relres_out, B, Nx,
+                                                 Ny, (cudaStream_t)stream)
+                            : direct_impl<double>(P, b3, x3, alpha, beta, levels, n_levels, workspace, workspace_bytes, relres_out, B, Nx,
+                                                  Ny, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -180,6 +180,58 @@ def solve(P, b, x, speed_alpha, remodelling_alpha, rtol=1e-6, max_it=1000, optio
     return iters, relres, conv
 
 
+_plan_cache = {}
+
+
+def _direct_plan(Nx, Ny, device):
+    """Nested-dissection plan of an Nx x Ny frame on `device`: (ctypes array of ofb_nd_level, tensors kept alive, n_levels)."""
+    from . import ndplan
+    key = (int(Nx), int(Ny), str(device))
+    hit = _plan_cache.get(key)
+    if hit is None:
+        levels = ndplan.build(int(Nx), int(Ny))
+        structs = (_lib.NdLevel * len(levels))()
+        keep = []
+        for k, lv in enumerate(levels):
+            own, border, slot = (torch.from_numpy(np.ascontiguousarray(a)).to(device) for a in (lv.own, lv.border, lv.parent_slot))
+            keep += [own, border, slot]
+            structs[k] = _lib.NdLevel(lv.n_nodes, lv.n_own, lv.n_border, 0, own.data_ptr(), border.data_ptr(), slot.data_ptr())
+        if len(_plan_cache) > 4:
+            _plan_cache.clear()
+        hit = _plan_cache[key] = (structs, keep, len(levels))
+    return hit
+
+
+def direct_solve_bytes(Nx, Ny):
+    """Device bytes the fronts of a direct solve of an Nx x Ny pair take (the workspace is this plus a few vectors)."""
+    from . import ndplan
+    return ndplan.memory_bytes(ndplan.build(int(Nx), int(Ny)))
+
+
+def direct_solve(P, b, speed_alpha, remodelling_alpha, workspace=None):
+    """Sparse direct solve of A x = b (``ofb_direct_solve``: multifrontal LU in fp64 on a nested dissection of the pixel
+    grid), the counterpart of the reference's SuperLU branch (optical_flow.py:1146-1147).
+    Returns ``(x [B,3,Nx,Ny] of P's dtype, relres float64[B])``; relres is the true residual of x."""
+    _require_cuda(P, b)
+    B, Nx, Ny = P.shape
+    assert b.shape == (B, 3, Nx, Ny) and b.dtype == P.dtype and P.is_contiguous() and b.is_contiguous()
+    lib = _lib.load()
+    structs, _, n_levels = _direct_plan(Nx, Ny, P.device)
+    a, be = _weights(speed_alpha, B, P.device), _weights(remodelling_alpha, B, P.device)
+    need = lib.ofb_direct_workspace_bytes(structs, n_levels, B, Nx, Ny)
+    if need == 0:
+        raise _lib.OfbError('direct solve: ' + lib.ofb_last_error().decode())
+    holder = workspace if workspace is not None else Workspace()
+    if holder.buffer is None or holder.buffer.numel() < need or holder.buffer.device != P.device:
+        holder.buffer = None                                   # release the old one before asking for tens of GB
+        holder.buffer = torch.empty(need, dtype=torch.uint8, device=P.device)
+    x = torch.empty_like(b)
+    relres = torch.zeros(B, dtype=torch.float64, device=P.device)
+    _lib.check(lib.ofb_direct_solve(_ptr(P), _ptr(b), _ptr(x), _ptr(a), _ptr(be), structs, n_levels, _ptr(holder.buffer), need,
+                                    _ptr(relres), B, Nx, Ny, _code(P), _stream_ptr(P.device)))
+    return x, relres
+
+
 def last_unconverged():
     """Pairs the calling thread's last ``solve`` left unconverged (-1 if unknown): a host integer, no device read."""
     return int(_lib.load().ofb_last_unconverged())

@@ -111,6 +111,25 @@ def test_solve_fp64_matches_direct_solution(cuda_device, shape, precond):
         assert int(it[0]) <= 40
 
 
+@pytest.mark.parametrize('shape', [(5, 5), (7, 6), (24, 24), (40, 56), (64, 64), (33, 130)])
+@pytest.mark.parametrize('alpha', [1e5, 1e3])
+def test_direct_solve_matches_superlu(cuda_device, shape, alpha):
+    """ofb_direct_solve (multifrontal LU on a nested dissection, fp64) against the oracle's SuperLU solve of the
+    reference's matrix (:1146-1147) - also at alpha = 1e3, where the operator is indefinite and the Krylov path fails."""
+    movie = fo.blur_movie(synthetic.rotating_shearing_movie(shape[0], shape[1], 3, seed=2), 2.5)
+    want = [fo.solve_pair(movie[k], movie[k + 1], alpha, 1e4)[0] for k in range(2)]
+    Pd, Cd = dev_t(movie[:-1], cuda_device), dev_t(movie[1:], cuda_device)
+    b = engine.build_rhs(Pd, Cd)
+    x, rr = engine.direct_solve(Pd, b, alpha, 1e4)
+    for k in range(2):
+        assert rel(x[k].cpu().numpy(), want[k]) < 1e-9, (k, float(rr[k]))         # raw solution, ghost ring included
+        assert float(rr[k]) < 1e-10
+    # float32 images and right-hand side, fp64 factorisation: within the float32 tolerance
+    x32, rr32 = engine.direct_solve(Pd.float().contiguous(), b.float().contiguous(), alpha, 1e4)
+    for k in range(2):
+        assert rel(x32[k].cpu().double().numpy(), want[k]) < 1e-3
+
+
 def test_solve_initial_guess_and_batch_weights(cuda_device):
     """Per-pair weights in one batch; nonzero initial guess; converged pairs stop iterating."""
     movie = fo.blur_movie(synthetic.translating_movie(48, 48, 3, seed=8), 2.5)
