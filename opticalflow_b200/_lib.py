@@ -141,7 +141,7 @@ def load():
     lib.ofb_direct_workspace_bytes.restype = sz
     lib.ofb_direct_workspace_bytes.argtypes = [ctypes.POINTER(NdLevel), i, i, i, i]
     lib.ofb_direct_solve.restype = i
-    lib.ofb_direct_solve.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(NdLevel), i, vp, sz, dp, i, i, i, i, vp]
+    lib.ofb_direct_solve.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(NdLevel), i, vp, sz, d, dp, ip, i, i, i, i, vp]
     lib.ofb_blur_noalloc.restype = i
     lib.ofb_blur_noalloc.argtypes = [vp, vp, dp, i, i, i, i, i, vp]
     if lib.ofb_version() != ABI_VERSION:

@@ -147,10 +147,16 @@ __global__ void k_nd_store_solution(Geom g, const double* __restrict__ w, T* __r
     const bool inside = i >= 1 && i <= g.Nx - 2 && j >= 1 && j <= g.Ny - 2;
     x[q * g.plane + (long long)i * g.pitch + j] = inside ? T(w[(long long)q * mx * my + (long long)(i - 1) * my + (j - 1)]) : T(0);
 }
-__global__ void k_nd_relres(const PairState* __restrict__ st, double* __restrict__ relres, int B) {
+// the verdict of ofb_solve (k_verify) on the direct solution: |b - A x| <= rtol |b| + 8 u |D x|
+__global__ void k_nd_relres(const PairState* __restrict__ st, double* __restrict__ relres, int* __restrict__ converged, int B, double rtol,
+                            double unit_roundoff) {
     const int pair = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pair >= B || relres == nullptr) return;
-    relres[pair] = st[pair].bnorm > 0.0 ? sqrt(st[pair].acc[0]) / st[pair].bnorm : 0.0;
+    if (pair >= B) return;
+    const double bn = st[pair].bnorm;
+    const double rr = bn > 0.0 ? sqrt(st[pair].acc[0]) / bn : 0.0;
+    const double floor_rr = bn > 0.0 ? unit_roundoff * sqrt(st[pair].acc[1]) / bn : 0.0;
+    if (relres != nullptr) relres[pair] = rr;
+    if (converged != nullptr) converged[pair] = (isfinite(rr) && rr <= rtol + 8.0 * floor_rr) ? 1 : 0;
 }
 
 }  // namespace ofb

@@ -1711,7 +1711,8 @@ int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, vo
 
 template <typename T>
 int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, const double* beta, const ofb_nd_level* levels,
-                int n_levels, void* workspace, size_t workspace_bytes, double* relres_out, int B, int Nx, int Ny, cudaStream_t stream) {
+                int n_levels, void* workspace, size_t workspace_bytes, double rtol, double* relres_out, int* converged_out, int B, int Nx,
+                int Ny, cudaStream_t stream) {
     DenseHandles* H = nullptr;
     if (int rc = dense_handles(&H)) return rc;
     OFB_CHECK_CUBLAS(cublasSetStream(H->blas, stream));
@@ -1834,7 +1835,8 @@ int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, c
     k_true_residual<T><<<dim3((Ny + 127) / 128, std::min(std::max(Nx - 2, 1), 64), B), 128, 0, stream>>>(g, (const T*)P_, (const T*)x3,
                                                                                                      (const T*)b3, alpha, beta, W.st);
     OFB_CHECK_LAUNCH();
-    k_nd_relres<<<sb, 128, 0, stream>>>(W.st, relres_out, B);
+    k_nd_relres<<<sb, 128, 0, stream>>>(W.st, relres_out, converged_out, B, rtol,
+                                        sizeof(T) == 4 ? 5.9604644775390625e-08 : 1.1102230246251565e-16);
     OFB_CHECK_LAUNCH();
     return 0;
 }
@@ -1853,14 +1855,14 @@ size_t ofb_direct_workspace_bytes(const ofb_nd_level* levels, int n_levels, int 
 }
 
 int ofb_direct_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta, const ofb_nd_level* levels,
-                     int n_levels, void* workspace, size_t workspace_bytes, double* relres_out, int B, int Nx, int Ny, int dtype,
-                     void* stream) {
+                     int n_levels, void* workspace, size_t workspace_bytes, double rtol, double* relres_out, int* converged_out, int B,
+                     int Nx, int Ny, int dtype, void* stream) {
     if (int rc = check_shape(B, Nx, Ny, dtype)) return rc;
     if (!P || !b3 || !x3 || !alpha || !beta || !levels) return fail(-6, "ofb_direct_solve: null pointer");
-    return dtype == OFB_F32 ? direct_impl<float>(P, b3, x3, alpha, beta, levels, n_levels, workspace, workspace_bytes, relres_out, B, Nx,
-                                                 Ny, (cudaStream_t)stream)
-                            : direct_impl<double>(P, b3, x3, alpha, beta, levels, n_levels, workspace, workspace_bytes, relres_out, B, Nx,
-                                                  Ny, (cudaStream_t)stream);
+    return dtype == OFB_F32 ? direct_impl<float>(P, b3, x3, alpha, beta, levels, n_levels, workspace, workspace_bytes, rtol, relres_out,
+                                                 converged_out, B, Nx, Ny, (cudaStream_t)stream)
+                            : direct_impl<double>(P, b3, x3, alpha, beta, levels, n_levels, workspace, workspace_bytes, rtol, relres_out,
+                                                  converged_out, B, Nx, Ny, (cudaStream_t)stream);
 }
 
 }  // extern "C"

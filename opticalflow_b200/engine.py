@@ -202,16 +202,26 @@ def _direct_plan(Nx, Ny, device):
     return hit
 
 
-def direct_solve_bytes(Nx, Ny):
-    """Device bytes the fronts of a direct solve of an Nx x Ny pair take (the workspace is this plus a few vectors)."""
-    from . import ndplan
-    return ndplan.memory_bytes(ndplan.build(int(Nx), int(Ny)))
+def direct_solve_estimate(Nx, Ny):
+    """Rough device bytes of a direct solve of an Nx x Ny pair without building the plan (measured: 1.25 / 5.9 / 27.5 GB
+    at 256^2 / 512^2 / 1024^2: ~ pixels^1.12)."""
+    return int(27.5e9 * (float(Nx) * float(Ny) / 1048576.0) ** 1.12)
 
 
-def direct_solve(P, b, speed_alpha, remodelling_alpha, workspace=None):
+def direct_solve_fits(Nx, Ny, device):
+    """True if the fronts of a direct solve fit in 70 % of the device memory that is free right now."""
+    try:
+        free = torch.cuda.mem_get_info(device)[0]
+    except Exception:
+        return False
+    return Nx * Ny <= (1 << 22) and direct_solve_estimate(Nx, Ny) * 1.05 < 0.7 * free
+
+
+def direct_solve(P, b, speed_alpha, remodelling_alpha, workspace=None, rtol=1e-6):
     """Sparse direct solve of A x = b (``ofb_direct_solve``: multifrontal LU in fp64 on a nested dissection of the pixel
     grid), the counterpart of the reference's SuperLU branch (optical_flow.py:1146-1147).
-    Returns ``(x [B,3,Nx,Ny] of P's dtype, relres float64[B])``; relres is the true residual of x."""
+    Returns ``(x [B,3,Nx,Ny] of P's dtype, relres float64[B], converged int32[B])``; relres is the true residual of x,
+    converged the verdict of ``solve`` on it (rtol plus what storing x in P's dtype leaves)."""
     _require_cuda(P, b)
     B, Nx, Ny = P.shape
     assert b.shape == (B, 3, Nx, Ny) and b.dtype == P.dtype and P.is_contiguous() and b.is_contiguous()
@@ -227,9 +237,10 @@ def direct_solve(P, b, speed_alpha, remodelling_alpha, workspace=None):
         holder.buffer = torch.empty(need, dtype=torch.uint8, device=P.device)
     x = torch.empty_like(b)
     relres = torch.zeros(B, dtype=torch.float64, device=P.device)
+    conv = torch.zeros(B, dtype=torch.int32, device=P.device)
     _lib.check(lib.ofb_direct_solve(_ptr(P), _ptr(b), _ptr(x), _ptr(a), _ptr(be), structs, n_levels, _ptr(holder.buffer), need,
-                                    _ptr(relres), B, Nx, Ny, _code(P), _stream_ptr(P.device)))
-    return x, relres
+                                    float(rtol), _ptr(relres), _ptr(conv), B, Nx, Ny, _code(P), _stream_ptr(P.device)))
+    return x, relres, conv
 
 
 def last_unconverged():

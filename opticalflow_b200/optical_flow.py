@@ -12,8 +12,10 @@ Differences from the reference that a caller can observe (all documented in DESI
   * the frame pairs of a movie are solved as independent systems, batched, each from the user's
     ``initial_*`` guess (the reference warm-starts pair k from pair k-1, :803-806); the answers agree to
     O(rtol);
-  * ``use_direct_solver=True`` has no sparse-direct equivalent on the device; it tightens the iterative
-    tolerance to 1e-12 instead;
+  * ``use_direct_solver=True`` runs a sparse direct solve on the device (multifrontal LU on a nested dissection
+    of the pixel grid, fp64) instead of SuperLU; frames whose fronts do not fit in device memory (beyond
+    ~2048^2) get the iterative solve with rtol 1e-12 instead.  The same direct solve takes over the pairs the
+    iterative solver does not converge (small speed_alpha: the operator is indefinite there);
   * nothing is printed unless ``verbose=True``;
   * solver diagnostics of every pair are returned under ``result['solver_info']``.
 Keyword-only extras (defaults preserve reference behaviour): ``dtype``, ``rtol``, ``max_it``,
@@ -196,16 +198,22 @@ class _EventWaiter:
 PROBE_IT = 100
 
 
-def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace, solver_options):
-    """Solve a batch.  Pairs the default multigrid cycle does not converge are redone with the robust V(2,2) cycle,
-    then (float32 only) in float64 - where alpha approaches max(I^2) the system is too ill-conditioned for float32
-    storage - and last with plain block-Jacobi BiCGStab, which wins on small frames.  A pair none of them converges
-    is reported like the reference reports it (:1137-1138): ``converged`` False, best iterate returned."""
-    B = P.shape[0]
+def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace, solver_options, direct=False, direct_workspace=None):
+    """Solve a batch.  ``direct``: every pair by the sparse direct solve (the reference's ``use_direct_solver=True`` branch,
+    :1146-1147).  Otherwise multigrid-preconditioned BiCGStab; pairs it has not converged after PROBE_IT iterations are in
+    the regime where the operator is indefinite (speed_alpha below ~max I^2 / 1.5) and go to the direct
+    solve when its fronts fit on the device (0.6 s per 1024^2 pair).  Where they do not fit (very large frames) the older chain
+    applies: the robust V(2,2) cycle, float64, block-Jacobi; a pair none of them converges is reported like the reference
+    reports it (:1137-1138): ``converged`` False, best iterate returned."""
+    B, Nx, Ny = P.shape
     b = engine.build_rhs(P, C)
+    fallback = torch.zeros(B, dtype=torch.bool, device=P.device)
+    direct_workspace = direct_workspace if direct_workspace is not None else engine.Workspace()
+    if direct:
+        x, relres, conv = engine.direct_solve(P, b, alpha, beta, direct_workspace, rtol)
+        return x, torch.zeros(B, dtype=torch.int32, device=P.device), relres, conv, fallback, relres.clone()
     x = x0.clone()
     opts = engine.make_options(preconditioner, **solver_options)
-    fallback = torch.zeros(B, dtype=torch.bool, device=P.device)
     recur = torch.zeros(B, dtype=torch.float64, device=P.device)
     if opts.precond != _lib.PRECOND_MG:
         iters, relres, conv = engine.solve(P, b, x, alpha, beta, rtol, max_it, opts, workspace, recurrence=recur)
@@ -217,6 +225,16 @@ def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace,
     if engine.last_unconverged() == 0:
         # every pair converged: no fallback, and no device->host read either - a read here would queue on the copy
         # engine behind the previous chunk's result planes (tens of ms for a 64-pair chunk)
+        return x, iters, relres, conv, fallback, recur
+    a_all, be_all = engine._weights(alpha, B, P.device), engine._weights(beta, B, P.device)
+    if os.environ.get('OFB_DIRECT_FALLBACK', '1') != '0' and engine.direct_solve_fits(Nx, Ny, P.device):
+        bad = (conv == 0).nonzero().flatten()
+        xb, rr2, cv2 = engine.direct_solve(P[bad].contiguous(), b[bad].contiguous(), a_all[bad], be_all[bad], direct_workspace, rtol)
+        x[bad] = xb
+        relres[bad] = rr2
+        recur[bad] = rr2
+        conv[bad] = cv2
+        fallback[bad] = True
         return x, iters, relres, conv, fallback, recur
     passthrough = {k: v for k, v in solver_options.items() if k in ('check_every', 'rows_per_strip', 'flags')}
     robust = engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8, omega_pre=(0.8, 0.8), omega_post=(0.8, 0.8), **passthrough)
@@ -233,8 +251,7 @@ def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace,
         bad = (conv == 0).nonzero().flatten()
         if bad.numel() == 0:
             break
-        a_b = engine._weights(alpha, B, P.device)[bad]
-        be_b = engine._weights(beta, B, P.device)[bad]
+        a_b, be_b = a_all[bad], be_all[bad]
         if widen:
             Pb, Cb = P[bad].double().contiguous(), C[bad].double().contiguous()
             bb, xb, ws = engine.build_rhs(Pb, Cb), x0[bad].double().contiguous(), engine.Workspace()
@@ -300,7 +317,10 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
         raise ValueError('movie must be [T>=2, Nx, Ny]')
     T, Nx, Ny = movie_np.shape
     n_pairs = T - 1
-    if use_direct_solver:
+    # use_direct_solver=True (:1146-1147): the sparse direct solve on the device when its fronts fit (frames up to ~2048^2 on a
+    # B200), else the iterative solve with the tightest tolerance
+    direct_mode = bool(use_direct_solver) and engine.direct_solve_fits(Nx, Ny, dev)
+    if use_direct_solver and not direct_mode:
         rtol = min(rtol, 1e-12)
     solver_options = dict(solver_options or {})
     itemsize = 4 if tdtype == torch.float32 else 8
@@ -365,6 +385,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info = dict(iterations=np.zeros(n_pairs, np.int32), relative_residual=np.zeros(n_pairs),
                 recurrence_residual=np.zeros(n_pairs), converged=np.zeros(n_pairs, bool), fallback=np.zeros(n_pairs, bool))
     workspace = engine.Workspace()
+    direct_workspace = engine.Workspace()                                      # allocated only if a direct solve happens
     nplanes = 5 if blur else 4                                                 # v_x, v_y, speed, remodelling (, blurred)
     main_stream = torch.cuda.current_stream(dev)
     copy_stream = _copy_stream(dev)
@@ -409,7 +430,7 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
                     x0[:, q] = guess[q]
             t_prep = time.perf_counter()
             x, iters, relres, conv, fb, recur = _solve_pairs(P, C, speed_alpha, remodelling_alpha, x0, rtol, max_it,
-                                                             preconditioner, workspace, solver_options)
+                                                             preconditioner, workspace, solver_options, direct_mode, direct_workspace)
             t_solve = time.perf_counter()
             if warm_start:
                 previous_last = x[-1:].clone()
@@ -524,12 +545,13 @@ def variational_optical_flow(movie, delta_x=1.0, delta_t=1.0, speed_alpha=1.0, r
     info['d2h_bytes'] = int((len(wire_planes) * n_pairs + (T if ship_blur else 0)) * Nx * Ny * (wire.itemsize if direct else itemsize))
     info['speed_on_host'] = bool(host_speed)
     info['direct_egress'] = bool(direct)
+    info['direct_solver'] = bool(direct_mode)
     result['solver_info'] = info
     return result
 
 
 def _sweep_pairs(movie_np, first_pair, last_pair, cell_alpha, cell_beta, dev, tdtype, smoothing_sigma, guess, scale, rtol, max_it,
-                 preconditioner, solver_options, batch_entries):
+                 preconditioner, solver_options, batch_entries, direct_mode=False):
     """Pairs [first_pair, last_pair) of the movie x every (alpha, beta) cell on one device.  Returns host arrays
     (moments [cells, 4], functional [cells], converged of the last pair handled [cells])."""
     n_cells = cell_alpha.size
@@ -540,6 +562,7 @@ def _sweep_pairs(movie_np, first_pair, last_pair, cell_alpha, cell_beta, dev, td
     fun_dev = torch.zeros(n_cells, dtype=torch.float64, device=dev)
     conv_dev = torch.zeros(n_cells, dtype=torch.int32, device=dev)
     workspace = engine.Workspace()
+    direct_workspace = engine.Workspace()
     # entries = (pair, cell), pairs outermost, solved in batches that span pairs: 4 pairs x 16 cells fill a 64-entry solve
     pairs_per_batch = max(1, int(round(batch_entries / float(n_cells))))     # 11 cells: 6 pairs = 66 entries, not 5 = 55
     cells_per_batch = min(n_cells, batch_entries)
@@ -559,7 +582,8 @@ def _sweep_pairs(movie_np, first_pair, last_pair, cell_alpha, cell_beta, dev, td
             x0 = torch.empty((nc * npairs, 3, Nx, Ny), dtype=tdtype, device=dev)
             for q in range(3):
                 x0[:, q] = guess[q]
-            x, iters, relres, conv, fb, _ = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace, solver_options)
+            x, iters, relres, conv, fb, _ = _solve_pairs(P, C, a, be, x0, rtol, max_it, preconditioner, workspace, solver_options,
+                                                         direct_mode, direct_workspace)
             _, _, _, _, fun, mom = engine.epilogue(P, C, x, a, be, scale)
             mom_dev[c0:c1] += mom.view(npairs, nc, 4).sum(dim=0)
             # L1 + 'speed' (= remodelling, :1205) + remodelling
@@ -596,12 +620,14 @@ def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
     smoothing_sigma = kwargs.pop('smoothing_sigma', None)
     guess = (float(kwargs.pop('initial_v_x', 0.0)) * delta_t / delta_x,
              float(kwargs.pop('initial_v_y', 0.0)) * delta_t / delta_x, float(kwargs.pop('initial_remodelling', 0.0)))
-    if kwargs.pop('use_direct_solver', False):
-        rtol = min(rtol, 1e-12)
+    use_direct = bool(kwargs.pop('use_direct_solver', False))
     if kwargs:
         raise TypeError('unexpected keyword arguments: %s' % sorted(kwargs))
     movie_np = np.ascontiguousarray(np.asarray(movie))
     T, Nx, Ny = movie_np.shape
+    direct_mode = use_direct and engine.direct_solve_fits(Nx, Ny, devs[0])
+    if use_direct and not direct_mode:
+        rtol = min(rtol, 1e-12)
     n_pairs = T - 1
     alphas = np.asarray(speed_alpha_values, dtype=np.float64)
     betas = np.asarray(remodelling_alpha_values, dtype=np.float64)
@@ -618,7 +644,7 @@ def vary_regularisation(movie, speed_alpha_values=np.arange(500, 2000, 500),
         with torch.cuda.device(devs[rank]):
             B = int(batch_pairs) if batch_pairs else _default_batch(Nx, Ny, itemsize, n_cells * (stop - start), devs[rank], pipelined=False)
             return _sweep_pairs(movie_np, start, stop, cell_alpha, cell_beta, devs[rank], tdtype, smoothing_sigma, guess, scale, rtol,
-                                max_it, preconditioner, solver_options, B)
+                                max_it, preconditioner, solver_options, B, direct_mode)
 
     if len(devs) == 1:
         parts = [shard(0)]

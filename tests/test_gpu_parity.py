@@ -120,12 +120,14 @@ def test_direct_solve_matches_superlu(cuda_device, shape, alpha):
     want = [fo.solve_pair(movie[k], movie[k + 1], alpha, 1e4)[0] for k in range(2)]
     Pd, Cd = dev_t(movie[:-1], cuda_device), dev_t(movie[1:], cuda_device)
     b = engine.build_rhs(Pd, Cd)
-    x, rr = engine.direct_solve(Pd, b, alpha, 1e4)
+    x, rr, cv = engine.direct_solve(Pd, b, alpha, 1e4)
+    assert cv.tolist() == [1, 1]
     for k in range(2):
         assert rel(x[k].cpu().numpy(), want[k]) < 1e-9, (k, float(rr[k]))         # raw solution, ghost ring included
         assert float(rr[k]) < 1e-10
     # float32 images and right-hand side, fp64 factorisation: within the float32 tolerance
-    x32, rr32 = engine.direct_solve(Pd.float().contiguous(), b.float().contiguous(), alpha, 1e4)
+    x32, rr32, cv32 = engine.direct_solve(Pd.float().contiguous(), b.float().contiguous(), alpha, 1e4)
+    assert cv32.tolist() == [1, 1]
     for k in range(2):
         assert rel(x32[k].cpu().double().numpy(), want[k]) < 1e-3
 
@@ -235,18 +237,37 @@ def test_float32_pairs_that_stall_are_redone_in_float64(cuda_device):
         assert np.abs(got[key] - want[key]).max() < 1e-2
 
 
-def test_low_alpha_regime_falls_back_and_still_matches(cuda_device):
-    """Regularisation weights where the multigrid cycle is not contractive: the block-Jacobi path must take over."""
-    movie = fo.blur_movie(synthetic.translating_movie(32, 32, 2, seed=13), 2.5)
-    want = fo.variational_optical_flow(movie, speed_alpha=1e3, remodelling_alpha=1e4)
-    got = optical_flow.variational_optical_flow(movie, speed_alpha=1e3, remodelling_alpha=1e4, rtol=1e-11, max_it=300,
-                                                solver_options=dict())
-    if not got['converged']:
-        got = optical_flow.variational_optical_flow(movie, speed_alpha=1e3, remodelling_alpha=1e4, rtol=1e-11,
-                                                    max_it=20000, preconditioner='bjacobi')
-    assert got['converged']
-    for key in ('v_x', 'v_y', 'remodelling'):
-        assert rel(got[key], want[key]) < 1e-6
+@pytest.mark.parametrize('N,alpha', [(256, 1e3), (128, 4.64e3), (128, 2.15e4)])
+def test_low_alpha_regime_matches_the_oracle(cuda_device, N, alpha):
+    """speed_alpha below ~max I^2 / 1.5: the operator is indefinite (profiles/r02_indefinite_regime.txt), the multigrid
+    BiCGStab does not converge, and the pairs go to the sparse direct solve - no rescue in the test.  The reference's real-data
+    regime (alpha = 2e4 on 8-bit frames, analysis/analyse_variational_optical_flow.py:114) and config d-4's lowest cells."""
+    movie = synthetic.rotating_shearing_movie(N, N, 2, seed=2)
+    kw = dict(speed_alpha=alpha, remodelling_alpha=1e4, smoothing_sigma=2.5)
+    want = fo.variational_optical_flow(movie, **kw)
+    got64 = optical_flow.variational_optical_flow(movie, dtype='float64', rtol=1e-10, **kw)         # parity setting of north_star
+    got32 = optical_flow.variational_optical_flow(movie, dtype='float32', rtol=1e-6, **kw)
+    for got, tol in ((got64, 1e-6), (got32, 1e-3)):
+        assert got['converged'] and got['solver_info']['converged'].all()
+        for key in ('v_x', 'v_y', 'remodelling'):
+            assert rel(got[key], want[key]) < tol, (key, got['solver_info'])
+    assert np.abs(got32['v_x'] - want['v_x']).max() < 1e-2 and np.abs(got32['v_y'] - want['v_y']).max() < 1e-2
+    if N == 256:
+        assert got64['solver_info']['fallback'].all()          # 256^2 at alpha = 1e3: the Krylov path cannot have converged
+
+
+@pytest.mark.parametrize('name', GOLDEN_NAMES)
+def test_use_direct_solver_reproduces_the_reference_direct_branch(cuda_device, name):
+    """use_direct_solver=True (:1146-1147): the device's sparse direct solve against the golden outputs of the reference's own
+    SuperLU branch - no iteration, no tolerance to choose."""
+    z, kwargs = load_golden(name)
+    got = optical_flow.variational_optical_flow(z['movie'], use_direct_solver=True, **kwargs)
+    assert got['solver_info']['direct_solver'] and got['converged'] and (got['solver_info']['iterations'] == 0).all()
+    for key in ('v_x', 'v_y', 'speed', 'remodelling'):
+        assert rel(got[key], z[key]) < 1e-8, key
+    fun = np.array([got['L1_functional'], got['remodelling_functional'], got['speed_functional']])
+    np.testing.assert_allclose(fun, z['functionals'], rtol=1e-8)
+    assert got['solver_info']['relative_residual'].max() < 1e-9
 
 
 # ------------------------------------------------------------------ bench sizes, anchored to the ORACLE operator

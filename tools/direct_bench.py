@@ -16,10 +16,10 @@ for N in sizes:
         ws = engine.Workspace()
         t0 = time.perf_counter(); engine._direct_plan(N, N, dev); plan_s = time.perf_counter() - t0
         for alpha in (1e5, 1e3):
-            x, rr = engine.direct_solve(P, b, alpha, 1e4, ws)            # warm-up (handles, workspace)
+            x, rr, cv = engine.direct_solve(P, b, alpha, 1e4, ws)        # warm-up (handles, workspace)
             torch.cuda.synchronize()
             t0 = time.perf_counter()
-            x, rr = engine.direct_solve(P, b, alpha, 1e4, ws)
+            x, rr, cv = engine.direct_solve(P, b, alpha, 1e4, ws)
             torch.cuda.synchronize()
             dt = (time.perf_counter() - t0) / P.shape[0]
             line = dict(frame=N, dtype=str(dtype).replace('torch.', ''), alpha=alpha, seconds_per_pair=round(dt, 4), relres=[float('%.3g' % v) for v in rr.tolist()],

@@ -1,5 +1,6 @@
 """Config d-4's regularisation sweep (speed_alpha = logspace(3, 8, 16), remodelling_alpha 1e4) on 1024^2 d-3 pairs:
-iterations and time of the default cycle, the V(2,2)/0.8 fallback and plain block-Jacobi BiCGStab per alpha."""
+iterations and time of the default cycle, the V(2,2)/0.8 fallback and plain block-Jacobi BiCGStab per alpha; mode `dropin`
+is what the drop-in does with a batch (multigrid BiCGStab probe, then the sparse direct solve for what it left)."""
 import argparse
 import json
 import os
@@ -10,7 +11,7 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from opticalflow_b200 import engine, synthetic  # noqa: E402
+from opticalflow_b200 import engine, optical_flow, synthetic  # noqa: E402
 
 
 def main():
@@ -34,9 +35,22 @@ def main():
     modes = {'default': engine.make_options('mg'), 'v22': engine.make_options('mg', nu_pre=2, nu_post=2, omega=0.8),
              'bjacobi': engine.make_options('bjacobi')}
     names = a.modes.split(',')
+    ws, dws = engine.Workspace(), engine.Workspace()
     for al in alphas:
         line = {'alpha': al, 'beta': a.beta}
         for name in names:
+            if name == 'dropin':
+                x0 = torch.zeros_like(b)
+                for rep in range(2):                      # the first pass allocates the workspaces
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record()
+                    x, it, rr, cv, fb, rec = optical_flow._solve_pairs(P, C, al, a.beta, x0, 1e-6, a.max_it, 'mg', ws, {}, False, dws)
+                    e1.record()
+                    torch.cuda.synchronize()
+                line[name] = dict(iters=float(it.float().mean()), conv=int(cv.sum()), direct=int(fb.sum()),
+                                  ms_per_pair=round(e0.elapsed_time(e1) / B, 2), relres=float(rr.max()))
+                continue
             av = torch.full((B,), al, dtype=torch.float64, device=dev)
             bv = torch.full((B,), a.beta, dtype=torch.float64, device=dev)
             x = torch.zeros_like(b)
