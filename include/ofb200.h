@@ -237,7 +237,7 @@ int ofb_subtract_background(const void* movie, const void* blurred, void* out, d
  * arrays that depend on the frame shape only) is built on the host (opticalflow_b200/ndplan.py) and handed in as
  * `levels`, root first: per level the padded pixel counts and DEVICE arrays of int32 pixel ids (i * (Ny-2) + j over the
  * interior, -1 = padding).  The array of structs itself lives in host memory.  Dense kernels are cuBLAS / cuSOLVER.
- * One pair is factorised and solved at a time (0.6 s per 1024^2 pair on a B200; ~28 GB of workspace).  relres_out
+ * One pair is factorised and solved at a time (0.22 s per 1024^2 pair on a B200; ~28 GB of workspace).  relres_out
  * (device, B doubles, may be NULL): |b - A x| / |b| recomputed from the returned x (:1150-1151); converged_out (device,
  * B ints, may be NULL): ofb_solve's verdict on it, |b - A x| <= rtol |b| + 8 u |D x|.  x3: out only.
  * ------------------------------------------------------------------------------------------------------- */

@@ -1642,7 +1642,15 @@ namespace {
 
 constexpr int ND_BATCHED_MAX = 128;       // owned variables per node up to which the batched cuBLAS LU is used
 
-struct DenseHandles { cublasHandle_t blas = nullptr; cusolverDnHandle_t solver = nullptr; };
+constexpr int ND_STREAMS = 8;             // side streams for the per-node LU of the mid-size fronts (one getrf cannot fill the GPU)
+struct DenseHandles {
+    cublasHandle_t blas = nullptr;
+    cusolverDnHandle_t solver = nullptr;                   // on the caller's stream
+    cusolverDnHandle_t side_solver[ND_STREAMS] = {};       // one per side stream
+    cudaStream_t side[ND_STREAMS] = {};
+    cudaEvent_t fork = nullptr, join[ND_STREAMS] = {};
+    std::mutex busy;                                       // the side streams and events serve one direct solve per device at a time
+};
 int dense_handles(DenseHandles** out) {
     static DenseHandles handles[MAX_DEVICES];
     static std::mutex mu;
@@ -1653,7 +1661,29 @@ int dense_handles(DenseHandles** out) {
     DenseHandles& h = handles[dev];
     if (h.blas == nullptr) OFB_CHECK_CUBLAS(cublasCreate(&h.blas));
     if (h.solver == nullptr) OFB_CHECK_CUSOLVER(cusolverDnCreate(&h.solver));
+    if (h.fork == nullptr) {
+        OFB_CHECK_CUDA(cudaEventCreateWithFlags(&h.fork, cudaEventDisableTiming));
+        for (int k = 0; k < ND_STREAMS; ++k) {
+            OFB_CHECK_CUDA(cudaStreamCreateWithFlags(&h.side[k], cudaStreamNonBlocking));
+            OFB_CHECK_CUDA(cudaEventCreateWithFlags(&h.join[k], cudaEventDisableTiming));
+            OFB_CHECK_CUSOLVER(cusolverDnCreate(&h.side_solver[k]));
+            OFB_CHECK_CUSOLVER(cusolverDnSetStream(h.side_solver[k], h.side[k]));
+        }
+    }
     *out = &h;
+    return 0;
+}
+// side streams wait for what the caller's stream has queued so far / the caller's stream waits for the side streams
+int nd_fork(DenseHandles* H, cudaStream_t stream, int n_used) {
+    OFB_CHECK_CUDA(cudaEventRecord(H->fork, stream));
+    for (int k = 0; k < n_used; ++k) OFB_CHECK_CUDA(cudaStreamWaitEvent(H->side[k], H->fork, 0));
+    return 0;
+}
+int nd_join(DenseHandles* H, cudaStream_t stream, int n_used) {
+    for (int k = 0; k < n_used; ++k) {
+        OFB_CHECK_CUDA(cudaEventRecord(H->join[k], H->side[k]));
+        OFB_CHECK_CUDA(cudaStreamWaitEvent(stream, H->join[k], 0));
+    }
     return 0;
 }
 
@@ -1701,10 +1731,10 @@ int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, vo
     W->F12ptr = (double**)take(max_nodes * sizeof(double*));
     W->zptr = (double**)take(max_nodes * sizeof(double*));
     W->getrf_lwork = lwork;
-    W->getrf_work = (double*)take((size_t)std::max(lwork, 1) * sizeof(double));
+    W->getrf_work = (double*)take((size_t)std::max(lwork, 1) * ND_STREAMS * sizeof(double));       // one slice per side stream
     W->st = (PairState*)take(sizeof(PairState) * (size_t)B);
     W->active = (int*)take(sizeof(int) * (size_t)B);
-    W->scratch_info = (int*)take(sizeof(int) * 4);
+    W->scratch_info = (int*)take(sizeof(int) * ND_STREAMS);
     W->bytes = off;
     return 0;
 }
@@ -1715,6 +1745,7 @@ int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, c
                 int Ny, cudaStream_t stream) {
     DenseHandles* H = nullptr;
     if (int rc = dense_handles(&H)) return rc;
+    std::lock_guard<std::mutex> one_at_a_time(H->busy);
     OFB_CHECK_CUBLAS(cublasSetStream(H->blas, stream));
     OFB_CHECK_CUSOLVER(cusolverDnSetStream(H->solver, stream));
     NdWorkspace W;
@@ -1754,12 +1785,18 @@ int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, c
                                                      &info, L.n_nodes));
                 if (info != 0) return fail(-51, "direct solve: cublasDgetrsBatched argument %d invalid", -info);
             } else {
+                // the few hundred mid-size fronts: one getrf + getrs per node, the nodes of the level dealt over side streams
+                const int used = std::min(ND_STREAMS, L.n_nodes);
+                if (int rc = nd_fork(H, stream, used)) return rc;
                 for (int n = 0; n < L.n_nodes; ++n) {
                     double* F = L.F + stride * n;
-                    OFB_CHECK_CUSOLVER(cusolverDnDgetrf(H->solver, no3, no3, F, nf, W.getrf_work, L.piv + (long long)n * no3, L.info + n));
-                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->solver, CUBLAS_OP_N, no3, nb3, F, nf, L.piv + (long long)n * no3,
-                                                        F + (long long)no3 * nf, nf, W.scratch_info));
+                    const int k = n % used;
+                    OFB_CHECK_CUSOLVER(cusolverDnDgetrf(H->side_solver[k], no3, no3, F, nf, W.getrf_work + (size_t)k * W.getrf_lwork,
+                                                        L.piv + (long long)n * no3, L.info + n));
+                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->side_solver[k], CUBLAS_OP_N, no3, nb3, F, nf, L.piv + (long long)n * no3,
+                                                        F + (long long)no3 * nf, nf, W.scratch_info + k));
                 }
+                if (int rc = nd_join(H, stream, used)) return rc;
             }
             // S = F22 - F21 X, in place in the F22 block of every front of the level
             OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, nb3, no3, &minus_one, L.F + no3, nf, stride,
@@ -1790,9 +1827,12 @@ int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, c
                 OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, 1, (const double* const*)W.Fptr, nf, L.piv, W.zptr, no3, &info,
                                                      L.n_nodes));
             } else {
+                const int used = std::min(ND_STREAMS, L.n_nodes);
+                if (int rc = nd_fork(H, stream, used)) return rc;
                 for (int n = 0; n < L.n_nodes; ++n)
-                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->solver, CUBLAS_OP_N, no3, 1, L.F + stride * n, nf, L.piv + (long long)n * no3,
-                                                        W.z + (long long)n * no3, no3, W.scratch_info));
+                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->side_solver[n % used], CUBLAS_OP_N, no3, 1, L.F + stride * n, nf,
+                                                        L.piv + (long long)n * no3, W.z + (long long)n * no3, no3, W.scratch_info + n % used));
+                if (int rc = nd_join(H, stream, used)) return rc;
             }
             k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
             OFB_CHECK_LAUNCH();

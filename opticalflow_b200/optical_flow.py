@@ -202,7 +202,7 @@ def _solve_pairs(P, C, alpha, beta, x0, rtol, max_it, preconditioner, workspace,
     """Solve a batch.  ``direct``: every pair by the sparse direct solve (the reference's ``use_direct_solver=True`` branch,
     :1146-1147).  Otherwise multigrid-preconditioned BiCGStab; pairs it has not converged after PROBE_IT iterations are in
     the regime where the operator is indefinite (speed_alpha below ~max I^2 / 1.5) and go to the direct
-    solve when its fronts fit on the device (0.6 s per 1024^2 pair).  Where they do not fit (very large frames) the older chain
+    solve when its fronts fit on the device (0.22 s per 1024^2 pair).  Where they do not fit (very large frames) the older chain
     applies: the robust V(2,2) cycle, float64, block-Jacobi; a pair none of them converges is reported like the reference
     reports it (:1137-1138): ``converged`` False, best iterate returned."""
     B, Nx, Ny = P.shape
