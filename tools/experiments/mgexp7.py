@@ -1,15 +1,22 @@
 import sys, time
-sys.path.insert(0, '/tmp/exp')
+sys.path.insert(0, __import__("os").path.dirname(__import__("os").path.abspath(__file__)))
 import gpuh
 from gpuh import *
 from opticalflow_b200 import synthetic
 N = int(sys.argv[1]); fix = int(sys.argv[2]); gam = [int(c) for c in sys.argv[3]] if len(sys.argv) > 3 else [1]*12
-alpha, beta = 1e5, 1e4
+alpha, beta = float(__import__('os').environ.get('ALPHA', 1e5)), 1e4
 movie = fo.blur_movie(synthetic.rotating_shearing_movie(N, N, 2, seed=2), 2.5)
 P, C = movie
 b = mg.zero_ghosts(fo.build_rhs(P, C))
-H = GH(P, alpha, beta, coef_mode='avg')
+import os
+H = GH(P, alpha, beta, coef_mode=os.environ.get('COEF_MODE', 'avg'))
 shapes = H.shapes
+if os.environ.get('COEF_ROUND'):
+    for _l in range(1, len(H.c)):
+        if os.environ['COEF_ROUND'] == 'f16':
+            H.c[_l] = H.c[_l].astype(np.float16).astype(np.float64)
+        else:      # bfloat16: keep 8 significant bits
+            _v = np.ascontiguousarray(H.c[_l].astype(np.float32)).view(np.uint32); _v = ((_v + 0x8000) & 0xFFFF0000).astype(np.uint32); H.c[_l] = _v.view(np.float32).astype(np.float64)
 # far-side rule per level and axis: 0 = node mirror (ghost = q(N-3)), 1 = midpoint mirror (ghost = q(N-2))
 far = [(0, 0)]
 pos = [(0.0, 0.0)]   # delta (axis offset beyond last interior node, in units of this level's cells)
