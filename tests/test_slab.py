@@ -62,3 +62,24 @@ def test_slab_solve_matches_single_gpu(cases):
     assert lines and all(l['ok'] for l in lines)
     for l in lines:
         assert abs(l['iterations'] - l['iterations_single']) <= 1
+
+
+@pytest.mark.gpu
+def test_slab_solve_matches_the_oracle(tmp_path):
+    """The slab-decomposed solve on two ranks against the ORACLE's direct solve of the same pair (the reference's matrix and SuperLU,
+    oracle/flow_oracle.py) - not only against the single-GPU solve: a 160 x 1024 pair, float64, rtol 1e-11."""
+    import torch
+    from oracle import flow_oracle as fo
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs (run with gpurun --gpus 2)')
+    dump = str(tmp_path / 'slab_result.npz')
+    cmd = [sys.executable, '-m', 'torch.distributed.run', '--nnodes=1', '--nproc-per-node', '2', '--master-addr', '127.0.0.1',
+           '--master-port', '29518', os.path.join(ROOT, 'tools', 'slab_check.py'), '--cases', 'oracle', '--dump', dump]
+    out = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
+    z = np.load(dump)
+    want = fo.variational_optical_flow(z['movie'], speed_alpha=float(z['alpha']), remodelling_alpha=float(z['beta']),
+                                       smoothing_sigma=float(z['sigma']))
+    for key in ('v_x', 'v_y', 'speed', 'remodelling'):
+        err = np.linalg.norm(z[key] - want[key]) / np.linalg.norm(want[key])
+        assert err < 1e-6, (key, err)

@@ -27,6 +27,8 @@ CASES = {
     'medium': [(1024, 1024, 'float32', 1e-6, 0, 2.5, 1e-3), (1024, 1024, 'float64', 1e-10, 0, 2.5, 1e-6),
                (2048, 1024, 'float32', 1e-6, 3, 2.5, 1e-3)],
     'd5': [(8192, 8192, 'float32', 1e-6, 0, 2.5, 1e-3)],
+    # wide and short: what tests/test_slab.py also holds to the oracle's SuperLU solve (--dump)
+    'oracle': [(160, 1024, 'float64', 1e-11, 0, 2.5, 1e-6)],
 }
 
 
@@ -47,6 +49,7 @@ def main():
     ap.add_argument('--alpha', type=float, default=1e5)
     ap.add_argument('--beta', type=float, default=1e4)
     ap.add_argument('--repeats', type=int, default=3)
+    ap.add_argument('--dump', default='', help='rank 0: save the movie and the gathered slab result of the last case to this .npz')
     args = ap.parse_args()
     rank, world = int(os.environ['RANK']), int(os.environ['WORLD_SIZE'])
     torch.cuda.set_device(int(os.environ.get('LOCAL_RANK', rank)))
@@ -129,6 +132,9 @@ def main():
             failed += 0 if ok else 1
         if rank == 0:
             print(json.dumps(line), flush=True)
+            if args.dump and res is not None and 'v_x' in res:
+                np.savez(args.dump, movie=movie, sigma=np.array(np.nan if sigma is None else sigma), alpha=np.array(args.alpha),
+                         beta=np.array(args.beta), **{k: res[k] for k in ('v_x', 'v_y', 'speed', 'remodelling')})
     dist.barrier()
     comm.close()
     dist.destroy_process_group()
