@@ -21,6 +21,7 @@ FLAG_NO_HALF_STEP_EXIT = 128
 FLAG_SERIAL_SETUP = 256
 FLAG_FUSED_PROLONG = 512
 FLAG_POLL_AHEAD = 1024
+FLAG_FP32_COEF = 2048
 ABI_VERSION = 6
 
 # every symbol include/ofb200.h declares

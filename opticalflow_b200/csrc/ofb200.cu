@@ -291,6 +291,8 @@ template <typename T> struct Workspace {
     PairState* st; int* active; int* n_active;
     T *r, *rhat, *p, *v, *s, *t, *ph, *sh, *zalt;              // level-0 vectors
     T* coef[MAX_LEVELS];                                      // level >= 1: 7 coefficient planes per pair
+    unsigned short* coef16[MAX_LEVELS];                       // float solves, levels wide enough for the streamed sweep: bfloat16 copies
+    int pitch16[MAX_LEVELS];
     T *lb[MAX_LEVELS], *xa[MAX_LEVELS], *xb[MAX_LEVELS], *res[MAX_LEVELS];
     double* dense_M; T* dense_Minv; int* dense_piv;
     T* stage;                                                 // slab solves: local planes at the gather level (7 per pair)
@@ -312,6 +314,10 @@ Workspace<T> carve(void* base, int B, const Plan& plan) {
     for (int l = 1; l < plan.nlevels; ++l) {
         const size_t planeb = (size_t)plan.lv[l].plane * B * sizeof(T);
         w.coef[l] = (T*)take(NCOEF * planeb);
+        if (sizeof(T) == 4 && plan.gather_level == 0 && plan.lv[l].Ny >= 2 * WARP * VecOf<T>::V) {
+            w.pitch16[l] = (plan.lv[l].Ny + 7) / 8 * 8;
+            w.coef16[l] = (unsigned short*)take((size_t)NCOEF * plan.lv[l].Nx * w.pitch16[l] * B * sizeof(unsigned short));
+        }
         w.lb[l] = (T*)take(3 * planeb);
         w.xa[l] = (T*)take(3 * planeb);
         w.xb[l] = (T*)take(3 * planeb);
@@ -502,6 +508,11 @@ template <typename T> struct Solver {
         else { L.coef = w.coef[l]; L.coef_pair = (long long)NCOEF * g[l].plane; }
         L.alpha = alpha; L.beta = beta; L.active = active;
         L.h2 = 1.0 / ((double)(1 << l) * (double)(1 << l));
+        L.coef16 = nullptr; L.pitch16 = 0; L.plane16 = 0; L.pair16 = 0;
+        if (l >= 1 && w.coef16[l] != nullptr && use_stream(l) && !slab.on && (opt.flags & OFB_FLAG_FP32_COEF) == 0) {
+            L.coef16 = w.coef16[l]; L.pitch16 = w.pitch16[l];
+            L.plane16 = (long long)g[l].Nx * w.pitch16[l]; L.pair16 = (long long)NCOEF * L.plane16;
+        }
         constexpr int V = VecOf<T>::V;
         L.tiles_x = (g[l].Ny + WARP * V - 1) / (WARP * V);
         int R = opt.rows_per_strip;
@@ -582,6 +593,15 @@ template <typename T> struct Solver {
             OFB_CHECK_LAUNCH();
             if (to_stage) { if ((rc = gather_planes(w.stage, out_pair, w.coef[l], (long long)NCOEF * g[l].plane, NCOEF))) return rc; }
             else if ((rc = exchange(l, w.coef[l], NCOEF, out_pair))) return rc;
+            if constexpr (sizeof(T) == 4) {
+                // bfloat16 copies of the planes for the streamed sweeps of this level (the next level is still restricted from fp32)
+                if (w.coef16[l] != nullptr && use_stream(l) && !slab.on && (opt.flags & OFB_FLAG_FP32_COEF) == 0) {
+                    dim3 pgrid((w.pitch16[l] + 127) / 128, g[l].Nx, B * NCOEF);
+                    k_pack_bf16<<<pgrid, 128, 0, stream>>>(g[l], (const float*)w.coef[l], w.coef16[l], w.pitch16[l],
+                                                          (long long)g[l].Nx * w.pitch16[l]);
+                    OFB_CHECK_LAUNCH();
+                }
+            }
         }
         if (plan.dense) {
             const int l = plan.nlevels - 1;

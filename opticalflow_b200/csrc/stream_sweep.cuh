@@ -158,6 +158,18 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
             const uint32_t bytes = (uint32_t)(hi - lo) * (uint32_t)sizeof(T);
             const int nk = i_end - i_begin + 2;
             const T* base = nullptr;
+            // coarse levels, float: the coefficient rows come from the bfloat16 planes (half the bytes; no halo columns needed)
+            bool coef_half = false;
+            const unsigned short* base16 = nullptr;
+            uint32_t bytes16 = 0;
+            if constexpr (!FROM_IMAGE && sizeof(T) == 4) {
+                if (L.coef16 != nullptr) {
+                    bytes16 = (uint32_t)(min(c0 + C::TW, L.pitch16) - c0) * 2u;
+                    coef_half = lane >= NWIN + NCOR + 3 * Op::NCEN && lane < NLANES;
+                    if (coef_half)
+                        base16 = L.coef16 + (long long)pair * L.pair16 + (long long)(lane - NWIN - NCOR - 3 * Op::NCEN) * L.plane16 + c0;
+                }
+            }
             uint32_t cbytes = 0;                    // bytes of one coarse correction row of this tile
             int cpitch = 0;
             if constexpr (PROLONG) {
@@ -184,7 +196,11 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                 const uint32_t ph = (n / STAGES) & 1u;
                 mbar_wait_sleep(empty + s, ph ^ 1u, 256);
                 const bool cen_valid = k >= 2;
-                if (lane == 0) mbar_arrive_expect_tx(full + s, (uint32_t)(cen_valid ? NWIN + NCENROWS : NWIN) * bytes + (uint32_t)NCOR * cbytes);
+                if (lane == 0) {
+                    uint32_t tx = (uint32_t)(cen_valid ? NWIN + NCENROWS : NWIN) * bytes + (uint32_t)NCOR * cbytes;
+                    if (bytes16 != 0 && cen_valid) tx = (uint32_t)(NWIN + 3 * Op::NCEN) * bytes + (uint32_t)NCOEF * bytes16;
+                    mbar_arrive_expect_tx(full + s, tx);
+                }
                 __syncwarp();
                 bool cor_done = false;
                 if constexpr (PROLONG) {
@@ -196,7 +212,12 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                         cor_done = true;
                     }
                 }
-                if (!cor_done && lane < NLANES && (is_win || cen_valid)) {
+                if (coef_half) {
+                    // the row slot of the plane, from its first element: 1024 bytes of bfloat16 in a 2080-byte slot
+                    if (cen_valid)
+                        bulk_g2s(ring + s * Lay::STAGE_ELEMS + (lane - NCOR + Lay::NCORSLOTS) * C::ROW,
+                                 base16 + (long long)(i_begin - 2 + k) * L.pitch16, bytes16, full + s);
+                } else if (!cor_done && lane < NLANES && (is_win || cen_valid)) {
                     int row;
                     if (is_win) {
                         row = i_begin - 1 + k;
@@ -294,12 +315,28 @@ __global__ void __launch_bounds__(StreamCfg<T>::THREADS, 3) k_stream(LevelArgs<T
                     if constexpr (!FROM_IMAGE) {
                         using VT = typename VecOf<T>::type;
                         T cr[NCOEF][V];
+                        bool half_rows = false;
+                        if constexpr (sizeof(T) == 4) half_rows = L.coef16 != nullptr;
+                        if (half_rows) {
+                            if constexpr (sizeof(T) == 4) {
+                                // four bfloat16 of this lane's columns: 8 bytes at (j0 - c0) elements into the plane's row slot
+                                const unsigned short* slot0 = reinterpret_cast<const unsigned short*>(ring + s * Lay::STAGE_ELEMS +
+                                                                                                      (NAHEAD + 3 * Op::NCEN) * C::ROW) + (j0 - c0);
+#pragma unroll
+                                for (int q = 0; q < NCOEF; ++q) {
+                                    const uint2 raw = *reinterpret_cast<const uint2*>(slot0 + (long long)q * C::ROW * 2);
+                                    cr[q][0] = __uint_as_float(raw.x << 16); cr[q][1] = __uint_as_float(raw.x & 0xffff0000u);
+                                    cr[q][2] = __uint_as_float(raw.y << 16); cr[q][3] = __uint_as_float(raw.y & 0xffff0000u);
+                                }
+                            }
+                        } else {
 #pragma unroll
                         for (int q = 0; q < NCOEF; ++q) {
                             const VT t = *reinterpret_cast<const VT*>(stg + (NAHEAD + 3 * Op::NCEN + q) * C::ROW + j0);
                             const T* p = reinterpret_cast<const T*>(&t);
 #pragma unroll
                             for (int kk = 0; kk < V; ++kk) cr[q][kk] = p[kk];
+                        }
                         }
 #pragma unroll
                         for (int kk = 0; kk < V; ++kk) {

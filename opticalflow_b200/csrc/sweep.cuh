@@ -24,6 +24,12 @@ template <typename T> struct LevelArgs {
     int tile_fastest;       // streamed sweep: consecutive work items are neighbouring column tiles of one strip
     int n_pairs;            // streamed sweep: batch size
     int balanced;           // streamed sweep: equal row ranges per CTA instead of strips (WorkWalk in stream_sweep.cuh)
+    // streamed sweeps on coarse levels (float only): the 7 coefficient planes as bfloat16, [B][7][Nx][pitch16]; nullptr = read `coef`.
+    // Halves the coefficient traffic of a coarse sweep (16 -> 12.5 words per pixel); a preconditioner does not notice the 8-bit
+    // mantissa (numpy study: identical iteration counts).
+    const unsigned short* coef16;
+    int pitch16;            // elements per row, a multiple of 8 (16-byte rows for the bulk copies)
+    long long plane16, pair16;
 };
 
 template <typename T, bool FROM_IMAGE> struct CoefRows {

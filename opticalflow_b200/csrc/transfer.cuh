@@ -147,6 +147,19 @@ __global__ void __launch_bounds__(128) k_prolong_add4(Geom gc, const float* __re
     }
 }
 
+// float32 coefficient planes [B][7][Nx][pitch] -> bfloat16 copies [B][7][Nx][pitch16] (round to nearest even; columns beyond Ny: 0)
+__global__ void k_pack_bf16(Geom g, const float* __restrict__ coef, unsigned short* __restrict__ out, int pitch16, long long plane16) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    const int pq = blockIdx.z;                   // pair * NCOEF + plane
+    if (j >= pitch16) return;
+    float v = 0.0f;
+    if (j < g.Ny) v = coef[(long long)pq * g.plane + (long long)i * g.pitch + j];
+    unsigned u = __float_as_uint(v);
+    u += 0x7fffu + ((u >> 16) & 1u);             // round to nearest even on the upper 16 bits (no NaN/inf in coefficients)
+    out[(long long)pq * plane16 + (long long)i * pitch16 + j] = (unsigned short)(u >> 16);
+}
+
 // ------------------------------------------------------------------ coarsest level: dense inverse
 // Point evaluation of (S x)(i,j) for an arbitrary accessor, reusing apply_point (k = 1).
 template <typename T, typename Acc>
