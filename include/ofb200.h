@@ -46,6 +46,7 @@ extern "C" {
 #define OFB_FLAG_SERIAL_SETUP 256 /* dense coarsest-level inverse on the solve's own stream instead of beside the first fine sweeps (A/B) */
 #define OFB_FLAG_SLAB_NCCL_HALO 8 /* slab solves: halo rows by ncclSend/ncclRecv instead of peer stores (A/B measurements) */
 
+#define OFB_FLAG_BF16_RESIDUAL 4096 /* float solves: the V-cycle's residual (read by the restriction only) as bfloat16 (measured slower: off by default) */
 #define OFB_FLAG_FP32_COEF 2048 /* float solves: stream the coarse-level coefficient planes as float32 instead of their bfloat16 copies (A/B) */
 #define OFB_FLAG_POLL_AHEAD 1024 /* ofb_solve: enqueue iteration k+1 before reading iteration k's convergence count (measured slower: off by default) */
 

@@ -22,6 +22,7 @@ FLAG_SERIAL_SETUP = 256
 FLAG_FUSED_PROLONG = 512
 FLAG_POLL_AHEAD = 1024
 FLAG_FP32_COEF = 2048
+FLAG_BF16_RESIDUAL = 4096
 ABI_VERSION = 6
 
 # every symbol include/ofb200.h declares

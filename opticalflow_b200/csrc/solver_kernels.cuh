@@ -75,6 +75,8 @@ template <typename T, bool INIT> struct OpResidual {
     static constexpr int NCEN = 1;
     static constexpr int V = VecOf<T>::V;
     Geom g; const T* cen[1]; T* r; T* r2; PairState* st; double acc[1];      // cen[0] = b
+    int half_out;       // float, !INIT: r receives bfloat16 values (two-byte elements, same layout): a V-cycle's residual is read by the
+                        // restriction only (k_restrict<.., SRC16>), and right preconditioning does not care how the preconditioner rounds
     template <typename Cen>
     __device__ __forceinline__ void row(int pair, int i, int j0, const Coef<T> (&cf)[V], const T (&sx)[3][V],
                                         const T (&xc)[3][V], const bool (&inside)[V], T a, T be, const Cen& cv) {
@@ -88,6 +90,9 @@ template <typename T, bool INIT> struct OpResidual {
                 out[q][k] = inside[k] ? bq[k] - sx[q][k] : T(0);
                 if (INIT) acc[0] += (double)out[q][k] * (double)out[q][k];
             }
+        }
+        if constexpr (sizeof(T) == 4 && !INIT) {
+            if (half_out) { store3_bf16(reinterpret_cast<unsigned short*>(r), g, pair, i, j0, out); return; }
         }
         store3<T>(r, g, pair, i, j0, out);
         if (INIT) store3<T>(r2, g, pair, i, j0, out);

@@ -44,6 +44,30 @@ __device__ __forceinline__ void store3(T* __restrict__ base, const Geom& g, int 
 #pragma unroll
     for (int q = 0; q < 3; ++q) store_own<T>(p + q * g.plane, j0, g.Ny, g.aligned != 0, v[q]);
 }
+// the same values as bfloat16 (round to nearest even) into planes of two-byte elements with the layout of `g`
+__device__ __forceinline__ unsigned short to_bf16(float v) {
+    unsigned u = __float_as_uint(v);
+    u += 0x7fffu + ((u >> 16) & 1u);
+    return (unsigned short)(u >> 16);
+}
+__device__ __forceinline__ void store3_bf16(unsigned short* __restrict__ base, const Geom& g, int pair, int i, int j0, const float (&v)[3][4]) {
+    unsigned short* p = base + (long long)pair * g.pair + (long long)i * g.pitch;
+#pragma unroll
+    for (int q = 0; q < 3; ++q) {
+        unsigned short* row = p + q * g.plane;
+        if (g.aligned != 0 && j0 + 4 <= g.Ny) {
+            uint2 t;        // one cvt per pair of values: the upper half of the result is the first operand
+            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(t.x) : "f"(v[q][1]), "f"(v[q][0]));
+            asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(t.y) : "f"(v[q][3]), "f"(v[q][2]));
+            *reinterpret_cast<uint2*>(row + j0) = t;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (j0 + k < g.Ny) row[j0 + k] = to_bf16(v[q][k]);
+        }
+    }
+}
+
 template <typename T>
 __device__ __forceinline__ void load3(const T* __restrict__ base, const Geom& g, int pair, int i, int j0,
                                       T (&v)[3][VecOf<T>::V]) {

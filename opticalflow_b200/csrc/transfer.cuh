@@ -55,7 +55,9 @@ __global__ void k_coef_from_image(Geom gf, const T* __restrict__ P, Geom gc, T* 
 // Full-weighting restriction of `nplanes` planes, fine ghost ring by even reflection.
 //   COEF = true : coefficient planes (per-plane rescale for the halved hinv, ghost ring kept)
 //   COEF = false: residuals (coarse ghost ring set to 0)
-template <typename T, bool COEF>
+//   SRC16 = true: the fine planes hold bfloat16 values (same element layout, two bytes each): the residual a float V-cycle wrote for
+//                 nobody but this kernel (OpResidual::half_out)
+template <typename T, bool COEF, bool SRC16 = false>
 __global__ void k_restrict(Geom gf, const T* __restrict__ fine, long long fine_pair, Geom gc, T* __restrict__ coarse,
                            long long coarse_pair, int nplanes, const int* __restrict__ active) {
     pdl_enter();
@@ -75,13 +77,17 @@ __global__ void k_restrict(Geom gf, const T* __restrict__ fine, long long fine_p
     const T scale[NCOEF] = {T(0.25), T(0.5), T(1), T(1), T(1), T(0.5), T(1)};
     for (int q = 0; q < nplanes; ++q) {
         const T* f = fine + (long long)pair * fine_pair + (long long)q * gf.plane;
+        const unsigned short* f16 = reinterpret_cast<const unsigned short*>(fine) + (long long)pair * fine_pair + (long long)q * gf.plane;
         T acc = T(0);
         if (COEF || !ghost) {
 #pragma unroll
             for (int a = 0; a < 3; ++a) {
                 T rowacc = T(0);
 #pragma unroll
-                for (int b = 0; b < 3; ++b) rowacc += w3[b] * f[(long long)ii[a] * gf.pitch + jj[b]];
+                for (int b = 0; b < 3; ++b) {
+                    const long long idx = (long long)ii[a] * gf.pitch + jj[b];
+                    rowacc += w3[b] * (SRC16 ? T(__uint_as_float((unsigned)f16[idx] << 16)) : f[idx]);
+                }
                 acc += w3[a] * rowacc;
             }
             if (COEF) acc *= scale[q];
