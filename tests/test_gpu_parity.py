@@ -188,14 +188,15 @@ def test_dropin_256_config_d1(cuda_device):
     assert got64['solver_info']['iterations'][0] <= 40
 
 
-@pytest.mark.parametrize('variant', ['default', 'cells_split', 'batch_spans_pairs', 'two_threads'])
+@pytest.mark.parametrize('variant', ['default', 'cells_split', 'batch_spans_pairs', 'two_threads', 'many_pairs'])
 def test_vary_regularisation_matches_loop(cuda_device, variant):
     """2 pairs x 6 cells against a loop of oracle calls (optical_flow.py:1960-1983): the cells of a pair in one batch,
-    a pair's cells split over batches, one batch spanning both pairs, and the pairs sharded over two host threads."""
-    movie = synthetic.translating_movie(40, 48, 3, seed=12)
+    a pair's cells split over batches, one batch spanning both pairs, the pairs sharded over two host threads; and 11 pairs
+    in batches of 8 pairs of one cell each (the layout long sweeps use), the last batch a short one."""
+    movie = synthetic.translating_movie(40, 48, 12 if variant == 'many_pairs' else 3, seed=12)
     alphas, betas = np.array([2e4, 1e5]), np.array([1e3, 1e4, 1e5])
     extra = {'default': {}, 'cells_split': dict(batch_pairs=4), 'batch_spans_pairs': dict(batch_pairs=12),
-             'two_threads': dict(devices=['cuda:0', 'cuda:0'])}[variant]
+             'two_threads': dict(devices=['cuda:0', 'cuda:0']), 'many_pairs': dict(batch_pairs=8)}[variant]
     got = optical_flow.vary_regularisation(movie, alphas, betas, smoothing_sigma=2.0, rtol=1e-11, max_it=20000, **extra)
     assert got['speed_means'].shape == (2, 3) and got['converged'].dtype == bool
     for i, a in enumerate(alphas):
