@@ -53,6 +53,13 @@ def test_eliminated_operator_matches_model(cuda_device, shape, dtype, tol):
         assert rel(got[k], want) < tol
 
 
+# The float32 blur bar: a separable Gaussian of n = 2 int(4 sigma + 0.5) + 1 positive taps summed in float32 carries a relative error
+# of at most ~(n + 1) u per axis (u = 6e-8); on data in [0, 255] and both axes that is 255 * 2 * (n + 1) * u: 7e-4 at sigma 2.5 (n = 21),
+# 1.7e-3 at sigma 9 (n = 73).  2e-3 absolute is that worst-case bound, 1e-5 of the data range; the float32 flow tolerance (1e-3 relative)
+# is two orders of magnitude looser.  Float64 is held to 1e-10.
+BLUR32_TOL = 2e-3
+
+
 @pytest.mark.parametrize('shape', [(5, 5), (23, 31), (64, 64), (129, 257)])
 def test_rhs_and_blur(cuda_device, shape):
     rng = np.random.default_rng(9)
@@ -65,7 +72,7 @@ def test_rhs_and_blur(cuda_device, shape):
         got = engine.blur(d, sigma).cpu().numpy()
         assert np.abs(got - fo.blur_movie(movie, sigma)).max() < 1e-10
         got32 = engine.blur(d.float(), sigma).cpu().numpy()
-        assert np.abs(got32 - fo.blur_movie(movie, sigma)).max() < 2e-3
+        assert np.abs(got32 - fo.blur_movie(movie, sigma)).max() < BLUR32_TOL
 
 
 @pytest.mark.parametrize('shape,sigma', [((150, 300), 5.0), ((70, 131), 9.0), ((96, 260), 17.0), ((1024, 1024), 2.5)])
@@ -77,7 +84,7 @@ def test_blur_tiles_and_wide_kernels(cuda_device, shape, sigma):
     got = engine.blur(dev_t(movie, cuda_device), sigma).cpu().numpy()
     assert np.abs(got - want).max() < 1e-10
     got32 = engine.blur(dev_t(movie, cuda_device).float(), sigma).cpu().numpy()
-    assert np.abs(got32 - want).max() < 2e-3
+    assert np.abs(got32 - want).max() < BLUR32_TOL
 
 
 def test_multigrid_hierarchy_matches_model(cuda_device):
