@@ -250,6 +250,9 @@ typedef struct ofb_nd_level {
     const int* parent_slot;     /* [n_nodes][n_border]  position of each border pixel in the parent's front */
 } ofb_nd_level;
 size_t ofb_direct_workspace_bytes(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny);
+/* 1: the process's last direct solve replayed the CUDA graph captured for its frame shape, -1: a library call refused to be captured
+ * and the solve was issued launch by launch, 0: no direct solve yet (diagnostics) */
+int ofb_direct_graph_state(void);
 int ofb_direct_solve(const void* P, const void* b3, void* x3, const double* alpha, const double* beta,
                      const ofb_nd_level* levels, int n_levels, void* workspace, size_t workspace_bytes,
                      double rtol, double* relres_out, int* converged_out, int B, int Nx, int Ny, int dtype, void* stream);

@@ -31,7 +31,7 @@ EXPORTED_SYMBOLS = ('ofb_version', 'ofb_last_error', 'ofb_default_options', 'ofb
                     'ofb_epilogue', 'ofb_slab_partition', 'ofb_slab_local_rows', 'ofb_comm_unique_id', 'ofb_comm_create',
                     'ofb_comm_destroy', 'ofb_comm_peer_halo', 'ofb_slab_workspace_bytes', 'ofb_solve_slab', 'ofb_epilogue_slab',
                     'ofb_liu_shen', 'ofb_movie_max', 'ofb_adaptive_threshold', 'ofb_clahe_workspace_bytes', 'ofb_clahe',
-                    'ofb_subtract_background', 'ofb_widen', 'ofb_blur_noalloc', 'ofb_direct_workspace_bytes', 'ofb_direct_solve')
+                    'ofb_subtract_background', 'ofb_widen', 'ofb_blur_noalloc', 'ofb_direct_workspace_bytes', 'ofb_direct_solve', 'ofb_direct_graph_state')
 BLUR_NOALLOC_MAX_BYTES = 16 << 20
 
 
@@ -142,6 +142,8 @@ def load():
     lib.ofb_subtract_background.argtypes = [vp, vp, vp, d, ll, i, vp]
     lib.ofb_direct_workspace_bytes.restype = sz
     lib.ofb_direct_workspace_bytes.argtypes = [ctypes.POINTER(NdLevel), i, i, i, i]
+    lib.ofb_direct_graph_state.restype = i
+    lib.ofb_direct_graph_state.argtypes = []
     lib.ofb_direct_solve.restype = i
     lib.ofb_direct_solve.argtypes = [vp, vp, vp, dp, dp, ctypes.POINTER(NdLevel), i, vp, sz, d, dp, ip, i, i, i, i, vp]
     lib.ofb_blur_noalloc.restype = i

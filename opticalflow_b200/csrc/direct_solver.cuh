@@ -99,6 +99,12 @@ __global__ void __launch_bounds__(128) k_nd_extend_add(NdLevel C, NdLevel Pn, in
     if (s != 0.0) Pn.F[(long long)(child >> 1) * nfp * nfp + (long long)(3 * sb + b % 3) * nfp + (3 * sa + a % 3)] += s;
 }
 
+// getrf's verdicts of a level -> one flag (1 + level of the first front with a zero pivot), read by the host once per pair
+__global__ void k_nd_check_info(const int* __restrict__ info, int n, int level, int* __restrict__ flag) {
+    const int k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k < n && info[k] != 0) atomicMax(flag, level + 1);
+}
+
 // pointer arrays of the batched cuBLAS calls: F11 (= front base), F12 block, and the per-node vectors
 __global__ void k_nd_pointers(NdLevel L, double* z, double** Fptr, double** F12ptr, double** zptr) {
     const int node = blockIdx.x * blockDim.x + threadIdx.x;

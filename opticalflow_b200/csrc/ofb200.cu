@@ -1678,6 +1678,8 @@ struct DenseHandles {
     cusolverDnHandle_t side_solver[ND_STREAMS] = {};       // one per side stream
     cudaStream_t side[ND_STREAMS] = {};
     cudaEvent_t fork = nullptr, join[ND_STREAMS] = {};
+    cudaStream_t graph_stream = nullptr;                   // the captured graph of a frame shape runs here (the caller's stream may be the
+    cudaEvent_t caller_ready = nullptr;                    // legacy default stream, which cannot be captured)
     std::mutex busy;                                       // the side streams and events serve one direct solve per device at a time
 };
 int dense_handles(DenseHandles** out) {
@@ -1691,6 +1693,8 @@ int dense_handles(DenseHandles** out) {
     if (h.blas == nullptr) OFB_CHECK_CUBLAS(cublasCreate(&h.blas));
     if (h.solver == nullptr) OFB_CHECK_CUSOLVER(cusolverDnCreate(&h.solver));
     if (h.fork == nullptr) {
+        OFB_CHECK_CUDA(cudaStreamCreateWithFlags(&h.graph_stream, cudaStreamNonBlocking));
+        OFB_CHECK_CUDA(cudaEventCreateWithFlags(&h.caller_ready, cudaEventDisableTiming));
         OFB_CHECK_CUDA(cudaEventCreateWithFlags(&h.fork, cudaEventDisableTiming));
         for (int k = 0; k < ND_STREAMS; ++k) {
             OFB_CHECK_CUDA(cudaStreamCreateWithFlags(&h.side[k], cudaStreamNonBlocking));
@@ -1723,12 +1727,16 @@ struct NdWorkspace {
     PairState* st;
     int* active;            // per-pair flags k_state_init wants (unused here)
     int* scratch_info;      // devInfo of the triangular solves (getrf's verdict stays in NdLevel::info)
+    int* flag;              // 0, or 1 + the level of a front whose LU hit a zero pivot
+    void *img_stage, *b_stage, *x_stage;    // fixed slots the captured graph of a frame shape works on
+    double* ab_stage;       // the pair's alpha, beta
     int getrf_lwork;
     size_t bytes;
 };
 
 // `levels` describe the plan (device index arrays); carve the fronts and the scratch vectors out of `base`.
-int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, void* base, NdWorkspace* W, cusolverDnHandle_t solver) {
+int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, void* base, NdWorkspace* W, cusolverDnHandle_t solver,
+             size_t elem = 8) {
     if (n_levels < 1 || n_levels > 64) return fail(-50, "direct solve: bad number of levels %d", n_levels);
     size_t off = 0;
     auto take = [&](size_t nbytes) { void* p = base ? (char*)base + off : nullptr; off = align_up(off + nbytes, 256); return p; };
@@ -1761,12 +1769,136 @@ int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, vo
     W->zptr = (double**)take(max_nodes * sizeof(double*));
     W->getrf_lwork = lwork;
     W->getrf_work = (double*)take((size_t)std::max(lwork, 1) * ND_STREAMS * sizeof(double));       // one slice per side stream
+    W->scratch_info = (int*)take(sizeof(int) * ND_STREAMS);
+    W->flag = (int*)take(sizeof(int));
+    W->img_stage = take((size_t)Nx * Ny * elem);
+    W->b_stage = take((size_t)3 * Nx * Ny * elem);
+    W->x_stage = take((size_t)3 * Nx * Ny * elem);
+    W->ab_stage = (double*)take(2 * sizeof(double));
+    // everything above is independent of B (a captured graph holds those addresses); the per-pair arrays come last
     W->st = (PairState*)take(sizeof(PairState) * (size_t)B);
     W->active = (int*)take(sizeof(int) * (size_t)B);
-    W->scratch_info = (int*)take(sizeof(int) * ND_STREAMS);
     W->bytes = off;
     return 0;
 }
+
+// Everything one pair takes, queued on `stream` (and the side streams): numeric factorisation leaves to root, the two triangular
+// sweeps, the solution into x with its ghost ring.  No host synchronisation inside: it is what the CUDA graph of a frame shape captures.
+template <typename T>
+int nd_enqueue_pair(DenseHandles* H, NdWorkspace& W, int n_levels, const Geom& g, int Nx, int Ny, const T* img, const T* b, T* x,
+                    const double* alpha, const double* beta, int pair, cudaStream_t stream) {
+    const long long M = (long long)(Nx - 2) * (Ny - 2);
+    const double one = 1.0, minus_one = -1.0;
+    OFB_CHECK_CUDA(cudaMemsetAsync(W.flag, 0, sizeof(int), stream));
+    // ---- numeric factorisation, leaves to root
+    for (int l = n_levels - 1; l >= 0; --l) {
+        const NdLevel& L = W.lv[l];
+        const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
+        const long long stride = (long long)nf * nf;
+        OFB_CHECK_CUDA(cudaMemsetAsync(L.F, 0, sizeof(double) * stride * L.n_nodes, stream));
+        k_nd_assemble<T><<<dim3(L.n_nodes, no3, (nf + 127) / 128), 128, 0, stream>>>(L, g, img, alpha, beta, pair);
+        OFB_CHECK_LAUNCH();
+        if (l + 1 < n_levels) {
+            const NdLevel& C = W.lv[l + 1];
+            for (int parity = 0; parity < 2; ++parity) {
+                k_nd_extend_add<<<dim3(C.n_nodes / 2, C.nb3(), (C.nb3() + 127) / 128), 128, 0, stream>>>(C, L, parity);
+                OFB_CHECK_LAUNCH();
+            }
+        }
+        if (no3 <= ND_BATCHED_MAX) {
+            k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
+            OFB_CHECK_LAUNCH();
+            OFB_CHECK_CUBLAS(cublasDgetrfBatched(H->blas, no3, W.Fptr, nf, L.piv, L.info, L.n_nodes));
+            int info = 0;
+            OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, nb3, (const double* const*)W.Fptr, nf, L.piv, W.F12ptr, nf,
+                                                 &info, L.n_nodes));
+            if (info != 0) return fail(-51, "direct solve: cublasDgetrsBatched argument %d invalid", -info);
+        } else {
+            // the few hundred mid-size fronts: one getrf + getrs per node, the nodes of the level dealt over side streams
+            const int used = std::min(ND_STREAMS, L.n_nodes);
+            if (int rc = nd_fork(H, stream, used)) return rc;
+            for (int n = 0; n < L.n_nodes; ++n) {
+                double* F = L.F + stride * n;
+                const int k = n % used;
+                OFB_CHECK_CUSOLVER(cusolverDnDgetrf(H->side_solver[k], no3, no3, F, nf, W.getrf_work + (size_t)k * W.getrf_lwork,
+                                                    L.piv + (long long)n * no3, L.info + n));
+                OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->side_solver[k], CUBLAS_OP_N, no3, nb3, F, nf, L.piv + (long long)n * no3,
+                                                    F + (long long)no3 * nf, nf, W.scratch_info + k));
+            }
+            if (int rc = nd_join(H, stream, used)) return rc;
+        }
+        k_nd_check_info<<<(L.n_nodes + 255) / 256, 256, 0, stream>>>(L.info, L.n_nodes, l, W.flag);        // a zero pivot: remember where
+        OFB_CHECK_LAUNCH();
+        // S = F22 - F21 X, in place in the F22 block of every front of the level
+        OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, nb3, no3, &minus_one, L.F + no3, nf, stride,
+                                                   L.F + (long long)no3 * nf, nf, stride, &one, L.F + (long long)no3 * nf + no3, nf,
+                                                   stride, L.n_nodes));
+    }
+    // ---- forward sweep, leaves to root: z = F11^-1 w[own]; w[own] = z; w[border] -= F21 z
+    k_nd_load_rhs<T><<<dim3((Ny - 2 + 127) / 128, Nx - 2, 3), 128, 0, stream>>>(g, b, W.w);
+    OFB_CHECK_LAUNCH();
+    for (int l = n_levels - 1; l >= 0; --l) {
+        const NdLevel& L = W.lv[l];
+        const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
+        const long long stride = (long long)nf * nf;
+        k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
+        OFB_CHECK_LAUNCH();
+        if (no3 <= ND_BATCHED_MAX) {
+            k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
+            OFB_CHECK_LAUNCH();
+            int info = 0;
+            OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, 1, (const double* const*)W.Fptr, nf, L.piv, W.zptr, no3, &info,
+                                                 L.n_nodes));
+        } else {
+            const int used = std::min(ND_STREAMS, L.n_nodes);
+            if (int rc = nd_fork(H, stream, used)) return rc;
+            for (int n = 0; n < L.n_nodes; ++n)
+                OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->side_solver[n % used], CUBLAS_OP_N, no3, 1, L.F + stride * n, nf,
+                                                    L.piv + (long long)n * no3, W.z + (long long)n * no3, no3, W.scratch_info + n % used));
+            if (int rc = nd_join(H, stream, used)) return rc;
+        }
+        k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
+        OFB_CHECK_LAUNCH();
+        const double zero = 0.0;
+        OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, 1, no3, &one, L.F + no3, nf, stride, W.z, no3, no3,
+                                                   &zero, W.u, nb3, nb3, L.n_nodes));
+        k_nd_scatter_border<<<dim3(L.n_nodes, (nb3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.u);
+        OFB_CHECK_LAUNCH();
+    }
+    // ---- backward sweep, root to leaves: x[own] = z - X x[border]
+    for (int l = 0; l < n_levels; ++l) {
+        const NdLevel& L = W.lv[l];
+        const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
+        const long long stride = (long long)nf * nf;
+        k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
+        OFB_CHECK_LAUNCH();
+        k_nd_gather<<<dim3(L.n_nodes, (nb3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.u, 1);
+        OFB_CHECK_LAUNCH();
+        OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, no3, 1, nb3, &minus_one, L.F + (long long)no3 * nf, nf,
+                                                   stride, W.u, nb3, nb3, &one, W.z, no3, no3, L.n_nodes));
+        k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
+        OFB_CHECK_LAUNCH();
+    }
+    k_nd_store_solution<T><<<dim3((Ny + 127) / 128, Nx, 3), 128, 0, stream>>>(g, W.w, x);
+    OFB_CHECK_LAUNCH();
+    const int ring = 2 * Nx + 2 * Ny;
+    k_fill_ghosts<T><<<dim3((ring + 127) / 128, 1), 128, 0, stream>>>(g, x);
+    OFB_CHECK_LAUNCH();
+    return 0;
+}
+
+// One graph per device: the launch sequence of a pair depends on the frame shape (the plan), the workspace and the element type only, so
+// it is captured once over staging slots in the workspace and replayed per pair - a solve is ~16 400 launches, most of them from inside
+// cuSOLVER / cuBLAS calls, and the host could not issue them faster than 13 us each (profiles/r02_direct_solve_launches.txt).
+struct NdGraph {
+    cudaGraphExec_t exec = nullptr;
+    void* workspace = nullptr;
+    const void* plan = nullptr;
+    int Nx = 0, Ny = 0, n_levels = 0, elem = 0;
+    bool unsupported = false;            // a library call refused to be captured: stay on the eager path
+};
+
+std::atomic<int> g_direct_graph_state{0};       // 0: no direct solve yet, 1: the last one replayed a captured graph, -1: capture refused, eager
 
 template <typename T>
 int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, const double* beta, const ofb_nd_level* levels,
@@ -1778,118 +1910,79 @@ int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, c
     OFB_CHECK_CUBLAS(cublasSetStream(H->blas, stream));
     OFB_CHECK_CUSOLVER(cusolverDnSetStream(H->solver, stream));
     NdWorkspace W;
-    if (int rc = nd_carve(levels, n_levels, B, Nx, Ny, workspace, &W, H->solver)) return rc;
+    if (int rc = nd_carve(levels, n_levels, B, Nx, Ny, workspace, &W, H->solver, sizeof(T))) return rc;
     if (workspace == nullptr || workspace_bytes < W.bytes)
         return fail(-4, "direct solve: workspace too small: need %zu bytes, got %zu", W.bytes, workspace_bytes);
     LevelPlan lp{Nx, Ny, Ny, (long long)Nx * Ny, 2, 2, 0.0, 0.0};
     const Geom g = make_geom<T>(lp, false);
-    const long long M = (long long)(Nx - 2) * (Ny - 2);
-    const double one = 1.0, minus_one = -1.0;
-    std::vector<int> infos;
+    static NdGraph graphs[MAX_DEVICES];
+    int dev = 0;
+    OFB_CHECK_CUDA(cudaGetDevice(&dev));
+    NdGraph& G = graphs[std::min(std::max(dev, 0), MAX_DEVICES - 1)];
+    // OFB_DIRECT_GRAPH=1: replay a captured graph per pair instead of issuing the ~16 400 launches.  Measured: 0.21 s per 1024^2 pair
+    // either way - the solve is bound by the chains of dependent LU panel kernels of the large fronts on the device, not by the host -
+    // so it only frees the host thread; off by default.
+    const char* graph_env = getenv("OFB_DIRECT_GRAPH");
+    const bool want_graph = !G.unsupported && graph_env != nullptr && graph_env[0] == '1';
+    T* img_stage = (T*)W.img_stage;
+    T* b_stage = (T*)W.b_stage;
+    T* x_stage = (T*)W.x_stage;
     for (int pair = 0; pair < B; ++pair) {
         const T* img = (const T*)P_ + (long long)pair * g.img_pair;
         const T* b = (const T*)b3 + (long long)pair * g.pair;
         T* x = (T*)x3 + (long long)pair * g.pair;
-        // ---- numeric factorisation, leaves to root
-        for (int l = n_levels - 1; l >= 0; --l) {
-            const NdLevel& L = W.lv[l];
-            const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
-            const long long stride = (long long)nf * nf;
-            OFB_CHECK_CUDA(cudaMemsetAsync(L.F, 0, sizeof(double) * stride * L.n_nodes, stream));
-            k_nd_assemble<T><<<dim3(L.n_nodes, no3, (nf + 127) / 128), 128, 0, stream>>>(L, g, img, alpha, beta, pair);
-            OFB_CHECK_LAUNCH();
-            if (l + 1 < n_levels) {
-                const NdLevel& C = W.lv[l + 1];
-                for (int parity = 0; parity < 2; ++parity) {
-                    k_nd_extend_add<<<dim3(C.n_nodes / 2, C.nb3(), (C.nb3() + 127) / 128), 128, 0, stream>>>(C, L, parity);
-                    OFB_CHECK_LAUNCH();
+        bool done = false;
+        cudaStream_t flag_stream = stream;
+        if (want_graph && !G.unsupported) {
+            cudaStream_t gs = H->graph_stream;
+            const bool cached = G.exec != nullptr && G.workspace == workspace && G.plan == (const void*)levels[0].own && G.Nx == Nx && G.Ny == Ny &&
+                                G.n_levels == n_levels && G.elem == (int)sizeof(T);
+            if (!cached) {
+                if (G.exec != nullptr) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
+                cudaGraph_t graph = nullptr;
+                OFB_CHECK_CUDA(cudaStreamSynchronize(gs));
+                OFB_CHECK_CUBLAS(cublasSetStream(H->blas, gs));
+                OFB_CHECK_CUSOLVER(cusolverDnSetStream(H->solver, gs));
+                int rc = 0;
+                cudaError_t ce = cudaStreamBeginCapture(gs, cudaStreamCaptureModeThreadLocal);
+                if (ce == cudaSuccess) {
+                    rc = nd_enqueue_pair<T>(H, W, n_levels, g, Nx, Ny, img_stage, b_stage, x_stage, W.ab_stage, W.ab_stage + 1, 0, gs);
+                    ce = cudaStreamEndCapture(gs, &graph);
                 }
-            }
-            if (no3 <= ND_BATCHED_MAX) {
-                k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
-                OFB_CHECK_LAUNCH();
-                OFB_CHECK_CUBLAS(cublasDgetrfBatched(H->blas, no3, W.Fptr, nf, L.piv, L.info, L.n_nodes));
-                int info = 0;
-                OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, nb3, (const double* const*)W.Fptr, nf, L.piv, W.F12ptr, nf,
-                                                     &info, L.n_nodes));
-                if (info != 0) return fail(-51, "direct solve: cublasDgetrsBatched argument %d invalid", -info);
-            } else {
-                // the few hundred mid-size fronts: one getrf + getrs per node, the nodes of the level dealt over side streams
-                const int used = std::min(ND_STREAMS, L.n_nodes);
-                if (int rc = nd_fork(H, stream, used)) return rc;
-                for (int n = 0; n < L.n_nodes; ++n) {
-                    double* F = L.F + stride * n;
-                    const int k = n % used;
-                    OFB_CHECK_CUSOLVER(cusolverDnDgetrf(H->side_solver[k], no3, no3, F, nf, W.getrf_work + (size_t)k * W.getrf_lwork,
-                                                        L.piv + (long long)n * no3, L.info + n));
-                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->side_solver[k], CUBLAS_OP_N, no3, nb3, F, nf, L.piv + (long long)n * no3,
-                                                        F + (long long)no3 * nf, nf, W.scratch_info + k));
+                if (rc != 0 || ce != cudaSuccess || graph == nullptr || cudaGraphInstantiate(&G.exec, graph, 0) != cudaSuccess) {
+                    cudaGetLastError();
+                    G.exec = nullptr;
+                    G.unsupported = true;           // a call refused to be captured: eager from now on
+                } else {
+                    G.workspace = workspace; G.plan = (const void*)levels[0].own; G.Nx = Nx; G.Ny = Ny; G.n_levels = n_levels; G.elem = (int)sizeof(T);
                 }
-                if (int rc = nd_join(H, stream, used)) return rc;
+                if (graph != nullptr) cudaGraphDestroy(graph);
+                OFB_CHECK_CUBLAS(cublasSetStream(H->blas, stream));
+                OFB_CHECK_CUSOLVER(cusolverDnSetStream(H->solver, stream));
             }
-            // S = F22 - F21 X, in place in the F22 block of every front of the level
-            OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, nb3, no3, &minus_one, L.F + no3, nf, stride,
-                                                       L.F + (long long)no3 * nf, nf, stride, &one, L.F + (long long)no3 * nf + no3, nf,
-                                                       stride, L.n_nodes));
+            if (G.exec != nullptr) {
+                OFB_CHECK_CUDA(cudaEventRecord(H->caller_ready, stream));           // inputs queued on the caller's stream are ready
+                OFB_CHECK_CUDA(cudaStreamWaitEvent(gs, H->caller_ready, 0));
+                OFB_CHECK_CUDA(cudaMemcpyAsync(img_stage, img, sizeof(T) * g.plane, cudaMemcpyDeviceToDevice, gs));
+                OFB_CHECK_CUDA(cudaMemcpyAsync(b_stage, b, sizeof(T) * g.pair, cudaMemcpyDeviceToDevice, gs));
+                OFB_CHECK_CUDA(cudaMemcpyAsync(W.ab_stage, alpha + pair, sizeof(double), cudaMemcpyDeviceToDevice, gs));
+                OFB_CHECK_CUDA(cudaMemcpyAsync(W.ab_stage + 1, beta + pair, sizeof(double), cudaMemcpyDeviceToDevice, gs));
+                OFB_CHECK_CUDA(cudaGraphLaunch(G.exec, gs));
+                g_launches.fetch_add(1);
+                OFB_CHECK_CUDA(cudaMemcpyAsync(x, x_stage, sizeof(T) * g.pair, cudaMemcpyDeviceToDevice, gs));
+                flag_stream = gs;                   // the host waits for this stream below: what the caller queues next comes after it
+                done = true;
+            }
+        }
+        g_direct_graph_state.store(done ? 1 : (G.unsupported ? -1 : 0));
+        if (!done) {
+            if (int rc = nd_enqueue_pair<T>(H, W, n_levels, g, Nx, Ny, img, b, x, alpha, beta, pair, stream)) return rc;
         }
         // a zero pivot anywhere makes the factorisation useless: report it instead of returning garbage
-        for (int l = 0; l < n_levels; ++l) {
-            infos.resize(W.lv[l].n_nodes);
-            OFB_CHECK_CUDA(cudaMemcpyAsync(infos.data(), W.lv[l].info, sizeof(int) * W.lv[l].n_nodes, cudaMemcpyDeviceToHost, stream));
-            OFB_CHECK_CUDA(cudaStreamSynchronize(stream));
-            for (int n = 0; n < W.lv[l].n_nodes; ++n)
-                if (infos[n] != 0) return fail(-52, "direct solve: singular front (pair %d, level %d, node %d, pivot %d)", pair, l, n, infos[n]);
-        }
-        // ---- forward sweep, leaves to root: z = F11^-1 w[own]; w[own] = z; w[border] -= F21 z
-        k_nd_load_rhs<T><<<dim3((Ny - 2 + 127) / 128, Nx - 2, 3), 128, 0, stream>>>(g, b, W.w);
-        OFB_CHECK_LAUNCH();
-        for (int l = n_levels - 1; l >= 0; --l) {
-            const NdLevel& L = W.lv[l];
-            const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
-            const long long stride = (long long)nf * nf;
-            k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
-            OFB_CHECK_LAUNCH();
-            if (no3 <= ND_BATCHED_MAX) {
-                k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
-                OFB_CHECK_LAUNCH();
-                int info = 0;
-                OFB_CHECK_CUBLAS(cublasDgetrsBatched(H->blas, CUBLAS_OP_N, no3, 1, (const double* const*)W.Fptr, nf, L.piv, W.zptr, no3, &info,
-                                                     L.n_nodes));
-            } else {
-                const int used = std::min(ND_STREAMS, L.n_nodes);
-                if (int rc = nd_fork(H, stream, used)) return rc;
-                for (int n = 0; n < L.n_nodes; ++n)
-                    OFB_CHECK_CUSOLVER(cusolverDnDgetrs(H->side_solver[n % used], CUBLAS_OP_N, no3, 1, L.F + stride * n, nf,
-                                                        L.piv + (long long)n * no3, W.z + (long long)n * no3, no3, W.scratch_info + n % used));
-                if (int rc = nd_join(H, stream, used)) return rc;
-            }
-            k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
-            OFB_CHECK_LAUNCH();
-            const double zero = 0.0;
-            OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, nb3, 1, no3, &one, L.F + no3, nf, stride, W.z, no3, no3,
-                                                       &zero, W.u, nb3, nb3, L.n_nodes));
-            k_nd_scatter_border<<<dim3(L.n_nodes, (nb3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.u);
-            OFB_CHECK_LAUNCH();
-        }
-        // ---- backward sweep, root to leaves: x[own] = z - X x[border]
-        for (int l = 0; l < n_levels; ++l) {
-            const NdLevel& L = W.lv[l];
-            const int nf = L.nf(), no3 = L.no3(), nb3 = L.nb3();
-            const long long stride = (long long)nf * nf;
-            k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
-            OFB_CHECK_LAUNCH();
-            k_nd_gather<<<dim3(L.n_nodes, (nb3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.u, 1);
-            OFB_CHECK_LAUNCH();
-            OFB_CHECK_CUBLAS(cublasDgemmStridedBatched(H->blas, CUBLAS_OP_N, CUBLAS_OP_N, no3, 1, nb3, &minus_one, L.F + (long long)no3 * nf, nf,
-                                                       stride, W.u, nb3, nb3, &one, W.z, no3, no3, L.n_nodes));
-            k_nd_store_own<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z);
-            OFB_CHECK_LAUNCH();
-        }
-        k_nd_store_solution<T><<<dim3((Ny + 127) / 128, Nx, 3), 128, 0, stream>>>(g, W.w, x);
-        OFB_CHECK_LAUNCH();
-        const int ring = 2 * Nx + 2 * Ny;
-        k_fill_ghosts<T><<<dim3((ring + 127) / 128, 1), 128, 0, stream>>>(g, x);
-        OFB_CHECK_LAUNCH();
+        int flag = 0;
+        OFB_CHECK_CUDA(cudaMemcpyAsync(&flag, W.flag, sizeof(int), cudaMemcpyDeviceToHost, flag_stream));
+        OFB_CHECK_CUDA(cudaStreamSynchronize(flag_stream));
+        if (flag != 0) return fail(-52, "direct solve: singular front (pair %d, level %d)", pair, flag - 1);
     }
     // the reference's independent residual (:1150-1151) of what is returned, in fp64
     const long long nvec = g.pair;
@@ -1913,6 +2006,8 @@ int direct_impl(const void* P_, const void* b3, void* x3, const double* alpha, c
 }  // namespace
 
 extern "C" {
+
+int ofb_direct_graph_state(void) { return g_direct_graph_state.load(); }
 
 size_t ofb_direct_workspace_bytes(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny) {
     if (levels == nullptr || B < 1 || Nx < 5 || Ny < 5) return 0;

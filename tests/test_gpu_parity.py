@@ -139,6 +139,25 @@ def test_direct_solve_matches_superlu(cuda_device, shape, alpha):
         assert rel(x32[k].cpu().double().numpy(), want[k]) < 1e-3
 
 
+def test_direct_solve_graph_replay_matches_eager(cuda_device, monkeypatch):
+    """OFB_DIRECT_GRAPH=1: the launch sequence of a frame shape captured once over staging slots and replayed per pair - the same
+    answers as the launch-by-launch path, also when the batch size and the weights change between calls on one workspace."""
+    from opticalflow_b200 import _lib
+    movie = fo.blur_movie(synthetic.rotating_shearing_movie(40, 56, 4, seed=2), 2.5)
+    Pd, Cd = dev_t(movie[:-1], cuda_device), dev_t(movie[1:], cuda_device)
+    b = engine.build_rhs(Pd, Cd)
+    ws = engine.Workspace()
+    monkeypatch.delenv('OFB_DIRECT_GRAPH', raising=False)
+    eager = [engine.direct_solve(Pd, b, a, 1e4, ws)[0].clone() for a in (1e5, 1e3)]
+    monkeypatch.setenv('OFB_DIRECT_GRAPH', '1')
+    for k, a in enumerate((1e5, 1e3)):
+        x, rr, cv = engine.direct_solve(Pd, b, a, 1e4, ws)                        # three pairs
+        assert _lib.load().ofb_direct_graph_state() == 1 and cv.tolist() == [1, 1, 1]
+        assert float((x - eager[k]).abs().max()) <= 1e-9 * float(eager[k].abs().max())
+        x1, _, _ = engine.direct_solve(Pd[1:2].contiguous(), b[1:2].contiguous(), a, 1e4, ws)      # one pair, same workspace, same graph
+        assert float((x1[0] - eager[k][1]).abs().max()) <= 1e-9 * float(eager[k].abs().max())
+
+
 def test_solve_initial_guess_and_batch_weights(cuda_device):
     """Per-pair weights in one batch; nonzero initial guess; converged pairs stop iterating."""
     movie = fo.blur_movie(synthetic.translating_movie(48, 48, 3, seed=8), 2.5)

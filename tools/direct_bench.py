@@ -23,7 +23,8 @@ for N in sizes:
             torch.cuda.synchronize()
             dt = (time.perf_counter() - t0) / P.shape[0]
             line = dict(frame=N, dtype=str(dtype).replace('torch.', ''), alpha=alpha, seconds_per_pair=round(dt, 4), relres=[float('%.3g' % v) for v in rr.tolist()],
-                        workspace_gb=round(ws.buffer.numel() / 1e9, 2), plan_seconds=round(plan_s, 2))
+                        workspace_gb=round(ws.buffer.numel() / 1e9, 2), plan_seconds=round(plan_s, 2),
+                        graph=int(__import__('opticalflow_b200._lib', fromlist=['x']).load().ofb_direct_graph_state()))
             if alpha == 1e5:                                               # where the Krylov path works: the two must agree
                 xk = torch.zeros_like(b)
                 it, rk, cv = engine.solve(P, b, xk, alpha, 1e4, rtol=1e-10 if dtype == torch.float64 else 1e-6, max_it=200)
