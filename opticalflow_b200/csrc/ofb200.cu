@@ -542,10 +542,36 @@ template <typename T> struct Solver {
             return launch_stream<T, false, Op>(L, x, op, B, opt.rows_per_strip, true, stream, pdl());
         }
         const int warps_per_block = 4;
-        const int items = L.tiles_x * L.strips;
+        LevelArgs<T> Lr = L;
+        if (opt.rows_per_strip <= 0) {
+            // One wave: a small level is latency bound, and a grid that exceeds the resident blocks by a few per cent runs a second,
+            // nearly empty wave (130^2 x 64 pairs: 640 blocks on 592 slots).  Lengthen the strips until the launch fits.
+            static std::atomic<int> blocks_per_sm[MAX_DEVICES][2];
+            int dev = 0;
+            cudaGetDevice(&dev);
+            dev = std::min(std::max(dev, 0), MAX_DEVICES - 1);
+            int nb = blocks_per_sm[dev][l == 0 ? 0 : 1].load();
+            if (nb == 0) {
+                cudaError_t e = (l == 0) ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_sweep<T, true, Op>, warps_per_block * 32, 0)
+                                         : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, k_sweep<T, false, Op>, warps_per_block * 32, 0);
+                if (e != cudaSuccess || nb < 1) { cudaGetLastError(); nb = 4; }
+                blocks_per_sm[dev][l == 0 ? 0 : 1].store(nb);
+            }
+            const long long slots = (long long)device_sms() * nb;
+            auto blocks_for = [&](int R) {
+                const long long strips = (g[l].Nx + R - 1) / R;
+                return ((long long)Lr.tiles_x * strips + warps_per_block - 1) / warps_per_block * B;
+            };
+            int R = Lr.rows_per_strip;
+            if (blocks_for(R) > slots && blocks_for(R) <= 2 * slots)
+                while (R < 64 && blocks_for(R) > slots) ++R;
+            Lr.rows_per_strip = R;
+            Lr.strips = (g[l].Nx + R - 1) / R;
+        }
+        const int items = Lr.tiles_x * Lr.strips;
         dim3 grid((items + warps_per_block - 1) / warps_per_block, B);
-        if (l == 0) OFB_LAUNCH(pdl(), (k_sweep<T, true, Op>), grid, dim3(warps_per_block * 32), 0, stream, L, x, op);
-        else        OFB_LAUNCH(pdl(), (k_sweep<T, false, Op>), grid, dim3(warps_per_block * 32), 0, stream, L, x, op);
+        if (l == 0) OFB_LAUNCH(pdl(), (k_sweep<T, true, Op>), grid, dim3(warps_per_block * 32), 0, stream, Lr, x, op);
+        else        OFB_LAUNCH(pdl(), (k_sweep<T, false, Op>), grid, dim3(warps_per_block * 32), 0, stream, Lr, x, op);
         return 0;
     }
 
