@@ -1695,7 +1695,15 @@ namespace {
         if (s__ != CUSOLVER_STATUS_SUCCESS) return fail(-4000 - (int)s__, "%s: cuSOLVER status %d", #expr, (int)s__); \
     } while (0)
 
-constexpr int ND_BATCHED_MAX = 128;       // owned variables per node up to which the batched cuBLAS LU is used
+// Which levels take the batched cuBLAS LU instead of one cuSOLVER getrf per node: fronts of up to 128 owned variables, and up to 192 where
+// the level has at least 128 of them.  Measured (tools/direct_threshold.py; the fronts in question have 189 unknowns): a 1024^2 pair - levels
+// of 128 and 256 such nodes - 0.224 -> 0.205 s with them batched; a 512^2 pair - 32 and 64 nodes - 0.055 -> 0.066 s, so those stay with
+// cuSOLVER; batching the 381-unknown fronts as well: 0.229 s, the 765s: 0.390 s.  OFB_ND_BATCHED_MAX = n makes it "up to n" for A/B runs.
+bool nd_use_batched(int no3, int n_nodes) {
+    static const int forced = [] { const char* e = getenv("OFB_ND_BATCHED_MAX"); return e ? atoi(e) : 0; }();
+    if (forced > 0) return no3 <= forced;
+    return no3 <= 128 || (no3 <= 192 && n_nodes >= 128);
+}
 
 constexpr int ND_STREAMS = 8;             // side streams for the per-node LU of the mid-size fronts (one getrf cannot fill the GPU)
 struct DenseHandles {
@@ -1780,7 +1788,7 @@ int nd_carve(const ofb_nd_level* levels, int n_levels, int B, int Nx, int Ny, vo
         max_nodes = std::max(max_nodes, (size_t)L.n_nodes);
         max_z = std::max(max_z, (size_t)L.n_nodes * L.no3());
         max_u = std::max(max_u, (size_t)L.n_nodes * L.nb3());
-        if (L.no3() > ND_BATCHED_MAX && solver != nullptr) {
+        if (!nd_use_batched(L.no3(), L.n_nodes) && solver != nullptr) {
             int lw = 0;
             OFB_CHECK_CUSOLVER(cusolverDnDgetrf_bufferSize(solver, L.no3(), L.no3(), nullptr, (int)nf, &lw));
             lwork = std::max(lwork, lw);
@@ -1831,7 +1839,7 @@ int nd_enqueue_pair(DenseHandles* H, NdWorkspace& W, int n_levels, const Geom& g
                 OFB_CHECK_LAUNCH();
             }
         }
-        if (no3 <= ND_BATCHED_MAX) {
+        if (nd_use_batched(no3, L.n_nodes)) {
             k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
             OFB_CHECK_LAUNCH();
             OFB_CHECK_CUBLAS(cublasDgetrfBatched(H->blas, no3, W.Fptr, nf, L.piv, L.info, L.n_nodes));
@@ -1869,7 +1877,7 @@ int nd_enqueue_pair(DenseHandles* H, NdWorkspace& W, int n_levels, const Geom& g
         const long long stride = (long long)nf * nf;
         k_nd_gather<<<dim3(L.n_nodes, (no3 + 127) / 128), 128, 0, stream>>>(L, W.w, M, W.z, 0);
         OFB_CHECK_LAUNCH();
-        if (no3 <= ND_BATCHED_MAX) {
+        if (nd_use_batched(no3, L.n_nodes)) {
             k_nd_pointers<<<(L.n_nodes + 127) / 128, 128, 0, stream>>>(L, W.z, W.Fptr, W.F12ptr, W.zptr);
             OFB_CHECK_LAUNCH();
             int info = 0;
