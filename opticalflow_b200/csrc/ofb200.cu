@@ -630,8 +630,8 @@ template <typename T> struct Solver {
             if constexpr (sizeof(T) == 4) {
                 // bfloat16 copies of the planes for the streamed sweeps of this level (the next level is still restricted from fp32)
                 if (w.coef16[l] != nullptr && use_stream(l) && !slab.on && (opt.flags & OFB_FLAG_FP32_COEF) == 0) {
-                    dim3 pgrid((w.pitch16[l] + 127) / 128, g[l].Nx, B * NCOEF);
-                    k_pack_bf16<<<pgrid, 128, 0, stream>>>(g[l], (const float*)w.coef[l], w.coef16[l], w.pitch16[l],
+                    dim3 pgrid((unsigned)(((long long)g[l].Nx * (w.pitch16[l] / 8) + 255) / 256), 1, B * NCOEF);
+                    k_pack_bf16<<<pgrid, 256, 0, stream>>>(g[l], (const float*)w.coef[l], w.coef16[l], w.pitch16[l],
                                                           (long long)g[l].Nx * w.pitch16[l]);
                     OFB_CHECK_LAUNCH();
                 }

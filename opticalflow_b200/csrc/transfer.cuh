@@ -153,17 +153,31 @@ __global__ void __launch_bounds__(128) k_prolong_add4(Geom gc, const float* __re
     }
 }
 
-// float32 coefficient planes [B][7][Nx][pitch] -> bfloat16 copies [B][7][Nx][pitch16] (round to nearest even; columns beyond Ny: 0)
-__global__ void k_pack_bf16(Geom g, const float* __restrict__ coef, unsigned short* __restrict__ out, int pitch16, long long plane16) {
-    const int j = blockIdx.x * blockDim.x + threadIdx.x;
-    const int i = blockIdx.y;
+// float32 coefficient planes [B][7][Nx][pitch] -> bfloat16 copies [B][7][Nx][pitch16] (round to nearest even; columns beyond Ny: 0).
+// One thread per eight columns: two 16-byte loads, one 16-byte store (pitch % 4 == 0, pitch16 % 8 == 0, 16-byte aligned planes: the
+// conditions of the streamed sweeps that read the copies).  grid = (ceil(Nx * pitch16 / 8 / 256), 1, pairs * NCOEF).
+__global__ void __launch_bounds__(256) k_pack_bf16(Geom g, const float* __restrict__ coef, unsigned short* __restrict__ out, int pitch16,
+                                                   long long plane16) {
+    const int p8 = pitch16 >> 3;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = t / p8;
+    if (i >= g.Nx) return;
+    const int j = (t - i * p8) << 3;
     const int pq = blockIdx.z;                   // pair * NCOEF + plane
-    if (j >= pitch16) return;
-    float v = 0.0f;
-    if (j < g.Ny) v = coef[(long long)pq * g.plane + (long long)i * g.pitch + j];
-    unsigned u = __float_as_uint(v);
-    u += 0x7fffu + ((u >> 16) & 1u);             // round to nearest even on the upper 16 bits (no NaN/inf in coefficients)
-    out[(long long)pq * plane16 + (long long)i * pitch16 + j] = (unsigned short)(u >> 16);
+    const float* src = coef + (long long)pq * g.plane + (long long)i * g.pitch + j;
+    float v[8];
+    const float4 lo = j < g.pitch ? *reinterpret_cast<const float4*>(src) : make_float4(0.f, 0.f, 0.f, 0.f);
+    const float4 hi = j + 4 < g.pitch ? *reinterpret_cast<const float4*>(src + 4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
+    unsigned h[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        unsigned u = j + k < g.Ny ? __float_as_uint(v[k]) : 0u;
+        u += 0x7fffu + ((u >> 16) & 1u);         // round to nearest even on the upper 16 bits (no NaN/inf in coefficients)
+        h[k] = u >> 16;
+    }
+    const uint4 packed = make_uint4(h[0] | (h[1] << 16), h[2] | (h[3] << 16), h[4] | (h[5] << 16), h[6] | (h[7] << 16));
+    *reinterpret_cast<uint4*>(out + (long long)pq * plane16 + (long long)i * pitch16 + j) = packed;
 }
 
 // ------------------------------------------------------------------ coarsest level: dense inverse
