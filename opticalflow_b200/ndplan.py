@@ -45,12 +45,8 @@ def _ring(i0, i1, j0, j1, mx, my):
     return (I[outside] * my + J[outside]).astype(np.int64)
 
 
-@functools.lru_cache(maxsize=8)
-def build(Nx, Ny, max_depth=None):
-    """Plan for an Nx x Ny frame (ghost ring included).  Returns a list of ``Level`` from the root (index 0) to the leaves."""
-    mx, my = Nx - 2, Ny - 2
-    if mx < 1 or my < 1:
-        raise ValueError('frame too small')
+def _dissect(mx, my, max_depth):
+    """The rectangles of every tree depth and the separator lines that cut them (plain Python: ~2 x 10^5 tuples at 1024^2)."""
     rects = [[(0, mx, 0, my)]]
     seps = []
     while max_depth is None or len(seps) < max_depth:
@@ -69,6 +65,82 @@ def build(Nx, Ny, max_depth=None):
                 nxt += [(i0, i1, j0, m), (i0, i1, m + 1, j1)]
         seps.append(sep)
         rects.append(nxt)
+    return rects, seps
+
+
+def _pack_rows(node, values, n_nodes, floor=1):
+    """(node index, value) pairs in node-major order -> [n_nodes, max count] int32, -1 padded, order kept."""
+    counts = np.bincount(node, minlength=n_nodes)
+    width = max(floor, int(counts.max()) if counts.size else 0)
+    out = np.full((n_nodes, width), -1, np.int32)
+    start = np.cumsum(counts) - counts
+    out[node, np.arange(node.size) - start[node]] = values
+    return out
+
+
+@functools.lru_cache(maxsize=8)
+def build(Nx, Ny, max_depth=None):
+    """Plan for an Nx x Ny frame (ghost ring included).  Returns a list of ``Level`` from the root (index 0) to the leaves.
+    Array operations over all nodes of a level (1 s at 1024^2); ``build_loops`` is the node-by-node statement of the same plan."""
+    mx, my = Nx - 2, Ny - 2
+    if mx < 1 or my < 1:
+        raise ValueError('frame too small')
+    rects, seps = _dissect(mx, my, max_depth)
+    depth = len(seps)
+    M = mx * my
+    levels = []
+    for d in range(depth + 1):
+        R = np.asarray(rects[d], np.int64).reshape(-1, 4)
+        O = np.asarray(seps[d] if d < depth else rects[d], np.int64).reshape(-1, 4)        # leaves own their whole rectangle
+        n = R.shape[0]
+        # owned pixels, row-major over the owned rectangle (a separator is a line, a leaf a few pixels each way)
+        h, w = O[:, 1] - O[:, 0], O[:, 3] - O[:, 2]
+        di = np.arange(int(h.max()))[None, :, None]
+        dj = np.arange(int(w.max()))[None, None, :]
+        ok = (di < h[:, None, None]) & (dj < w[:, None, None])
+        pix = (O[:, 0][:, None, None] + di) * my + (O[:, 2][:, None, None] + dj)
+        node, a, b = np.nonzero(ok)
+        own = _pack_rows(node, pix[node, a, b], n)
+        # the ring around the rectangle in row-major order: the row above, (left, right) of every row, the row below; clipped to the grid
+        i0, i1, j0, j1 = R[:, 0][:, None], R[:, 1][:, None], R[:, 2][:, None], R[:, 3][:, None]
+        hh, ww = i1 - i0, j1 - j0
+        t1, t2 = ww + 2, ww + 2 + 2 * hh
+        k = np.arange(int((2 * (ww + 2) + 2 * hh).max()))[None, :]
+        top, mid, bot = k < t1, (k >= t1) & (k < t2), (k >= t2) & (k < t2 + ww + 2)
+        r, side = (k - t1) // 2, (k - t1) % 2
+        I = np.where(top, i0 - 1, np.where(mid, i0 + r, i1))
+        J = np.where(top, j0 - 1 + k, np.where(mid, np.where(side == 0, j0 - 1, j1), j0 - 1 + (k - t2)))
+        ok = (top | mid | bot) & (I >= 0) & (I < mx) & (J >= 0) & (J < my)
+        node, pos = np.nonzero(ok)
+        border = _pack_rows(node, (I * my + J)[node, pos], n)
+        lv = Level(n, own.shape[1], border.shape[1])
+        lv.own, lv.border = own, border
+        lv.parent_slot = np.full(border.shape, -1, np.int32)
+        lv.rect = R.astype(np.int32)
+        levels.append(lv)
+    # where a node's border pixels sit in its parent's front (own pixels first, then the parent's border; padding slots count)
+    for d in range(1, depth + 1):
+        lv, par = levels[d], levels[d - 1]
+        front = np.concatenate([par.own, par.border], axis=1).astype(np.int64)                 # [parents, front slots]
+        p_idx, slot = np.nonzero(front >= 0)
+        keys = p_idx * M + front[p_idx, slot]                                                  # (parent, pixel): unique
+        order = np.argsort(keys, kind='stable')
+        keys, slot = keys[order], slot[order]
+        c_idx, c_pos = np.nonzero(lv.border >= 0)
+        want = (c_idx // 2) * M + lv.border[c_idx, c_pos].astype(np.int64)
+        at = np.minimum(np.searchsorted(keys, want), keys.size - 1)
+        if not np.array_equal(keys[at], want):
+            raise AssertionError('border pixel of a node is not in its parent front')
+        lv.parent_slot[c_idx, c_pos] = slot[at]
+    return levels
+
+
+def build_loops(Nx, Ny, max_depth=None):
+    """The same plan node by node (the statement ``build`` is checked against in tests/test_ndplan_cpu.py; 10 s at 1024^2)."""
+    mx, my = Nx - 2, Ny - 2
+    if mx < 1 or my < 1:
+        raise ValueError('frame too small')
+    rects, seps = _dissect(mx, my, max_depth)
     depth = len(seps)
     levels = []
     for d in range(depth + 1):

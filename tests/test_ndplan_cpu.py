@@ -37,3 +37,15 @@ def test_plan_sizes_at_the_bench_shapes():
     assert 1.0e9 < ndplan.memory_bytes(levels) < 1.5e9
     small = ndplan.build(5, 5)
     assert len(small) == 1 and small[0].n_own == 9                                 # 3 x 3 interior: one dense front
+
+
+@pytest.mark.parametrize('shape', [(5, 5), (7, 6), (6, 200), (23, 31), (33, 130), (300, 44), (129, 257), (256, 256)])
+def test_array_builder_equals_the_node_by_node_statement(shape):
+    """``build`` works on all nodes of a level at once; ``build_loops`` states the same plan node by node: same arrays, same order."""
+    fast, slow = ndplan.build(*shape), ndplan.build_loops(*shape)
+    assert len(fast) == len(slow)
+    for a, b in zip(fast, slow):
+        assert (a.n_nodes, a.n_own, a.n_border) == (b.n_nodes, b.n_own, b.n_border)
+        for name in ('own', 'border', 'parent_slot', 'rect'):
+            x, y = getattr(a, name), getattr(b, name)
+            assert x.dtype == y.dtype and np.array_equal(x, y), name
